@@ -1,0 +1,550 @@
+// fqk_api.cu -- the C ABI of include/fqk.h: context, batch staging, kernel
+// launches, run-level merge (NCCL) and the host-side packer.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <dlfcn.h>
+#include "fqk_kernels.h"
+#include "fqk_fused.h"
+
+// ------------------------------------------------------------------- NCCL
+// NCCL is bound at run time (dlopen) so that the library also loads on hosts
+// without it; only ncclUniqueId crosses the ABI (as 128 opaque bytes).
+namespace nccl {
+struct UniqueId { char internal[128]; };
+typedef void* Comm;
+typedef int (*GetUniqueId_t)(UniqueId*);
+typedef int (*CommInitRank_t)(Comm*, int, UniqueId, int);
+typedef int (*AllReduce_t)(const void*, void*, size_t, int, int, Comm, cudaStream_t);
+typedef int (*CommDestroy_t)(Comm);
+typedef const char* (*GetErrorString_t)(int);
+enum { Uint8 = 1, Uint32 = 3, Uint64 = 5 };      // ncclDataType_t, nccl.h
+enum { Sum = 0, Max = 2, Min = 3 };              // ncclRedOp_t, nccl.h
+static void* handle = nullptr;
+static GetUniqueId_t GetUniqueId; static CommInitRank_t CommInitRank; static AllReduce_t AllReduce;
+static CommDestroy_t CommDestroy; static GetErrorString_t GetErrorString;
+static bool load(){
+    if(handle) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for(const char* n : names){ handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if(handle) break; }
+    if(!handle) return false;
+    GetUniqueId = (GetUniqueId_t)dlsym(handle, "ncclGetUniqueId");
+    CommInitRank = (CommInitRank_t)dlsym(handle, "ncclCommInitRank");
+    AllReduce = (AllReduce_t)dlsym(handle, "ncclAllReduce");
+    CommDestroy = (CommDestroy_t)dlsym(handle, "ncclCommDestroy");
+    GetErrorString = (GetErrorString_t)dlsym(handle, "ncclGetErrorString");
+    return GetUniqueId && CommInitRank && AllReduce && CommDestroy;
+}
+}
+
+// ---------------------------------------------------------------- context
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    int ensure(size_t bytes){
+        if(bytes <= cap) return 0;
+        if(p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        if(cudaMalloc(&p, want) != cudaSuccess){ p = nullptr; return FQK_E_NOMEM; }
+        cap = want;
+        return 0;
+    }
+    void release(){ if(p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct StagedBatch { DevBuf off, len, b2, q; DevBatch dev; };
+
+struct fqk_ctx {
+    DevParams D;
+    int device = 0, rank = 0, nranks = 1, sms = 148;
+    cudaStream_t stream = nullptr;
+    uint64_t* flat = nullptr;                 // device accumulators (fq_stats_layout)
+    uint32_t* err = nullptr;                  // device error flag
+    unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
+    uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
+    StagedBatch st[2];
+    DevBuf res1, res2, resp;
+    nccl::Comm comm = nullptr;
+    uint64_t launches = 0;
+    int impl = 0;
+    int stats_cs_se = 0, stats_cs_pe = 0;     // cycles privatised in shared memory (0 = global atomics)
+    bool timing = false;
+    struct Ev { cudaEvent_t a, b; int slot; };
+    std::vector<Ev> evs;
+    std::vector<cudaEvent_t> evpool;
+    double t_ms[FQK_T_SLOTS] = {0}; uint64_t t_n[FQK_T_SLOTS] = {0};
+    std::string error;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(fqk_ctx* c, int code, const std::string& msg){
+    if(c) c->error = msg; else g_create_error = msg;
+    return code;
+}
+#define CU(call) do{ cudaError_t e_ = (call); if(e_ != cudaSuccess) return fail(c, FQK_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); }while(0)
+
+static cudaEvent_t ev_get(fqk_ctx* c){
+    if(!c->evpool.empty()){ cudaEvent_t e = c->evpool.back(); c->evpool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+struct Timer {
+    fqk_ctx* c; int slot; cudaEvent_t a = nullptr;
+    Timer(fqk_ctx* c_, int s) : c(c_), slot(s) { if(c->timing){ a = ev_get(c); cudaEventRecord(a, c->stream); } }
+    ~Timer(){ if(a){ cudaEvent_t b = ev_get(c); cudaEventRecord(b, c->stream); c->evs.push_back({a, b, slot}); } }
+};
+static void timers_collect(fqk_ctx* c){
+    for(auto& e : c->evs){
+        cudaEventSynchronize(e.b);
+        float ms = 0; cudaEventElapsedTime(&ms, e.a, e.b);
+        c->t_ms[e.slot] += ms; c->t_n[e.slot] += 1;
+        c->evpool.push_back(e.a); c->evpool.push_back(e.b);
+    }
+    c->evs.clear();
+}
+
+// ----------------------------------------------------------------- params
+extern "C" void fqk_default_params(fq_params* p){
+    memset(p, 0, sizeof(*p));
+    p->abi_version = FQK_ABI_VERSION;
+    // defaults of /root/reference/src/options.h after CLI11's flag reset and Options::update()
+    p->cut_front_window = p->cut_tail_window = p->cut_right_window = 4;
+    p->cut_front_qual = p->cut_tail_qual = p->cut_right_qual = 20;
+    p->polyg_min_len = 10; p->polyg_max_mismatch = 1; p->polyg_one_mismatch_each = 10;
+    p->polyx_base_mask = 31; p->polyx_min_len = 10; p->polyx_max_mismatch = 1; p->polyx_one_mismatch_each = 10;
+    p->low_quality_limit = 20 + 33; p->low_quality_base_limit = 22; p->n_base_limit = 5;
+    p->min_read_length = 15; p->complexity_threshold = 0.3;
+    p->overlap_require = 30; p->overlap_diff_limit = 5; p->insert_size_max = 512;
+    p->dup_keylen = 12; p->max_cycles = 512;
+}
+
+extern "C" int fqk_stats_layout(const fq_params* p, fq_stats_layout* L){
+    if(!p || !L) return FQK_E_INVALID;
+    memset(L, 0, sizeof(*L));
+    const uint64_t C = p->max_cycles > 0 ? (uint64_t)p->max_cycles : 512;
+    L->max_cycles = C;
+    L->kmer_bins = p->kmer_len > 0 ? (1ull << (2 * p->kmer_len)) : 0;
+    L->s_q20 = 0; L->s_q30 = 8 * C; L->s_content = 16 * C; L->s_qualsum = 24 * C;
+    L->s_total_base = 32 * C; L->s_total_qual = 33 * C;
+    L->s_reads = 34 * C; L->s_length_sum = 34 * C + 1; L->s_kmer = 34 * C + 2;
+    L->stats_stride = 34 * C + 2 + L->kmer_bins;
+    for(int s = 0; s < 4; ++s) L->stats_off[s] = (uint64_t)s * L->stats_stride;
+    uint64_t o = 4 * L->stats_stride;
+    L->filter_off = o; o += FQK_FILTER_RESULT_TYPES;
+    L->adapter_reads_off = o++; L->adapter_bases_off = o++;
+    L->polyx_reads_off = o; o += 5; L->polyx_bases_off = o; o += 5;
+    L->merged_pairs_off = o++;
+    L->insert_hist_off = o; L->insert_hist_len = (uint64_t)p->insert_size_max + 1; o += L->insert_hist_len;
+    L->total_u64 = o;
+    L->dup_bins = p->dup_enabled ? (1ull << (2 * p->dup_keylen)) : 0;
+    return 0;
+}
+
+static int cls_of_char(char ch){
+    switch(ch){ case 'A': return 0; case 'T': return 1; case 'C': return 2; case 'G': return 3; case 'N': return 4; default: return -1; }
+}
+
+static int validate_params(const fq_params* p, std::string& why){
+    if(p->abi_version != FQK_ABI_VERSION){ why = "abi_version mismatch"; return FQK_E_INVALID; }
+    if(p->correction_enabled){ why = "PE base correction (-c) is not on the hot path yet"; return FQK_E_INVALID; }
+    if((p->cut_front_enabled && p->cut_front_window < 1) || (p->cut_tail_enabled && p->cut_tail_window < 1) ||
+       (p->cut_right_enabled && p->cut_right_window < 1)){ why = "cut window must be >= 1"; return FQK_E_INVALID; }
+    if(p->polyg_enabled && (p->polyg_one_mismatch_each < 1 || (p->is_paired && p->polyg_min_len < 1))){ why = "polyG one_mismatch_each must be >= 1"; return FQK_E_INVALID; }
+    if(p->polyx_enabled && p->polyx_one_mismatch_each < 1){ why = "polyX one_mismatch_each must be >= 1"; return FQK_E_INVALID; }
+    if(p->kmer_len != 0 && (p->kmer_len < 4 || p->kmer_len > 15)){ why = "kmer_len must be 0 or 4..15"; return FQK_E_INVALID; }
+    if(p->dup_enabled && (p->dup_keylen < 12 || p->dup_keylen > 14)){ why = "dup_keylen must be 12..14 on the device"; return FQK_E_INVALID; }
+    if(p->adapter_r1_len < 0 || p->adapter_r1_len > FQK_MAX_ADAPTER || p->adapter_r2_len < 0 || p->adapter_r2_len > FQK_MAX_ADAPTER){ why = "adapter too long"; return FQK_E_INVALID; }
+    for(int i = 0; i < p->adapter_r1_len; ++i) if(cls_of_char(p->adapter_r1[i]) < 0){ why = "adapter_r1 outside ACGTN"; return FQK_E_ALPHABET; }
+    for(int i = 0; i < p->adapter_r2_len; ++i) if(cls_of_char(p->adapter_r2[i]) < 0){ why = "adapter_r2 outside ACGTN"; return FQK_E_ALPHABET; }
+    if(p->max_cycles < 0 || p->max_cycles > 65535){ why = "max_cycles out of range"; return FQK_E_INVALID; }
+    if(p->insert_size_max < 1 || p->insert_size_max > 65534){ why = "insert_size_max out of range"; return FQK_E_INVALID; }
+    if(p->trim_front1 < 0 || p->trim_tail1 < 0 || p->trim_front2 < 0 || p->trim_tail2 < 0){ why = "negative trim"; return FQK_E_INVALID; }
+    return 0;
+}
+
+// ----------------------------------------------------------------- create
+extern "C" int fqk_nccl_unique_id(void* out128){
+    if(!out128) return FQK_E_INVALID;
+    if(!nccl::load()) return FQK_E_NCCL;
+    nccl::UniqueId id;
+    if(nccl::GetUniqueId(&id) != 0) return FQK_E_NCCL;
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+extern "C" int fqk_reset(fqk_ctx* c){
+    if(!c) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(c->flat, 0, c->D.L.total_u64 * sizeof(uint64_t), c->stream));
+    CU(cudaMemsetAsync(c->err, 0, sizeof(uint32_t), c->stream));
+    if(c->D.L.dup_bins){
+        CU(cudaMemsetAsync(c->tab128, 0, c->D.L.dup_bins * 16, c->stream));
+        CU(cudaMemsetAsync(c->first64, 0xFF, c->D.L.dup_bins * 8, c->stream));
+        c->dup_final = false;
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal, int rank, int nranks,
+                          const void* nccl_unique_id){
+    if(!out || !p) return fail(nullptr, FQK_E_INVALID, "null argument");
+    *out = nullptr;
+    std::string why;
+    int rc = validate_params(p, why);
+    if(rc) return fail(nullptr, rc, why);
+    if(nranks < 1 || rank < 0 || rank >= nranks) return fail(nullptr, FQK_E_INVALID, "bad rank/nranks");
+    if(nranks > 1 && !nccl_unique_id) return fail(nullptr, FQK_E_INVALID, "nccl_unique_id required when nranks > 1");
+    int ndev = 0;
+    if(cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, FQK_E_CUDA, "no CUDA device: the hot path has no CPU fallback");
+    if(device_ordinal < 0 || device_ordinal >= ndev) return fail(nullptr, FQK_E_INVALID, "bad device ordinal");
+    fqk_ctx* c = new fqk_ctx();
+    c->device = device_ordinal; c->rank = rank; c->nranks = nranks;
+    memset(&c->D, 0, sizeof(c->D));
+    c->D.P = *p;
+    if(c->D.P.max_cycles == 0) c->D.P.max_cycles = 512;
+    for(int i = 0; i < p->adapter_r1_len; ++i) c->D.ad1[i] = (uint8_t)cls_of_char(p->adapter_r1[i]);
+    for(int i = 0; i < p->adapter_r2_len; ++i) c->D.ad2[i] = (uint8_t)cls_of_char(p->adapter_r2[i]);
+    fqk_stats_layout(&c->D.P, &c->D.L);
+    auto bail = [&](int code, const std::string& m){ std::string mm = m; fqk_destroy(c); return fail(nullptr, code, mm); };
+    if(cudaSetDevice(device_ordinal) != cudaSuccess) return bail(FQK_E_CUDA, "cudaSetDevice failed");
+    cudaDeviceProp prop;
+    if(cudaGetDeviceProperties(&prop, device_ordinal) != cudaSuccess) return bail(FQK_E_CUDA, "cudaGetDeviceProperties failed");
+    c->sms = prop.multiProcessorCount;
+    if(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(FQK_E_CUDA, "stream create failed");
+    if(cudaMalloc(&c->flat, c->D.L.total_u64 * sizeof(uint64_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "accumulator alloc failed");
+    if(cudaMalloc(&c->err, sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "flag alloc failed");
+    c->D.err = c->err;
+    if(c->D.L.dup_bins){
+        const uint64_t n = c->D.L.dup_bins;
+        if(cudaMalloc(&c->tab128, n * 16) != cudaSuccess || cudaMalloc(&c->first64, n * 8) != cudaSuccess ||
+           cudaMalloc(&c->d_dups, n * 8) != cudaSuccess || cudaMalloc(&c->d_counts, n * 4) != cudaSuccess ||
+           cudaMalloc(&c->d_gc, n) != cudaSuccess) return bail(FQK_E_NOMEM, "dup table alloc failed");
+    }
+    // shared-memory budget of the generic stats kernels
+    const size_t smem_max = prop.sharedMemPerBlockOptin > 2048 ? prop.sharedMemPerBlockOptin - 2048 : 0;
+    const size_t C = c->D.L.max_cycles;
+    c->stats_cs_se = (2 * 20 * C * 4 <= smem_max) ? (int)C : 0;
+    c->stats_cs_pe = (4 * 20 * C * 4 <= smem_max) ? (int)C : 0;
+    if(c->stats_cs_se) cudaFuncSetAttribute(k_stats_se, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 20 * (int)C * 4);
+    if(c->stats_cs_pe) cudaFuncSetAttribute(k_stats_pe, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 20 * (int)C * 4);
+    fused_configure(prop);
+    if(nranks > 1){
+        if(!nccl::load()) return bail(FQK_E_NCCL, "libnccl.so.2 not found");
+        nccl::UniqueId id; memcpy(&id, nccl_unique_id, sizeof(id));
+        int e = nccl::CommInitRank(&c->comm, nranks, id, rank);
+        if(e != 0) return bail(FQK_E_NCCL, std::string("ncclCommInitRank: ") + (nccl::GetErrorString ? nccl::GetErrorString(e) : "?"));
+    }
+    rc = fqk_reset(c);
+    if(rc){ std::string m = c->error; fqk_destroy(c); return fail(nullptr, rc, m); }
+    *out = c;
+    return 0;
+}
+
+extern "C" void fqk_destroy(fqk_ctx* c){
+    if(!c) return;
+    cudaSetDevice(c->device);
+    if(c->stream) cudaStreamSynchronize(c->stream);
+    if(c->comm) nccl::CommDestroy(c->comm);
+    for(auto& e : c->evs){ cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for(auto& e : c->evpool) cudaEventDestroy(e);
+    for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
+    c->res1.release(); c->res2.release(); c->resp.release();
+    cudaFree(c->flat); cudaFree(c->err); cudaFree(c->tab128); cudaFree(c->first64);
+    cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
+    if(c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" const char* fqk_last_error(const fqk_ctx* c){
+    return c ? c->error.c_str() : g_create_error.c_str();
+}
+extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
+extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 1) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
+extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
+    if(!c) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    timers_collect(c);
+    for(int i = 0; i < FQK_T_SLOTS; ++i){
+        if(ms) ms[i] = c->t_ms[i];
+        if(launches) launches[i] = c->t_n[i];
+        c->t_ms[i] = 0; c->t_n[i] = 0;
+    }
+    return 0;
+}
+
+// --------------------------------------------------------------- launches
+static int grid_for(fqk_ctx* c, uint32_t n, int per_block, int blocks_per_sm){
+    long long need = ((long long)n + per_block - 1) / per_block;
+    long long cap = (long long)c->sms * blocks_per_sm;
+    return (int)std::max(1LL, std::min(need, cap));
+}
+
+static DevBatch to_dev(const fq_batch* b){
+    DevBatch d; d.n = b->n_reads; d.first_index = b->first_index; d.offsets = b->offsets; d.lengths = b->lengths;
+    d.bases2 = b->bases2; d.qual = b->qual;
+    return d;
+}
+
+static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
+    if(B.n == 0) return 0;
+    Timer all(c, FQK_T_ALL);
+    bool done = false;
+    if(c->impl == 0 && fused_supported_se(c->D)){
+        Timer t(c, FQK_T_FUSED);
+        int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
+        if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");
+        c->launches += nl; done = true;
+    }
+    if(!done){
+        { Timer t(c, FQK_T_TRIM);
+          k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
+        { Timer t(c, FQK_T_STATS);
+          const int Cs = c->stats_cs_se;
+          k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
+          c->launches++; }
+    }
+    if(c->D.P.dup_enabled){
+        Timer t(c, FQK_T_DUP);
+        k_dup<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, B, 0, c->tab128, c->first64); c->launches++;
+        c->dup_final = false;
+    }
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int launch_pe(fqk_ctx* c, const DevBatch& B1, const DevBatch& B2, fq_read_result* o1, fq_read_result* o2,
+                     fq_pair_result* op){
+    if(B1.n == 0) return 0;
+    Timer all(c, FQK_T_ALL);
+    { Timer t(c, FQK_T_TRIM);
+      k_trim_pe<<<grid_for(c, B1.n, 128, 8), 128, 0, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat); c->launches++; }
+    { Timer t(c, FQK_T_STATS);
+      const int Cs = c->stats_cs_pe;
+      k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs);
+      c->launches++; }
+    if(c->D.P.dup_enabled){
+        Timer t(c, FQK_T_DUP);
+        k_dup<<<grid_for(c, B1.n, 256, 8), 256, 0, c->stream>>>(c->D, B1, B2, 1, c->tab128, c->first64); c->launches++;
+        c->dup_final = false;
+    }
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int check_err_flag(fqk_ctx* c){
+    uint32_t e = 0;
+    CU(cudaMemcpyAsync(&e, c->err, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if(e & 1) return fail(c, FQK_E_LIMIT, "a read (or merged read) is longer than max_cycles");
+    if(e & 2) return fail(c, FQK_E_INVALID, "batch offsets must be multiples of FQK_PAD");
+    return 0;
+}
+
+extern "C" int fqk_sync(fqk_ctx* c){
+    if(!c) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    return check_err_flag(c);
+}
+
+extern "C" int fqk_process_se_device(fqk_ctx* c, const fq_batch* in, fq_read_result* out){
+    if(!c || !in || (!out && in->n_reads)) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    CU(cudaSetDevice(c->device));
+    return launch_se(c, to_dev(in), out);
+}
+
+extern "C" int fqk_process_pe_device(fqk_ctx* c, const fq_batch* r1, const fq_batch* r2, fq_read_result* o1,
+                                     fq_read_result* o2, fq_pair_result* op){
+    if(!c || !r1 || !r2) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    if(r1->n_reads != r2->n_reads) return fail(c, FQK_E_INVALID, "read1/read2 batches differ in size");
+    CU(cudaSetDevice(c->device));
+    return launch_pe(c, to_dev(r1), to_dev(r2), o1, o2, op);
+}
+
+// host batch -> device staging (4 H2D copies on the context's stream)
+static int stage(fqk_ctx* c, StagedBatch& s, const fq_batch* b){
+    const size_t n = b->n_reads;
+    if(b->total_bases % FQK_PAD) return fail(c, FQK_E_INVALID, "total_bases must be a multiple of FQK_PAD");
+    if(s.off.ensure(n * 4 + 16) || s.len.ensure(n * 2 + 16) || s.b2.ensure(b->total_bases / 4 + 16) || s.q.ensure(b->total_bases + 16))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    CU(cudaMemcpyAsync(s.off.p, b->offsets, n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.len.p, b->lengths, n * 2, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.b2.p, b->bases2, b->total_bases / 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.q.p, b->qual, b->total_bases, cudaMemcpyHostToDevice, c->stream));
+    s.dev.n = b->n_reads; s.dev.first_index = b->first_index;
+    s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
+    s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
+    return 0;
+}
+
+extern "C" int fqk_process_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out){
+    if(!c || !in || (!out && in->n_reads)) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    if(in->n_reads == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    int rc = stage(c, c->st[0], in); if(rc) return rc;
+    const size_t n = in->n_reads;
+    if(c->res1.ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
+    CU(cudaMemcpyAsync(out, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    return check_err_flag(c);
+}
+
+extern "C" int fqk_process_pe(fqk_ctx* c, const fq_batch* r1, const fq_batch* r2, fq_read_result* o1,
+                              fq_read_result* o2, fq_pair_result* op){
+    if(!c || !r1 || !r2) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    if(r1->n_reads != r2->n_reads) return fail(c, FQK_E_INVALID, "read1/read2 batches differ in size");
+    if(r1->n_reads == 0) return 0;
+    if(!o1 || !o2 || !op) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    int rc = stage(c, c->st[0], r1); if(rc) return rc;
+    rc = stage(c, c->st[1], r2); if(rc) return rc;
+    const size_t n = r1->n_reads;
+    if(c->res1.ensure(n * sizeof(fq_read_result)) || c->res2.ensure(n * sizeof(fq_read_result)) ||
+       c->resp.ensure(n * sizeof(fq_pair_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_pe(c, c->st[0].dev, c->st[1].dev, (fq_read_result*)c->res1.p, (fq_read_result*)c->res2.p, (fq_pair_result*)c->resp.p);
+    if(rc) return rc;
+    CU(cudaMemcpyAsync(o1, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(o2, c->res2.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(op, c->resp.p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
+    return check_err_flag(c);
+}
+
+// ---------------------------------------------------------------- finalize
+// cross-rank merge helpers for the duplication table
+__global__ void k_dup_split(uint64_t bins, const unsigned long long* tab128, unsigned long long* kmin){
+    for(uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < bins; k += (uint64_t)gridDim.x * blockDim.x)
+        kmin[k] = (uint32_t)(tab128[2 * k + 1] >> 32) ? tab128[2 * k] : ~0ull;
+}
+__global__ void k_dup_mask(uint64_t bins, const unsigned long long* tab128, const unsigned long long* kmin,
+                           uint32_t* cnt, uint32_t* idx){
+    for(uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < bins; k += (uint64_t)gridDim.x * blockDim.x){
+        const unsigned long long lo = tab128[2 * k], hi = tab128[2 * k + 1];
+        const uint32_t c = (uint32_t)(hi >> 32);
+        const bool keep = c && lo == kmin[k];
+        cnt[k] = keep ? c : 0; idx[k] = keep ? (uint32_t)hi : 0xFFFFFFFFu;
+    }
+}
+__global__ void k_dup_join(uint64_t bins, unsigned long long* tab128, const unsigned long long* kmin,
+                           const uint32_t* cnt, const uint32_t* idx){
+    for(uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < bins; k += (uint64_t)gridDim.x * blockDim.x){
+        tab128[2 * k] = cnt[k] ? kmin[k] : 0;
+        tab128[2 * k + 1] = ((unsigned long long)cnt[k] << 32) | idx[k];
+    }
+}
+
+static int dup_finalize(fqk_ctx* c){
+    const uint64_t n = c->D.L.dup_bins;
+    if(!n || c->dup_final) return 0;
+    const int g = c->sms * 8;
+    if(c->nranks > 1){
+        // min over kmer32, then sum of the counts / min of the indices that carry the global minimum,
+        // and min over the packed (first index, gc) word: 4 all-reduces, once per run
+        unsigned long long* kmin = (unsigned long long*)c->d_dups;       // reuse output arrays as scratch
+        uint32_t* cnt = c->d_counts; uint32_t* idx = nullptr;
+        CU(cudaMalloc(&idx, n * 4));
+        k_dup_split<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin);
+        int e = nccl::AllReduce(kmin, kmin, n, nccl::Uint64, nccl::Min, c->comm, c->stream);
+        k_dup_mask<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin, cnt, idx);
+        if(!e) e = nccl::AllReduce(cnt, cnt, n, nccl::Uint32, nccl::Sum, c->comm, c->stream);
+        if(!e) e = nccl::AllReduce(idx, idx, n, nccl::Uint32, nccl::Min, c->comm, c->stream);
+        if(!e) e = nccl::AllReduce(c->first64, c->first64, n, nccl::Uint64, nccl::Min, c->comm, c->stream);
+        k_dup_join<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin, cnt, idx);
+        c->launches += 3;
+        cudaStreamSynchronize(c->stream);
+        cudaFree(idx);
+        if(e) return fail(c, FQK_E_NCCL, "ncclAllReduce (dup table) failed");
+    }
+    k_dup_finish<<<g, 256, 0, c->stream>>>(n, c->tab128, c->first64, c->d_dups, c->d_counts, c->d_gc);
+    c->launches++;
+    CU(cudaGetLastError());
+    c->dup_final = true;
+    return 0;
+}
+
+extern "C" int fqk_finalize(fqk_ctx* c, uint64_t* flat){
+    if(!c || !flat) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    int rc = check_err_flag(c); if(rc) return rc;
+    const size_t n = c->D.L.total_u64;
+    if(c->nranks > 1){
+        // Stats::merge / FilterResult::merge are plain sums: one all-reduce of the flat buffer.
+        // The result is left in a scratch copy so that finalize can be called again.
+        uint64_t* tmp = nullptr;
+        CU(cudaMalloc(&tmp, n * 8));
+        int e = nccl::AllReduce(c->flat, tmp, n, nccl::Uint64, nccl::Sum, c->comm, c->stream);
+        if(e){ cudaFree(tmp); return fail(c, FQK_E_NCCL, "ncclAllReduce (stats) failed"); }
+        cudaMemcpyAsync(flat, tmp, n * 8, cudaMemcpyDeviceToHost, c->stream);
+        cudaStreamSynchronize(c->stream);
+        cudaFree(tmp);
+    }else{
+        CU(cudaMemcpyAsync(flat, c->flat, n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    return dup_finalize(c);
+}
+
+extern "C" int fqk_dup_table(fqk_ctx* c, uint64_t* dups, uint32_t* counts, uint8_t* gc){
+    if(!c) return FQK_E_INVALID;
+    const uint64_t n = c->D.L.dup_bins;
+    if(!n) return fail(c, FQK_E_INVALID, "duplication analysis is not enabled");
+    CU(cudaSetDevice(c->device));
+    int rc = dup_finalize(c); if(rc) return rc;
+    if(dups) CU(cudaMemcpyAsync(dups, c->d_dups, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    if(counts) CU(cudaMemcpyAsync(counts, c->d_counts, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if(gc) CU(cudaMemcpyAsync(gc, c->d_gc, n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ------------------------------------------------------------------ packer
+extern "C" uint64_t fqk_packed_bases(uint32_t n, const uint64_t* src_off){
+    uint64_t t = 0;
+    for(uint32_t r = 0; r < n; ++r){ uint64_t l = src_off[r + 1] - src_off[r]; t += (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD; }
+    return t;
+}
+
+extern "C" int fqk_pack_ascii(uint32_t n, const char* seq, const char* qual, const uint64_t* src_off,
+                              uint32_t* offsets, uint16_t* lengths, uint8_t* bases2, uint8_t* qual_out){
+    static int8_t lut[256]; static bool init = false;
+    if(!init){ for(int i = 0; i < 256; ++i) lut[i] = -1; lut['A'] = 0; lut['T'] = 1; lut['C'] = 2; lut['G'] = 3; lut['N'] = 4; init = true; }
+    uint64_t pos = 0;
+    for(uint32_t r = 0; r < n; ++r){
+        const uint64_t l = src_off[r + 1] - src_off[r];
+        if(l > FQK_MAX_READ_LEN) return FQK_E_LIMIT;
+        if(pos > 0xFFFFFFFFull) return FQK_E_LIMIT;
+        offsets[r] = (uint32_t)pos; lengths[r] = (uint16_t)l;
+        const uint64_t padded = (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD;
+        const char* s = seq + src_off[r]; const char* q = qual + src_off[r];
+        uint8_t* qo = qual_out + pos; uint8_t* bo = bases2 + pos / 4;
+        memset(bo, 0, padded / 4);
+        for(uint64_t i = 0; i < l; ++i){
+            const int c = lut[(uint8_t)s[i]];
+            if(c < 0) return FQK_E_ALPHABET;
+            const uint8_t qq = (uint8_t)q[i];
+            if(qq & 0x80) return FQK_E_ALPHABET;
+            if(c == 4) qo[i] = qq | 0x80;
+            else { qo[i] = qq; bo[i >> 2] |= (uint8_t)(c << ((i & 3) * 2)); }
+        }
+        memset(qo + l, 0, padded - l);
+        pos += padded;
+    }
+    return 0;
+}
+
+extern "C" void* fqk_host_alloc(size_t bytes){
+    void* p = nullptr;
+    if(cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess){ cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void fqk_host_free(void* p){ if(p) cudaFreeHost(p); }

@@ -1,0 +1,463 @@
+// fqk_kernels.cu -- generic (any length, any option) kernels of the hot path.
+//   k_trim_se / k_trim_pe : one thread per read / read pair, records + run counters
+//   k_stats_se / k_stats_pe: one warp per read, shared-memory privatised per-cycle
+//                            histograms (global atomics when they do not fit)
+//   k_dup                 : duplication table, order-independent (min, count, first) monoid
+// The specialised fused SE kernel lives in fqk_fused.cu.
+#include "fqk_trim.cuh"
+#include "fqk_kernels.h"
+
+// ------------------------------------------------------------ block counters
+// per-block shared counters flushed with one atomic each at block end
+struct BlockCounters {
+    uint32_t filter[FQK_FILTER_RESULT_TYPES];
+    uint32_t polyx_reads[5], polyx_bases[5];
+    uint32_t adapter_reads, adapter_bases, merged_pairs;
+};
+
+__device__ inline void counters_zero(BlockCounters* bc){
+    uint32_t* p = reinterpret_cast<uint32_t*>(bc);
+    for(int i = threadIdx.x; i < (int)(sizeof(BlockCounters) / 4); i += blockDim.x) p[i] = 0;
+}
+__device__ inline void counters_add_tally(BlockCounters* bc, const Tally& t){
+#pragma unroll
+    for(int b = 0; b < 5; ++b){
+        if(t.polyx_reads[b]) atomicAdd(&bc->polyx_reads[b], t.polyx_reads[b]);
+        if(t.polyx_bases[b]) atomicAdd(&bc->polyx_bases[b], t.polyx_bases[b]);
+    }
+    if(t.adapter_reads) atomicAdd(&bc->adapter_reads, t.adapter_reads);
+    if(t.adapter_bases) atomicAdd(&bc->adapter_bases, t.adapter_bases);
+}
+__device__ inline void counters_flush(const BlockCounters* bc, const fq_stats_layout& L, uint64_t* flat){
+    for(int i = threadIdx.x; i < FQK_FILTER_RESULT_TYPES; i += blockDim.x)
+        if(bc->filter[i]) add_u64(flat + L.filter_off + i, bc->filter[i]);
+    if(threadIdx.x < 5){
+        if(bc->polyx_reads[threadIdx.x]) add_u64(flat + L.polyx_reads_off + threadIdx.x, bc->polyx_reads[threadIdx.x]);
+        if(bc->polyx_bases[threadIdx.x]) add_u64(flat + L.polyx_bases_off + threadIdx.x, bc->polyx_bases[threadIdx.x]);
+    }
+    if(threadIdx.x == 0){
+        if(bc->adapter_reads) add_u64(flat + L.adapter_reads_off, bc->adapter_reads);
+        if(bc->adapter_bases) add_u64(flat + L.adapter_bases_off, bc->adapter_bases);
+        if(bc->merged_pairs) add_u64(flat + L.merged_pairs_off, bc->merged_pairs);
+    }
+}
+
+// ------------------------------------------------------------------ SE trim
+// loop body of SingleEndProcessor::processSingleEnd, src/seprocessor.cpp:313-340
+__device__ inline void se_read(const DevParams& D, ReadView& v, fq_read_result& rec, Tally& tl){
+    const fq_params& P = D.P;
+    const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
+    if(alive){
+        if(P.polyg_enabled)
+            dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
+        if(P.adapter_trim_enabled && P.adapter_r1_len > 0)
+            dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
+        if(P.polyx_enabled)
+            dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
+        if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
+    }
+    rec.result = (uint8_t)dev_pass_filter_view(P, v, !alive);
+    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
+    else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
+}
+
+__global__ void __launch_bounds__(256) k_trim_se(const __grid_constant__ DevParams D, DevBatch B,
+                                                  fq_read_result* __restrict__ out, uint64_t* __restrict__ flat){
+    __shared__ BlockCounters bc;
+    counters_zero(&bc);
+    __syncthreads();
+    Tally tl = {};
+    for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B.n; r += gridDim.x * blockDim.x){
+        ReadView v = make_view(B, r);
+        fq_read_result rec = {};
+        se_read(D, v, rec, tl);
+        out[r] = rec;
+        atomicAdd(&bc.filter[rec.result], 1u);          // addFilterResult, mPaired == false
+    }
+    counters_add_tally(&bc, tl);
+    __syncthreads();
+    counters_flush(&bc, D.L, flat);
+}
+
+// ------------------------------------------------------------------ PE trim
+__device__ inline int insert_size_of(const fq_params& P, const ReadView& a, const ReadView& b, const OvRes& ov){
+    int isize = P.insert_size_max;                       // statInsertSize, src/peprocessor.cpp:510-523
+    if(ov.overlapped) isize = ov.offset > 0 ? a.len + b.len - ov.len : ov.len;
+    return min(isize, P.insert_size_max);
+}
+
+// base class / quality of base i of the merged read, src/overlapanalysis.cpp:77-93
+struct MergedGet {
+    const ReadView& a; const ReadView& b; int len1, ol;
+    __device__ __forceinline__ void operator()(int i, int& c, int& q) const {
+        if(i < len1){ c = a.cls(i); q = a.qual(i); }
+        else { const int j = ol + i - len1; c = rc_cls(b, j); q = b.qual(b.len - 1 - j); }
+    }
+};
+
+__global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
+                                                  fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
+                                                  fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat){
+    __shared__ BlockCounters bc;
+    counters_zero(&bc);
+    __syncthreads();
+    const fq_params& P = D.P;
+    Tally tl = {};
+    for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B1.n; r += gridDim.x * blockDim.x){
+        ReadView a = make_view(B1, r), b = make_view(B2, r);
+        fq_read_result rec1 = {}, rec2 = {};
+        fq_pair_result pr = {};
+        pr.insert_size = 0xFFFF;
+        // loop body of PairEndProcessor::processPairEnd, src/peprocessor.cpp:292-429 (threadId 0)
+        const bool a1 = dev_trim_and_cut(P, a, P.trim_front1, P.trim_tail1);
+        const bool a2 = dev_trim_and_cut(P, b, P.trim_front2, P.trim_tail2);
+        const bool both = a1 && a2;
+        if(both && P.polyg_enabled){
+            // src/peprocessor.cpp:297 hands (maxMismatch, oneEach, minLen) to (compareReq, maxMismatch, oneEach)
+            dev_trim_polyg(a, P.polyg_max_mismatch, P.polyg_one_mismatch_each, P.polyg_min_len, rec1, tl);
+            dev_trim_polyg(b, P.polyg_max_mismatch, P.polyg_one_mismatch_each, P.polyg_min_len, rec2, tl);
+        }
+        bool have_ov = false; OvRes ov = {0, 0, 0, 0};
+        if(both){
+            // first analyze(): :303 when -a/-c, else :330 (insert size only); identical inputs either way
+            ov = dev_analyze(a, b, P.overlap_diff_limit, P.overlap_require);
+            have_ov = true;
+            pr.flags |= FQK_P_OV1_DONE | (ov.overlapped ? FQK_P_OV1_OVERLAP : 0);
+            pr.ov1_offset = (int16_t)ov.offset; pr.ov1_len = (uint16_t)ov.len; pr.ov1_diff = (uint16_t)ov.diff;
+            const int isize = insert_size_of(P, a, b, ov);
+            pr.insert_size = (uint16_t)isize;
+            add_u64(flat + D.L.insert_hist_off + isize, 1);
+        }
+        bool modified = false;                            // reads changed since the first analyze()
+        if(both && P.adapter_trim_enabled){
+            // AdapterTrimmer::trimByOverlapAnalysis, src/adaptertrimmer.cpp:14-27
+            if(ov.diff <= 5 && ov.overlapped && ov.offset < 0 && ov.len > a.len / 3){
+                const int t1 = a.len - ov.len, t2 = b.len - ov.len;
+                a.len = ov.len; b.len = ov.len;
+                rec1.flags |= FQK_F_ADAPTER_OV; rec1.adapter_pos = (int16_t)ov.len; rec1.adapter_len = (uint16_t)t1;
+                rec2.flags |= FQK_F_ADAPTER_OV; rec2.adapter_pos = (int16_t)ov.len; rec2.adapter_len = (uint16_t)t2;
+                tl.adapter_reads += 2; tl.adapter_bases += (uint32_t)(t1 + t2);     // filterresult.cpp:159-161
+                modified = true;
+            }else{
+                if(P.adapter_r1_len > 0) modified |= dev_trim_by_sequence(a, D.ad1, P.adapter_r1_len, rec1, tl);
+                if(P.adapter_r2_len > 0) modified |= dev_trim_by_sequence(b, D.ad2, P.adapter_r2_len, rec2, tl);
+            }
+        }
+        if(both && P.polyx_enabled){
+            const int l1 = a.len, l2 = b.len;
+            dev_trim_polyx(a, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec1, tl);
+            dev_trim_polyx(b, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec2, tl);
+            modified |= (a.len != l1) | (b.len != l2);
+        }
+        if(both){
+            if(P.trim_max_len1 > 0 && P.trim_max_len1 < a.len){ view_resize(a, P.trim_max_len1); modified = true; }
+            if(P.trim_max_len2 > 0 && P.trim_max_len2 < b.len){ view_resize(b, P.trim_max_len2); modified = true; }
+        }
+        bool merge_processed = false; int res1 = 0, res2 = 0;
+        if(P.merge_enabled && both){
+            // second analyze(), :354: same answer as the first when neither read changed
+            OvRes ov2 = (have_ov && !modified) ? ov : dev_analyze(a, b, P.overlap_diff_limit, P.overlap_require);
+            pr.flags |= FQK_P_OV2_DONE | (ov2.overlapped ? FQK_P_OV2_OVERLAP : 0);
+            pr.ov2_offset = (int16_t)ov2.offset; pr.ov2_len = (uint16_t)ov2.len; pr.ov2_diff = (uint16_t)ov2.diff;
+            if(ov2.overlapped){
+                int result;
+                if(ov2.len == 0){ result = FQK_FAIL_LENGTH; }          // merge() == NULL
+                else{
+                    const int len1 = ov2.len + max(0, ov2.offset);
+                    const int len2 = ov2.offset > 0 ? b.len - ov2.len : 0;
+                    pr.merge_len1 = (uint16_t)len1; pr.merge_len2 = (uint16_t)len2;
+                    MergedGet mg{a, b, len1, ov2.len};
+                    result = dev_pass_filter(P, len1 + len2, false, mg);
+                    if(result == FQK_PASS_FILTER){ pr.flags |= FQK_P_MERGED; atomicAdd(&bc.merged_pairs, 1u); }
+                }
+                atomicAdd(&bc.filter[result], 2u);                      // :358
+                pr.merged_result = (uint8_t)result;
+                res1 = res2 = result;
+                merge_processed = true;
+            }else if(!P.merge_discard_unmerged){
+                res1 = dev_pass_filter_view(P, a, false); atomicAdd(&bc.filter[res1], 1u);
+                res2 = dev_pass_filter_view(P, b, false); atomicAdd(&bc.filter[res2], 1u);
+                merge_processed = true;
+            }
+            if(merge_processed) pr.flags |= FQK_P_MERGE_PROC;
+        }
+        if(!merge_processed){
+            res1 = dev_pass_filter_view(P, a, !a1);
+            res2 = dev_pass_filter_view(P, b, !a2);
+            atomicAdd(&bc.filter[max(res1, res2)], 2u);                 // :390, mPaired == true
+        }
+        rec1.result = (uint8_t)res1; rec2.result = (uint8_t)res2;
+        if(!a1) rec1.flags |= FQK_F_DROPPED; else { rec1.start = (uint16_t)a.start; rec1.len = (uint16_t)a.len; }
+        if(!a2) rec2.flags |= FQK_F_DROPPED; else { rec2.start = (uint16_t)b.start; rec2.len = (uint16_t)b.len; }
+        out1[r] = rec1; out2[r] = rec2; outp[r] = pr;
+    }
+    counters_add_tally(&bc, tl);
+    __syncthreads();
+    counters_flush(&bc, D.L, flat);
+}
+
+// -------------------------------------------------------------------- stats
+// Stats::statRead, src/stats.cpp:237-295.  A warp owns a read; lane j handles
+// cycles j, j+32, ...  Per block the four per-cycle arrays of every Stats
+// object are privatised in shared memory as u32 [kind][class][cycle] (kinds:
+// content, q20, q30, qualsum; classes A T C G N) and flushed once with 64-bit
+// global atomics, where total_base/total_qual are formed as sums over classes.
+struct StatsAcc {
+    uint32_t* sm;        // shared-memory privatised arrays or nullptr
+    uint64_t* flat;      // global accumulators
+    int Cs;              // cycles held in shared memory
+    const fq_stats_layout* L;
+    uint32_t* err;
+    int se;              // SE: shared slots are {pre1, post1} = Stats objects {0, 2}
+    unsigned long long* cnt;   // shared [4][2]: reads, length_sum per Stats object
+};
+
+__device__ __forceinline__ void stat_base(const StatsAcc& A, int obj, int i, int cls, int q){
+    const int qv = q - 33;
+    if(A.sm){
+        uint32_t* s = A.sm + (size_t)(A.se ? obj >> 1 : obj) * 20 * A.Cs + i;
+        atomicAdd(s + (0 * 5 + cls) * A.Cs, 1u);
+        if(q > '5') atomicAdd(s + (1 * 5 + cls) * A.Cs, 1u);
+        if(q > '?') atomicAdd(s + (2 * 5 + cls) * A.Cs, 1u);
+        atomicAdd(s + (3 * 5 + cls) * A.Cs, (uint32_t)qv);
+    }else{
+        const fq_stats_layout& L = *A.L;
+        uint64_t* S = A.flat + L.stats_off[obj];
+        const uint64_t C = L.max_cycles;
+        const int b = cls_to_bin(cls);
+        add_u64(S + L.s_content + b * C + i, 1);
+        if(q > '5') add_u64(S + L.s_q20 + b * C + i, 1);
+        if(q > '?') add_u64(S + L.s_q30 + b * C + i, 1);
+        add_u64(S + L.s_qualsum + b * C + i, (uint64_t)qv);
+        add_u64(S + L.s_total_base + i, 1);
+        add_u64(S + L.s_total_qual + i, (uint64_t)qv);
+    }
+}
+
+// one warp accumulates one read (any accessor); k-mers via the rolling 2-bit
+// code of Evaluator::seq2int (src/evaluator.cpp:3-49): counted iff all k bases are A/T/C/G
+template <class Get>
+__device__ inline void stat_stream(const StatsAcc& A, int obj, int len, int k, Get get){
+    const int lane = threadIdx.x & 31;
+    const fq_stats_layout& L = *A.L;
+    if(len > (int)L.max_cycles){ if(lane == 0) atomicOr(A.err, 1u); return; }
+    for(int i = lane; i < len; i += 32){
+        int c, q; get(i, c, q);
+        stat_base(A, obj, i, c, q);
+        if(k && i >= k - 1){
+            uint32_t code = 0; bool ok = true;
+            for(int j = i - k + 1; j <= i; ++j){
+                int cj, qj; get(j, cj, qj);
+                ok &= (cj != CLS_N);
+                code = (code << 2) | (uint32_t)(cj & 3);
+            }
+            if(ok) add_u64(A.flat + L.stats_off[obj] + L.s_kmer + code, 1);
+        }
+    }
+    if(lane == 0){
+        atomicAdd(A.cnt + obj * 2, 1ull);
+        atomicAdd(A.cnt + obj * 2 + 1, (unsigned long long)len);
+    }
+}
+
+__device__ inline void stats_cnt_flush(const StatsAcc& A){
+    const fq_stats_layout& L = *A.L;
+    if(threadIdx.x < 4 && A.cnt[threadIdx.x * 2]){
+        add_u64(A.flat + L.stats_off[threadIdx.x] + L.s_reads, A.cnt[threadIdx.x * 2]);
+        add_u64(A.flat + L.stats_off[threadIdx.x] + L.s_length_sum, A.cnt[threadIdx.x * 2 + 1]);
+    }
+}
+
+__device__ inline void stats_smem_zero(uint32_t* sm, int words){
+    for(int i = threadIdx.x; i < words; i += blockDim.x) sm[i] = 0;
+}
+
+__device__ inline void stats_smem_flush(const StatsAcc& A, int nobj, const int* objmap){
+    const fq_stats_layout& L = *A.L;
+    const uint64_t C = L.max_cycles;
+    for(int o = 0; o < nobj; ++o){
+        uint64_t* S = A.flat + L.stats_off[objmap[o]];
+        const uint32_t* s = A.sm + (size_t)o * 20 * A.Cs;
+        for(int i = threadIdx.x; i < A.Cs; i += blockDim.x){
+            uint64_t tb = 0, tq = 0;
+#pragma unroll
+            for(int cls = 0; cls < 5; ++cls){
+                const int b = cls_to_bin(cls);
+                const uint32_t n = s[(0 * 5 + cls) * A.Cs + i];
+                if(n){
+                    const uint32_t n20 = s[(1 * 5 + cls) * A.Cs + i], n30 = s[(2 * 5 + cls) * A.Cs + i];
+                    const uint32_t qs = s[(3 * 5 + cls) * A.Cs + i];
+                    add_u64(S + L.s_content + b * C + i, n);
+                    if(n20) add_u64(S + L.s_q20 + b * C + i, n20);
+                    if(n30) add_u64(S + L.s_q30 + b * C + i, n30);
+                    if(qs) add_u64(S + L.s_qualsum + b * C + i, qs);
+                    tb += n; tq += qs;
+                }
+            }
+            if(tb){ add_u64(S + L.s_total_base + i, tb); add_u64(S + L.s_total_qual + i, tq); }
+        }
+    }
+}
+
+struct ViewGet {
+    const ReadView& v;
+    __device__ __forceinline__ void operator()(int i, int& c, int& q) const { c = v.cls(i); q = v.qual(i); }
+};
+
+// SE: pre1 (obj 0) over the raw read, post1 (obj 2) over the kept part of passing reads
+__global__ void __launch_bounds__(256) k_stats_se(const __grid_constant__ DevParams D, DevBatch B,
+                                                   const fq_read_result* __restrict__ res,
+                                                   uint64_t* __restrict__ flat, int Cs){
+    extern __shared__ uint32_t sm[];
+    __shared__ unsigned long long cnt[8];
+    StatsAcc A{Cs ? sm : nullptr, flat, Cs, &D.L, D.err, 1, cnt};
+    if(threadIdx.x < 8) cnt[threadIdx.x] = 0;
+    if(Cs) stats_smem_zero(sm, 2 * 20 * Cs);
+    __syncthreads();
+    const int warps = blockDim.x >> 5, w = threadIdx.x >> 5;
+    const int k = D.P.kmer_len;
+    for(uint32_t r = blockIdx.x * warps + w; r < B.n; r += gridDim.x * warps){
+        ReadView v = make_view(B, r);
+        stat_stream(A, 0, v.len, k, ViewGet{v});
+        const fq_read_result rec = res[r];
+        if(!(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER){
+            v.start = rec.start; v.len = rec.len;
+            stat_stream(A, 2, v.len, k, ViewGet{v});
+        }
+    }
+    __syncthreads();
+    stats_cnt_flush(A);
+    if(Cs){ const int om[2] = {0, 2}; stats_smem_flush(A, 2, om); }
+}
+
+// PE: pre1, pre2 raw; post1/post2 following src/peprocessor.cpp:353-429
+__global__ void __launch_bounds__(256) k_stats_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
+                                                   const fq_read_result* __restrict__ res1,
+                                                   const fq_read_result* __restrict__ res2,
+                                                   const fq_pair_result* __restrict__ resp,
+                                                   uint64_t* __restrict__ flat, int Cs){
+    extern __shared__ uint32_t sm[];
+    __shared__ unsigned long long cnt[8];
+    StatsAcc A{Cs ? sm : nullptr, flat, Cs, &D.L, D.err, 0, cnt};
+    if(threadIdx.x < 8) cnt[threadIdx.x] = 0;
+    if(Cs) stats_smem_zero(sm, 4 * 20 * Cs);
+    __syncthreads();
+    const int warps = blockDim.x >> 5, w = threadIdx.x >> 5;
+    const int k = D.P.kmer_len;
+    const bool merge = D.P.merge_enabled;
+    for(uint32_t r = blockIdx.x * warps + w; r < B1.n; r += gridDim.x * warps){
+        ReadView a = make_view(B1, r), b = make_view(B2, r);
+        stat_stream(A, 0, a.len, k, ViewGet{a});
+        stat_stream(A, 1, b.len, k, ViewGet{b});
+        const fq_read_result r1 = res1[r], r2 = res2[r];
+        const fq_pair_result pr = resp[r];
+        const bool alive = !(r1.flags & FQK_F_DROPPED) && !(r2.flags & FQK_F_DROPPED);
+        if(!alive) continue;
+        a.start = r1.start; a.len = r1.len; b.start = r2.start; b.len = r2.len;
+        if(!merge){
+            if(r1.result == FQK_PASS_FILTER && r2.result == FQK_PASS_FILTER){          // :392-401
+                stat_stream(A, 2, a.len, k, ViewGet{a});
+                stat_stream(A, 3, b.len, k, ViewGet{b});
+            }
+        }else if(pr.flags & FQK_P_OV2_OVERLAP){
+            if(pr.flags & FQK_P_MERGED){                                               // :359-362
+                MergedGet mg{a, b, pr.merge_len1, pr.ov2_len};
+                stat_stream(A, 2, pr.merge_len1 + pr.merge_len2, k, mg);
+            }
+        }else if(pr.flags & FQK_P_MERGE_PROC){                                         // :367-380
+            if(r1.result == FQK_PASS_FILTER) stat_stream(A, 2, a.len, k, ViewGet{a});
+            if(r2.result == FQK_PASS_FILTER) stat_stream(A, 3, b.len, k, ViewGet{b});
+        }
+    }
+    __syncthreads();
+    stats_cnt_flush(A);
+    if(Cs){ const int om[4] = {0, 1, 2, 3}; stats_smem_flush(A, 4, om); }
+}
+
+// ---------------------------------------------------------------- duplicate
+// Duplicate::statRead / statPair / addRecord, src/duplicate.cpp:46-129, as an
+// order-independent reduction.  Per key:
+//   tab128[key] = { kmer32 (64) , count (32) | minidx (32) } under the monoid
+//      smaller kmer wins; equal kmers add counts and keep the smaller index
+//   first64[key] = min over reads of (global index << 8 | gc byte)
+// so that after the run  mDups = kmer32, mCounts = count and
+//   mGC = gc(first read of the key) if that read carries the final minimum else 0.
+__device__ __forceinline__ void cas128(unsigned long long* addr, unsigned long long clo, unsigned long long chi,
+                                       unsigned long long slo, unsigned long long shi,
+                                       unsigned long long& olo, unsigned long long& ohi){
+    asm volatile("{\n\t.reg .b128 c, s, d;\n\tmov.b128 c, {%3, %4};\n\tmov.b128 s, {%5, %6};\n\t"
+                 "atom.global.cas.b128 d, [%2], c, s;\n\tmov.b128 {%0, %1}, d;\n\t}"
+                 : "=l"(olo), "=l"(ohi) : "l"(addr), "l"(clo), "l"(chi), "l"(slo), "l"(shi) : "memory");
+}
+
+// 2-bit code of `n` bases from `p` (Duplicate::seq2int); false if any base is N
+__device__ inline bool dup_code(const ReadView& v, int p, int n, uint64_t& out){
+    uint64_t r = 0;
+    for(int i = 0; i < n; ++i){
+        if(v.isN(p + i)) return false;
+        r = (r << 2) | (uint64_t)v.code(p + i);
+    }
+    out = r;
+    return true;
+}
+
+__device__ inline uint32_t gc_count(const ReadView& v){
+    uint32_t g = 0;
+    for(int i = 0; i < v.len; ++i){ const int c = v.cls(i); g += (c == 2 || c == 3); }
+    return g;
+}
+
+__device__ inline void dup_insert(unsigned long long* tab128, unsigned long long* first64,
+                                  uint32_t key, uint64_t kmer, uint64_t gidx, uint32_t gcbyte){
+    atomicMin(first64 + key, (unsigned long long)((gidx << 8) | gcbyte));
+    unsigned long long* slot = tab128 + 2ull * key;
+    unsigned long long olo = slot[0], ohi = slot[1];       // racy peek; the CAS validates it
+    while(true){
+        unsigned long long nlo, nhi;
+        const uint32_t ocnt = (uint32_t)(ohi >> 32), oidx = (uint32_t)ohi;
+        if(ocnt == 0 || kmer < olo){ nlo = kmer; nhi = (1ull << 32) | (uint32_t)gidx; }
+        else if(kmer == olo){ nlo = olo; nhi = ((unsigned long long)(ocnt + 1) << 32) | min(oidx, (uint32_t)gidx); }
+        else return;                                        // larger kmer32: ignored (:55-59)
+        unsigned long long rlo, rhi;
+        cas128(slot, olo, ohi, nlo, nhi, rlo, rhi);
+        if(rlo == olo && rhi == ohi) return;
+        olo = rlo; ohi = rhi;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_dup(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, int paired,
+                                              unsigned long long* tab128, unsigned long long* first64){
+    const int kl = D.P.dup_keylen;
+    for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B1.n; r += gridDim.x * blockDim.x){
+        ReadView a = make_view(B1, r);
+        uint64_t key64, kmer; uint32_t gc; int tot;
+        if(!paired){
+            if(a.len < 32) continue;                                        // :65-67
+            if(!dup_code(a, 0, kl, key64)) continue;
+            if(!dup_code(a, max(0, a.len - 37), 32, kmer)) continue;        // :70,79
+            gc = gc_count(a) & 0xFF;                                        // uint8_t counter wraps, :83-89
+            tot = a.len;
+        }else{
+            ReadView b = make_view(B2, r);
+            if(a.len < 32 || b.len < 32) continue;                          // :96-98
+            if(!dup_code(a, 0, kl, key64)) continue;
+            if(!dup_code(b, 0, 32, kmer)) continue;                         // :108
+            gc = (gc_count(a) + gc_count(b)) & 0xFF;
+            tot = a.len + b.len;
+        }
+        const uint32_t gcbyte = (uint32_t)(uint8_t)round(255.0 * (double)gc / (double)tot);   // :91,127
+        dup_insert(tab128, first64, (uint32_t)key64, kmer, B1.first_index + r, gcbyte);
+    }
+}
+
+// after the run (and after the cross-rank merge): unpack into the reference's three arrays
+__global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, const unsigned long long* first64,
+                             uint64_t* dups, uint32_t* counts, uint8_t* gcs){
+    for(uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < bins; k += (uint64_t)gridDim.x * blockDim.x){
+        const unsigned long long lo = tab128[2 * k], hi = tab128[2 * k + 1], f = first64[k];
+        const uint32_t cnt = (uint32_t)(hi >> 32), idx = (uint32_t)hi;
+        dups[k] = cnt ? lo : 0;
+        counts[k] = cnt;
+        gcs[k] = (cnt && (uint32_t)(f >> 8) == idx) ? (uint8_t)(f & 0xFF) : 0;
+    }
+}

@@ -1,0 +1,116 @@
+"""One GPU context behind the C ABI (include/fqk.h): the object a host thread owns.
+
+``Engine`` is the Python face of ``fqk_ctx``: process packs of reads (host
+buffers, H2D/D2H inside the call), accumulate run-level statistics on the
+device, ``finalize()`` once per run (NCCL all-reduce across ranks).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class FqkError(RuntimeError):
+    pass
+
+
+class Engine:
+    def __init__(self, params, device=0, rank=0, nranks=1, nccl_unique_id=None):
+        self.lib = abi.load()
+        self.params = params
+        self.h = C.c_void_p()
+        uid = None
+        if nccl_unique_id is not None:
+            self._uid = (C.c_char * 128).from_buffer_copy(bytes(nccl_unique_id))
+            uid = C.cast(self._uid, C.c_void_p)
+        rc = self.lib.fqk_create(C.byref(self.h), C.byref(params), device, rank, nranks, uid)
+        if rc:
+            self.h = None
+            raise FqkError(f"fqk_create rc={rc}: {self.lib.fqk_last_error(None).decode()}")
+        self.layout = abi.FqStatsLayout()
+        self.lib.fqk_stats_layout(C.byref(params), C.byref(self.layout))
+
+    @staticmethod
+    def nccl_unique_id():
+        lib = abi.load()
+        buf = (C.c_char * 128)()
+        rc = lib.fqk_nccl_unique_id(C.cast(buf, C.c_void_p))
+        if rc:
+            raise FqkError(f"fqk_nccl_unique_id rc={rc}")
+        return bytes(buf)
+
+    def _check(self, rc, what):
+        if rc:
+            raise FqkError(f"{what} rc={rc}: {self.lib.fqk_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.fqk_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    # ---- host-buffer path (the drop-in call) ----
+    def process_se(self, batch, out=None):
+        if out is None:
+            out = np.zeros(batch.n, dtype=abi.READ_RESULT_DTYPE)
+        b = batch.c_struct()
+        self._check(self.lib.fqk_process_se(self.h, C.byref(b), abi.ptr(out)), "fqk_process_se")
+        return out
+
+    def process_pe(self, batch1, batch2, out=None):
+        n = batch1.n
+        if out is None:
+            out = (np.zeros(n, dtype=abi.READ_RESULT_DTYPE), np.zeros(n, dtype=abi.READ_RESULT_DTYPE),
+                   np.zeros(n, dtype=abi.PAIR_RESULT_DTYPE))
+        b1, b2 = batch1.c_struct(), batch2.c_struct()
+        self._check(self.lib.fqk_process_pe(self.h, C.byref(b1), C.byref(b2), abi.ptr(out[0]), abi.ptr(out[1]),
+                                            abi.ptr(out[2])), "fqk_process_pe")
+        return out
+
+    # ---- device-resident path (pointers are raw device addresses) ----
+    def process_se_device(self, dev_batch, out_ptr):
+        self._check(self.lib.fqk_process_se_device(self.h, C.byref(dev_batch), out_ptr), "fqk_process_se_device")
+
+    def process_pe_device(self, dev_batch1, dev_batch2, out1_ptr, out2_ptr, outp_ptr):
+        self._check(self.lib.fqk_process_pe_device(self.h, C.byref(dev_batch1), C.byref(dev_batch2), out1_ptr, out2_ptr,
+                                                   outp_ptr), "fqk_process_pe_device")
+
+    def sync(self):
+        self._check(self.lib.fqk_sync(self.h), "fqk_sync")
+
+    @property
+    def stream(self):
+        return self.lib.fqk_stream(self.h)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.fqk_launch_count(self.h))
+
+    def set_impl(self, impl):
+        self._check(self.lib.fqk_set_impl(self.h, impl), "fqk_set_impl")
+
+    def set_kernel_timing(self, on):
+        self._check(self.lib.fqk_set_kernel_timing(self.h, int(on)), "fqk_set_kernel_timing")
+
+    def kernel_times(self):
+        ms = (C.c_double * abi.T_SLOTS)()
+        n = (C.c_uint64 * abi.T_SLOTS)()
+        self._check(self.lib.fqk_kernel_times(self.h, ms, n), "fqk_kernel_times")
+        return list(ms), list(n)
+
+    def reset(self):
+        self._check(self.lib.fqk_reset(self.h), "fqk_reset")
+
+    def finalize(self):
+        flat = np.zeros(self.layout.total_u64, dtype=np.uint64)
+        self._check(self.lib.fqk_finalize(self.h, abi.ptr(flat)), "fqk_finalize")
+        return flat
+
+    def dup_table(self):
+        n = self.layout.dup_bins
+        dups = np.zeros(n, dtype=np.uint64); counts = np.zeros(n, dtype=np.uint32); gc = np.zeros(n, dtype=np.uint8)
+        self._check(self.lib.fqk_dup_table(self.h, abi.ptr(dups), abi.ptr(counts), abi.ptr(gc)), "fqk_dup_table")
+        return dups, counts, gc
