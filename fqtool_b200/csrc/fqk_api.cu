@@ -295,20 +295,18 @@ static DevBatch to_dev(const fq_batch* b){
 static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     if(B.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
-    bool done = false;
-    if(c->impl == 0 && fused_supported_se(c->D)){
+    { Timer t(c, FQK_T_TRIM);
+      k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
+    if(c->impl == 0 && swar_stats_supported_se(c->D)){
         Timer t(c, FQK_T_FUSED);
-        int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
-        if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");
-        c->launches += nl; done = true;
-    }
-    if(!done){
-        { Timer t(c, FQK_T_TRIM);
-          k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
-        { Timer t(c, FQK_T_STATS);
-          const int Cs = c->stats_cs_se;
-          k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
-          c->launches++; }
+        int nl = swar_stats_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
+        if(nl < 0) return fail(c, FQK_E_CUDA, "SWAR stats launch failed");
+        c->launches += nl;
+    }else{
+        Timer t(c, FQK_T_STATS);
+        const int Cs = c->stats_cs_se;
+        k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
+        c->launches++;
     }
     if(c->D.P.dup_enabled){
         Timer t(c, FQK_T_DUP);
