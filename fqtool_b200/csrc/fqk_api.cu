@@ -264,7 +264,7 @@ extern "C" const char* fqk_last_error(const fqk_ctx* c){
 }
 extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
 extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
-extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 1) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 2) return FQK_E_INVALID; c->impl = impl; return 0; }
 extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
 extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
     if(!c) return FQK_E_INVALID;
@@ -287,7 +287,7 @@ static int grid_for(fqk_ctx* c, uint32_t n, int per_block, int blocks_per_sm){
 }
 
 static DevBatch to_dev(const fq_batch* b){
-    DevBatch d; d.n = b->n_reads; d.first_index = b->first_index; d.offsets = b->offsets; d.lengths = b->lengths;
+    DevBatch d; d.n = b->n_reads; d.first_index = b->first_index; d.total = b->total_bases; d.offsets = b->offsets; d.lengths = b->lengths;
     d.bases2 = b->bases2; d.qual = b->qual;
     return d;
 }
@@ -295,18 +295,25 @@ static DevBatch to_dev(const fq_batch* b){
 static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     if(B.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
-    { Timer t(c, FQK_T_TRIM);
-      k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
-    if(c->impl == 0 && swar_stats_supported_se(c->D)){
+    if(c->impl == 0 && fused_supported_se(c->D, B)){
         Timer t(c, FQK_T_FUSED);
-        int nl = swar_stats_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
-        if(nl < 0) return fail(c, FQK_E_CUDA, "SWAR stats launch failed");
+        int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
+        if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");
         c->launches += nl;
     }else{
-        Timer t(c, FQK_T_STATS);
-        const int Cs = c->stats_cs_se;
-        k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
-        c->launches++;
+        { Timer t(c, FQK_T_TRIM);
+          k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
+        if(c->impl != 1 && swar_stats_supported_se(c->D)){
+            Timer t(c, FQK_T_STATS);
+            int nl = swar_stats_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
+            if(nl < 0) return fail(c, FQK_E_CUDA, "SWAR stats launch failed");
+            c->launches += nl;
+        }else{
+            Timer t(c, FQK_T_STATS);
+            const int Cs = c->stats_cs_se;
+            k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
+            c->launches++;
+        }
     }
     if(c->D.P.dup_enabled){
         Timer t(c, FQK_T_DUP);
@@ -371,14 +378,14 @@ extern "C" int fqk_process_pe_device(fqk_ctx* c, const fq_batch* r1, const fq_ba
 // host batch -> device staging (4 H2D copies on the context's stream)
 static int stage(fqk_ctx* c, StagedBatch& s, const fq_batch* b){
     const size_t n = b->n_reads;
-    if(b->total_bases % FQK_PAD) return fail(c, FQK_E_INVALID, "total_bases must be a multiple of FQK_PAD");
+    if(b->total_bases % FQK_BATCH_PAD) return fail(c, FQK_E_INVALID, "total_bases must be a multiple of FQK_BATCH_PAD");
     if(s.off.ensure(n * 4 + 16) || s.len.ensure(n * 2 + 16) || s.b2.ensure(b->total_bases / 4 + 16) || s.q.ensure(b->total_bases + 16))
         return fail(c, FQK_E_NOMEM, "device staging allocation failed");
     CU(cudaMemcpyAsync(s.off.p, b->offsets, n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s.len.p, b->lengths, n * 2, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s.b2.p, b->bases2, b->total_bases / 4, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s.q.p, b->qual, b->total_bases, cudaMemcpyHostToDevice, c->stream));
-    s.dev.n = b->n_reads; s.dev.first_index = b->first_index;
+    s.dev.n = b->n_reads; s.dev.first_index = b->first_index; s.dev.total = b->total_bases;
     s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
     s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
     return 0;
@@ -509,7 +516,7 @@ extern "C" int fqk_dup_table(fqk_ctx* c, uint64_t* dups, uint32_t* counts, uint8
 extern "C" uint64_t fqk_packed_bases(uint32_t n, const uint64_t* src_off){
     uint64_t t = 0;
     for(uint32_t r = 0; r < n; ++r){ uint64_t l = src_off[r + 1] - src_off[r]; t += (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD; }
-    return t;
+    return (t + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
 }
 
 extern "C" int fqk_pack_ascii(uint32_t n, const char* seq, const char* qual, const uint64_t* src_off,
@@ -537,6 +544,9 @@ extern "C" int fqk_pack_ascii(uint32_t n, const char* seq, const char* qual, con
         memset(qo + l, 0, padded - l);
         pos += padded;
     }
+    const uint64_t total = (pos + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;   // zero tail of the batch
+    memset(qual_out + pos, 0, total - pos);
+    memset(bases2 + pos / 4, 0, (total - pos) / 4);
     return 0;
 }
 

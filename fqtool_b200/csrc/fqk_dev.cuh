@@ -13,6 +13,7 @@
 struct DevBatch {
     uint32_t n;
     uint64_t first_index;
+    uint64_t total;        // padded extent in bases (multiple of FQK_BATCH_PAD)
     const uint32_t* offsets;
     const uint16_t* lengths;
     const uint8_t* bases2;

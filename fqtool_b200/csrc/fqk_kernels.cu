@@ -7,60 +7,6 @@
 #include "fqk_trim.cuh"
 #include "fqk_kernels.h"
 
-// ------------------------------------------------------------ block counters
-// per-block shared counters flushed with one atomic each at block end
-struct BlockCounters {
-    uint32_t filter[FQK_FILTER_RESULT_TYPES];
-    uint32_t polyx_reads[5], polyx_bases[5];
-    uint32_t adapter_reads, adapter_bases, merged_pairs;
-};
-
-__device__ inline void counters_zero(BlockCounters* bc){
-    uint32_t* p = reinterpret_cast<uint32_t*>(bc);
-    for(int i = threadIdx.x; i < (int)(sizeof(BlockCounters) / 4); i += blockDim.x) p[i] = 0;
-}
-__device__ inline void counters_add_tally(BlockCounters* bc, const Tally& t){
-#pragma unroll
-    for(int b = 0; b < 5; ++b){
-        if(t.polyx_reads[b]) atomicAdd(&bc->polyx_reads[b], t.polyx_reads[b]);
-        if(t.polyx_bases[b]) atomicAdd(&bc->polyx_bases[b], t.polyx_bases[b]);
-    }
-    if(t.adapter_reads) atomicAdd(&bc->adapter_reads, t.adapter_reads);
-    if(t.adapter_bases) atomicAdd(&bc->adapter_bases, t.adapter_bases);
-}
-__device__ inline void counters_flush(const BlockCounters* bc, const fq_stats_layout& L, uint64_t* flat){
-    for(int i = threadIdx.x; i < FQK_FILTER_RESULT_TYPES; i += blockDim.x)
-        if(bc->filter[i]) add_u64(flat + L.filter_off + i, bc->filter[i]);
-    if(threadIdx.x < 5){
-        if(bc->polyx_reads[threadIdx.x]) add_u64(flat + L.polyx_reads_off + threadIdx.x, bc->polyx_reads[threadIdx.x]);
-        if(bc->polyx_bases[threadIdx.x]) add_u64(flat + L.polyx_bases_off + threadIdx.x, bc->polyx_bases[threadIdx.x]);
-    }
-    if(threadIdx.x == 0){
-        if(bc->adapter_reads) add_u64(flat + L.adapter_reads_off, bc->adapter_reads);
-        if(bc->adapter_bases) add_u64(flat + L.adapter_bases_off, bc->adapter_bases);
-        if(bc->merged_pairs) add_u64(flat + L.merged_pairs_off, bc->merged_pairs);
-    }
-}
-
-// ------------------------------------------------------------------ SE trim
-// loop body of SingleEndProcessor::processSingleEnd, src/seprocessor.cpp:313-340
-__device__ inline void se_read(const DevParams& D, ReadView& v, fq_read_result& rec, Tally& tl){
-    const fq_params& P = D.P;
-    const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
-    if(alive){
-        if(P.polyg_enabled)
-            dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
-        if(P.adapter_trim_enabled && P.adapter_r1_len > 0)
-            dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
-        if(P.polyx_enabled)
-            dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
-        if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
-    }
-    rec.result = (uint8_t)dev_pass_filter_view(P, v, !alive);
-    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
-    else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
-}
-
 __global__ void __launch_bounds__(256) k_trim_se(const __grid_constant__ DevParams D, DevBatch B,
                                                   fq_read_result* __restrict__ out, uint64_t* __restrict__ flat){
     __shared__ BlockCounters bc;

@@ -133,7 +133,10 @@ __global__ void k_synth_pe(uint64_t seed, uint64_t first, uint32_t n, int L, flo
     }
 }
 
-extern "C" uint64_t fqk_synth_total_bases(uint32_t n, int L){ return (uint64_t)n * (uint64_t)((L + 15) / 16 * 16); }
+extern "C" uint64_t fqk_synth_total_bases(uint32_t n, int L){
+    const uint64_t t = (uint64_t)n * (uint64_t)((L + 15) / 16 * 16);
+    return (t + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
+}
 
 extern "C" int fqk_synth_generate(void* stream, int model, uint64_t seed, uint64_t first_index, uint32_t n, int L,
                                   double frag_mean, double frag_sd,

@@ -49,8 +49,9 @@ class DeviceBatch:
         self.total = int(lib.fqk_synth_total_bases(n, L))
         self.offsets = torch.empty(max(n, 1), dtype=torch.int32, device=device)
         self.lengths = torch.empty(max(n, 1), dtype=torch.int16, device=device)
-        self.bases2 = torch.empty(max(self.total // 4, 1), dtype=torch.uint8, device=device)
-        self.qual = torch.empty(max(self.total, 1), dtype=torch.uint8, device=device)
+        # zero-filled: the generator leaves the (<64 bases) tail padding of the batch untouched
+        self.bases2 = torch.zeros(max(self.total // 4, 1), dtype=torch.uint8, device=device)
+        self.qual = torch.zeros(max(self.total, 1), dtype=torch.uint8, device=device)
 
     def c_struct(self):
         b = abi.FqBatch()
@@ -63,7 +64,7 @@ class DeviceBatch:
         """Copy the first n reads back as a host Batch (numpy views of torch CPU tensors)."""
         n = self.n if n is None else min(n, self.n)
         Lp = (self.L + 15) // 16 * 16
-        tot = n * Lp
+        tot = (n * Lp + 63) // 64 * 64
         def cp(t, k):
             h = torch.empty(k, dtype=t.dtype, pin_memory=pinned)
             h.copy_(t[:k])

@@ -51,6 +51,7 @@ extern "C" {
 #define FQK_MAX_ADAPTER   128      /* bases of an explicit adapter            */
 #define FQK_MAX_READ_LEN  4096     /* bases per read accepted by the kernels  */
 #define FQK_PAD           16       /* every read starts at a multiple of this */
+#define FQK_BATCH_PAD     64       /* total_bases of a batch is a multiple of this */
 
 /*
  * fq_params: flat POD mirror of the hot-path fields of the reference's
@@ -108,7 +109,10 @@ typedef struct fq_params {
  * N flag in bit 7.  Read r occupies base positions
  * [offsets[r], offsets[r]+lengths[r]) of both buffers and offsets[r] is a
  * multiple of FQK_PAD, so every read starts on a 16-byte quality boundary and
- * a 4-byte base boundary.  Padding content is ignored (the packer writes 0).
+ * a 4-byte base boundary.  Batches are dense and ordered: offsets[r+1] ==
+ * offsets[r] + lengths[r] rounded up to FQK_PAD; total_bases is the end of the
+ * last read rounded up to FQK_BATCH_PAD.  All padding bytes MUST be zero (the
+ * packer writes them so) and bases2/qual must be 16-byte aligned.
  * Buffers are caller-owned and must stay valid until the call returns.
  */
 typedef struct fq_batch {
@@ -252,7 +256,7 @@ uint64_t fqk_launch_count(const fqk_ctx* ctx);    /* kernels launched so far    
 int  fqk_set_kernel_timing(fqk_ctx* ctx, int enabled);
 int  fqk_kernel_times(fqk_ctx* ctx, double ms[FQK_T_SLOTS], uint64_t launches[FQK_T_SLOTS]);
 /* implementation selector for A/B tests: 0 = automatic (fused kernel when the
- * configuration allows), 1 = generic kernels only */
+ * configuration allows), 1 = generic kernels only, 2 = split trim + SWAR stats */
 int  fqk_set_impl(fqk_ctx* ctx, int impl);
 
 /* zero every accumulator (Stats, FilterResult counters, insert histogram, dup table) */
