@@ -264,7 +264,7 @@ extern "C" const char* fqk_last_error(const fqk_ctx* c){
 }
 extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
 extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
-extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 2) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 1) return FQK_E_INVALID; c->impl = impl; return 0; }
 extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
 extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
     if(!c) return FQK_E_INVALID;
@@ -303,12 +303,7 @@ static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     }else{
         { Timer t(c, FQK_T_TRIM);
           k_trim_se<<<grid_for(c, B.n, 256, 8), 256, 0, c->stream>>>(c->D, B, out, c->flat); c->launches++; }
-        if(c->impl != 1 && swar_stats_supported_se(c->D)){
-            Timer t(c, FQK_T_STATS);
-            int nl = swar_stats_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
-            if(nl < 0) return fail(c, FQK_E_CUDA, "SWAR stats launch failed");
-            c->launches += nl;
-        }else{
+        {
             Timer t(c, FQK_T_STATS);
             const int Cs = c->stats_cs_se;
             k_stats_se<<<grid_for(c, B.n, 8, Cs ? 1 : 4), 256, (size_t)2 * 20 * Cs * 4, c->stream>>>(c->D, B, out, c->flat, Cs);
