@@ -39,6 +39,10 @@ constexpr int S_ALL = 0, S_B0 = 1, S_B1 = 2, S_B01 = 3, S_N = 4;   // sets
 constexpr int NSETS = 5;
 constexpr int THREADS = 384;
 
+__device__ __forceinline__ uint32_t lds32(uint32_t a){ uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds8(uint32_t a){ uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint2 lds64(uint32_t a){ uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
+
 // level 1: 8-bit count lanes, 16-bit sum lanes (n[S_ALL] is unused: totals come from lengths)
 struct Acc1 {
     uint32_t n[NSETS], n20[NSETS], n30[NSETS], qe[NSETS], qo[NSETS];
@@ -47,26 +51,24 @@ struct Acc1 {
         for(int s = 0; s < NSETS; ++s){ n[s] = n20[s] = n30[s] = qe[s] = qo[s] = 0; }
     }
 };
-// level 2: per level-1 count register two registers of 2x16-bit lanes (bytes 0,2 / bytes 1,3),
-// per level-1 sum register two 32-bit sums
-struct Acc2 {
-    uint32_t n[NSETS][2], n20[NSETS][2], n30[NSETS][2], qe[NSETS][2], qo[NSETS][2];
-    __device__ __forceinline__ void zero(){
-#pragma unroll
-        for(int s = 0; s < NSETS; ++s)
-#pragma unroll
-            for(int h = 0; h < 2; ++h) n[s][h] = n20[s][h] = n30[s][h] = qe[s][h] = qo[s][h] = 0;
-    }
-};
-
-__device__ __forceinline__ void fold(Acc1& a, Acc2& b){
+// level 2 lives in per-thread private shared-memory slots (plain load/add/store, no atomics, conflict-free
+// layout [slot][thread]): per level-1 count register two words of 2x16-bit lanes (bytes 0,2 / bytes 1,3),
+// per level-1 sum register two 32-bit sums.  Slot index = (set*5 + kind5)*2 + half.
+constexpr int L2_SLOTS = NSETS * 5 * 2;
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v){ asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void l2_add(uint32_t l2, int slot, uint32_t v){
+    const uint32_t a = l2 + (uint32_t)slot * (THREADS * 4);
+    sts32(a, lds32(a) + v);
+}
+// l2 = shared address of this thread's slot 0
+__device__ __forceinline__ void fold(Acc1& a, uint32_t l2){
 #pragma unroll
     for(int s = 0; s < NSETS; ++s){
-        if(s){ b.n[s][0] += a.n[s] & 0x00FF00FFu; b.n[s][1] += (a.n[s] >> 8) & 0x00FF00FFu; }
-        b.n20[s][0] += a.n20[s] & 0x00FF00FFu; b.n20[s][1] += (a.n20[s] >> 8) & 0x00FF00FFu;
-        b.n30[s][0] += a.n30[s] & 0x00FF00FFu; b.n30[s][1] += (a.n30[s] >> 8) & 0x00FF00FFu;
-        b.qe[s][0] += a.qe[s] & 0xFFFFu; b.qe[s][1] += a.qe[s] >> 16;
-        b.qo[s][0] += a.qo[s] & 0xFFFFu; b.qo[s][1] += a.qo[s] >> 16;
+        if(s){ l2_add(l2, (s * 5 + 0) * 2, a.n[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 0) * 2 + 1, (a.n[s] >> 8) & 0x00FF00FFu); }
+        l2_add(l2, (s * 5 + 1) * 2, a.n20[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 1) * 2 + 1, (a.n20[s] >> 8) & 0x00FF00FFu);
+        l2_add(l2, (s * 5 + 2) * 2, a.n30[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 2) * 2 + 1, (a.n30[s] >> 8) & 0x00FF00FFu);
+        l2_add(l2, (s * 5 + 3) * 2, a.qe[s] & 0xFFFFu); l2_add(l2, (s * 5 + 3) * 2 + 1, a.qe[s] >> 16);
+        l2_add(l2, (s * 5 + 4) * 2, a.qo[s] & 0xFFFFu); l2_add(l2, (s * 5 + 4) * 2 + 1, a.qo[s] >> 16);
     }
     a.zero();
 }
@@ -151,18 +153,11 @@ __device__ __noinline__ void drain2(uint32_t* vals /*[NSETS*10]*/, uint32_t* smA
         }
     }
 }
-__device__ __forceinline__ void drain_l2(Acc2& b, uint32_t* smA, uint32_t* smB, int C, int w){
+__device__ __forceinline__ void drain_l2(uint32_t l2, uint32_t* smA, uint32_t* smB, int C, int w){
     uint32_t vals[NSETS * 10];
 #pragma unroll
-    for(int s = 0; s < NSETS; ++s){
-        vals[s * 10 + 0] = b.n[s][0]; vals[s * 10 + 1] = b.n[s][1];
-        vals[s * 10 + 2] = b.n20[s][0]; vals[s * 10 + 3] = b.n20[s][1];
-        vals[s * 10 + 4] = b.n30[s][0]; vals[s * 10 + 5] = b.n30[s][1];
-        vals[s * 10 + 6] = b.qe[s][0]; vals[s * 10 + 7] = b.qe[s][1];
-        vals[s * 10 + 8] = b.qo[s][0]; vals[s * 10 + 9] = b.qo[s][1];
-    }
+    for(int i = 0; i < NSETS * 10; ++i) vals[i] = lds32(l2 + (uint32_t)i * (THREADS * 4));
     drain2(vals, smA, smB, C, w);
-    b.zero();
 }
 
 // block retirement: sets -> bins, raw quality chars -> Phred (minus 33 per base), add to the global u64 arrays
@@ -257,7 +252,12 @@ __device__ __forceinline__ void swar_counts(const uint4* q128, int start, int le
     total -= 33 * len;
 }
 
-struct Desc { uint32_t off; uint16_t len; uint16_t start; uint16_t plen; uint16_t kind; };   // kind: 0 common, 1 raw only, 2 raw + shifted post
+// per-read descriptor of a tile, 8 bytes: x = (offset in tile)/16 | len << 17, y = start | plen << 13 | kind << 26
+// kind: 0 common (passing, untrimmed), 1 raw only, 2 raw + shifted kept part for post1
+struct Desc { uint32_t x, y; };
+__device__ __forceinline__ Desc make_desc(uint32_t off, uint32_t len, uint32_t start, uint32_t plen, uint32_t kind){
+    Desc d; d.x = (off >> 4) | (len << 17); d.y = start | (plen << 13) | (kind << 26); return d;
+}
 
 __global__ void __launch_bounds__(THREADS, 1)
 k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
@@ -270,9 +270,11 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
     uint32_t* smPost = smPre + statw;
     BlockCounters* bc = reinterpret_cast<BlockCounters*>(smPost + statw);
     uint64_t* mbar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bc + 1) + 7) & ~uintptr_t(7));
-    Desc* desc = reinterpret_cast<Desc*>(mbar + 2);
-    uint8_t* sp = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(desc + T) + 15) & ~uintptr_t(15));
-    const uint32_t qcap = (uint32_t)T * Cp, bcap = qcap / 4 + 16;
+    uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 2);         // 8 bytes of zeros
+    Desc* desc = reinterpret_cast<Desc*>(mbar + 3);
+    uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(desc + T) + 15) & ~uintptr_t(15));
+    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * THREADS);
+    const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
     const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
     const uint32_t stage_bytes = qcap + bcap + mo + ml;
     // stage s: quality bytes at sp + s*stage_bytes, then base bytes, offsets, lengths
@@ -280,6 +282,10 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
     auto stb = [&](int s){ return sp + (size_t)s * stage_bytes + qcap; };
     auto sto = [&](int s){ return reinterpret_cast<uint32_t*>(sp + (size_t)s * stage_bytes + qcap + bcap); };
     auto stl = [&](int s){ return reinterpret_cast<uint16_t*>(sp + (size_t)s * stage_bytes + qcap + bcap + mo); };
+    const uint32_t sp32 = smem_u32(sp), sd32 = smem_u32(desc), zero_addr = smem_u32(zero_word);
+    if(threadIdx.x == 0){ zero_word[0] = 0; zero_word[1] = 0; }
+    const uint32_t l2 = smem_u32(l2base) + 4 * threadIdx.x;          // this thread's private level-2 slots
+    for(int i = threadIdx.x; i < L2_SLOTS * THREADS; i += THREADS) l2base[i] = 0;
 
     for(int i = threadIdx.x; i < 2 * statw; i += THREADS) smPre[i] = 0;
     counters_zero(bc);
@@ -317,8 +323,7 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
     if(threadIdx.x == 0 && ntiles > 0) issue(0, (int)min((uint32_t)T, hi - lo));
 
     Acc1 common, preo, posto;
-    Acc2 common2;
-    common.zero(); preo.zero(); posto.zero(); common2.zero();
+    common.zero(); preo.zero(); posto.zero();
     int leftC = 255, leftO = 255;
     Tally tl = {};
     const bool fast_filter = !P.complexity_enabled;
@@ -338,12 +343,12 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
         const uint32_t bshift = (a0 >> 2) & 15u;
         // ---------------- phase 1: one thread per read ----------------
         for(int i = threadIdx.x; i < nt; i += THREADS){
-            Desc d; d.off = So[i] - a0; d.len = Sl[i];
-            const uint32_t padded = (d.len + 15u) & ~15u;
-            bool ok = !(So[i] & 15u) && So[i] >= a0 && d.off + padded <= qcap && d.len <= C;
+            uint32_t doff = So[i] - a0, dlen = Sl[i];
+            const uint32_t padded = (dlen + 15u) & ~15u;
+            bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
             if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
-            if(!ok){ atomicOr(D.err, d.len > C ? 1u : 2u); d.off = 0; d.len = 0; }
-            ReadView v; v.q = Sq + d.off; v.b2 = Sb + bshift + (d.off >> 2); v.start = 0; v.len = d.len;
+            if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
+            ReadView v; v.q = Sq + doff; v.b2 = Sb + bshift + (doff >> 2); v.start = 0; v.len = (int)dlen;
             fq_read_result rec = {};
             if(fast_filter){
                 const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
@@ -358,7 +363,7 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
                 else{
                     if(P.qual_filter_enabled){
                         int lowq, nn, total;
-                        swar_counts(reinterpret_cast<const uint4*>(Sq + d.off), v.start, v.len, P.low_quality_limit,
+                        swar_counts(reinterpret_cast<const uint4*>(Sq + doff), v.start, v.len, P.low_quality_limit,
                                     P.average_quality_limit > 0, lowq, nn, total);
                         if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
                         else if(P.average_quality_limit > 0 && P.average_quality_limit > (double)total / v.len) result = FQK_FAIL_QUALITY;
@@ -376,40 +381,49 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
             out[t0 + i] = rec;
             atomicAdd(&bc->filter[rec.result], 1u);
             const bool pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
-            d.start = rec.start; d.plen = rec.len;
-            d.kind = pass ? ((rec.start == 0 && rec.len == d.len) ? 0 : 2) : 1;
-            desc[i] = d;
-            atomicAdd(smPre + 4 * NSETS * C + d.len, 1u);
-            if(pass) atomicAdd(smPost + 4 * NSETS * C + d.plen, 1u);
+            const uint32_t kind = pass ? ((rec.start == 0 && rec.len == dlen) ? 0u : 2u) : 1u;
+            desc[i] = make_desc(doff, dlen, rec.start, rec.len, kind);
+            atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
+            if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
         }
         if((int)threadIdx.x < nt1){ sto(s ^ 1)[threadIdx.x] = moff; stl(s ^ 1)[threadIdx.x] = (uint16_t)mlen; }
         __syncthreads();
         if(threadIdx.x == 0 && nt1 > 0) issue(s ^ 1, nt1);
         // ---------------- phase 2: SWAR statistics ----------------
         if(active){
-            const uint8_t* sb = Sb + bshift;
+            const uint32_t sq0 = sp32 + (uint32_t)s * stage_bytes, sb0 = sq0 + qcap + bshift;
+            const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;           // this thread's word of a read at tile offset 0
+            const uint32_t sd = sd32;
+            // software pipeline: descriptor and data of the next read are loaded before the current one is reduced
+            uint2 dv = make_uint2(0u, 0u); uint32_t qraw = 0, b = 0;
+            auto fetch = [&](int i, uint2& d, uint32_t& q, uint32_t& bb){
+                d = lds64(sd + 8 * i);
+                const uint32_t off = (d.x & 0x1FFFFu) << 4, len = d.x >> 17;
+                const bool in = (uint32_t)(4 * w) < len;
+                q = lds32(in ? sqw + off : zero_addr);                 // words outside the read read a zero word
+                bb = in ? lds8(sbw + (off >> 2)) : 0u;
+            };
+            if(g < nt) fetch(g, dv, qraw, b);
             for(int i = g; i < nt; i += G){
-                const Desc d = desc[i];
-                const int nw = (d.len + 3) >> 2;
-                uint32_t qraw = 0, b = 0;
-                if(w < nw){
-                    qraw = *reinterpret_cast<const uint32_t*>(Sq + d.off + 4 * w);
-                    b = sb[(d.off >> 2) + w];
-                }
-                if(d.kind == 0){
-                    if(w < nw) acc_word(common, qraw, b);
-                    if(--leftC == 0){ fold(common, common2); leftC = 255; }
+                const uint2 dc = dv; const uint32_t qc = qraw, bcur = b;
+                if(i + G < nt) fetch(i + G, dv, qraw, b);
+                const uint32_t kind = dc.y >> 26;
+                if(kind == 0){
+                    acc_word(common, qc, bcur);
+                    if(--leftC == 0){ fold(common, l2); leftC = 255; }
                 }else{
-                    if(w < nw) acc_word(preo, qraw, b);
-                    if(d.kind == 2){
-                        const int nv = (int)d.plen - 4 * w;
+                    acc_word(preo, qc, bcur);
+                    if(kind == 2){
+                        const uint32_t off = (dc.x & 0x1FFFFu) << 4;
+                        const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
+                        const int nv = (int)plen - 4 * w;
                         if(nv > 0){
-                            const uint32_t p = d.off + d.start + 4 * w;
+                            const uint32_t p = off + start + 4 * w;
                             const uint32_t a1 = p & ~3u, sh = p & 3u;
-                            const uint32_t w0 = *reinterpret_cast<const uint32_t*>(Sq + a1);
-                            const uint32_t w1 = sh ? *reinterpret_cast<const uint32_t*>(Sq + a1 + 4) : 0u;
+                            const uint32_t w0 = lds32(sq0 + a1);
+                            const uint32_t w1 = sh ? lds32(sq0 + a1 + 4) : 0u;
                             uint32_t q2 = __funnelshift_r(w0, w1, sh * 8);
-                            const uint32_t c0 = sb[p >> 2], c1 = sh ? sb[(p >> 2) + 1] : 0u;
+                            const uint32_t c0 = lds8(sb0 + (p >> 2)), c1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
                             uint32_t b2 = ((c0 | (c1 << 8)) >> (2 * sh)) & 0xFF;
                             if(nv < 4){ q2 &= (1u << (8 * nv)) - 1u; b2 &= (1u << (2 * nv)) - 1u; }
                             acc_word(posto, q2, b2);
@@ -422,8 +436,8 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
         __syncthreads();
     }
     if(active){
-        fold(common, common2);
-        drain_l2(common2, smPre, smPost, C, w);
+        fold(common, l2);
+        drain_l2(l2, smPre, smPost, C, w);
         drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w);
     }
     counters_add_tally(bc, tl);
@@ -437,8 +451,9 @@ size_t g_smem_optin = 0;
 
 size_t fused_smem_bytes(int W, int T){
     const int C = 4 * W, Cp = (C + 15) & ~15;
-    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 16 + (size_t)T * sizeof(Desc) + 16;
-    s += 2 * ((size_t)T * Cp + (size_t)T * Cp / 4 + 16 + ((T * 4 + 15) & ~15) + ((T * 2 + 15) & ~15));
+    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 24 + (size_t)T * sizeof(Desc) + 16;
+    s += (size_t)L2_SLOTS * THREADS * 4;
+    s += 2 * ((size_t)T * Cp + (((size_t)T * Cp / 4 + 15) & ~(size_t)15) + 16 + ((T * 4 + 15) & ~15) + ((T * 2 + 15) & ~15));
     return s + 128;
 }
 // largest tile (multiple of the group count, at most THREADS reads) that fits one block per SM
