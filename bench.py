@@ -223,7 +223,7 @@ def main():
 
     for _ in range(a.warmup):
         step()
-    eng.sync()
+    eng.finalize()                               # warm-up of the run-level merge too (NCCL connects lazily)
     eng.reset()
     eng.set_kernel_timing(True)
     eng.kernel_times()
