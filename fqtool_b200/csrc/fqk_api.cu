@@ -153,6 +153,7 @@ static int validate_params(const fq_params* p, std::string& why){
        (p->cut_right_enabled && p->cut_right_window < 1)){ why = "cut window must be >= 1"; return FQK_E_INVALID; }
     if(p->polyg_enabled && (p->polyg_one_mismatch_each < 1 || (p->is_paired && p->polyg_min_len < 1))){ why = "polyG one_mismatch_each must be >= 1"; return FQK_E_INVALID; }
     if(p->polyx_enabled && p->polyx_one_mismatch_each < 1){ why = "polyX one_mismatch_each must be >= 1"; return FQK_E_INVALID; }
+    if(p->qual_filter_enabled && (p->low_quality_limit < 33 || p->low_quality_limit > 126)){ why = "low_quality_limit must be Phred+33 in 33..126"; return FQK_E_INVALID; }
     if(p->kmer_len != 0 && (p->kmer_len < 4 || p->kmer_len > 15)){ why = "kmer_len must be 0 or 4..15"; return FQK_E_INVALID; }
     if(p->dup_enabled && (p->dup_keylen < 12 || p->dup_keylen > 14)){ why = "dup_keylen must be 12..14 on the device"; return FQK_E_INVALID; }
     if(p->adapter_r1_len < 0 || p->adapter_r1_len > FQK_MAX_ADAPTER || p->adapter_r2_len < 0 || p->adapter_r2_len > FQK_MAX_ADAPTER){ why = "adapter too long"; return FQK_E_INVALID; }
@@ -264,7 +265,7 @@ extern "C" const char* fqk_last_error(const fqk_ctx* c){
 }
 extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
 extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
-extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 1) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 2) return FQK_E_INVALID; c->impl = impl; return 0; }
 extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
 extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
     if(!c) return FQK_E_INVALID;
@@ -295,9 +296,9 @@ static DevBatch to_dev(const fq_batch* b){
 static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     if(B.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
-    if(c->impl == 0 && fused_supported_se(c->D, B)){
+    if(c->impl != 1 && fused_supported_se(c->D, B)){
         Timer t(c, FQK_T_FUSED);
-        int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream);
+        int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream, c->impl);
         if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");
         c->launches += nl;
     }else{

@@ -223,32 +223,45 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity){
     }
 }
 
-// Filter::passFilter (src/filter.cpp:15-25) counts over the kept part [start, start+len) of a staged
-// read, 16 quality bytes per load: low-quality bases by a per-byte carry test, N bases by bit 7.
-__device__ __forceinline__ void swar_counts(const uint4* q128, int start, int len, int lim, bool want_total,
+// Filter::passFilter (src/filter.cpp:15-25) counts over the kept part [start, start+len) of a read staged
+// in shared memory at address qa (16-byte aligned), 16 quality bytes per load.  Low-quality bases: byte + k
+// carries into bit 7 iff byte >= limit; the four carry words of a chunk are merged into one word before the
+// popcount.  N bases: bit 7 of the stored byte (chunks without N skip the masking).
+__device__ __forceinline__ uint4 lds128(uint32_t a){
+    uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v;
+}
+__device__ __forceinline__ uint32_t byte_range_mask(int p, int start, int end){      // bytes of word at position p inside [start, end)
+    const int nlo = min(4, max(0, start - p)), nhi = min(4, max(0, p + 4 - end));
+    return (nlo + nhi >= 4) ? 0u : ((0xFFFFFFFFu << (8 * nlo)) & (0xFFFFFFFFu >> (8 * nhi)));
+}
+__device__ __forceinline__ void swar_counts(uint32_t qa, int start, int len, int lim, bool want_total,
                                             int& lowq, int& nn, int& total){
     lowq = nn = total = 0;
     if(len <= 0) return;
     const int end = start + len;
-    const uint32_t k = (uint32_t)(0x80 - lim) * 0x01010101u;          // byte + k carries into bit 7 iff byte >= lim
+    const uint32_t k = (uint32_t)(0x80 - lim) * 0x01010101u;
+    int ge_bytes = 0;                                                  // bytes with q >= limit
     for(int c = start >> 4; c <= (end - 1) >> 4; ++c){
-        const uint4 v = q128[c];
-        const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for(int j = 0; j < 4; ++j){
-            const int p = 16 * c + 4 * j;
-            uint32_t mask = 0xFFFFFFFFu;
-            if(p < start || p + 4 > end){
-                const int nlo = min(4, max(0, start - p)), nhi = min(4, max(0, p + 4 - end));
-                mask = (nlo + nhi >= 4) ? 0u : ((0xFFFFFFFFu << (8 * nlo)) & (0xFFFFFFFFu >> (8 * nhi)));
-            }
-            const uint32_t q7 = ws[j] & 0x7F7F7F7Fu;
-            const uint32_t ge = (q7 + k) & 0x80808080u;
-            lowq += __popc(~ge & 0x80808080u & mask);
-            nn += __popc(ws[j] & 0x80808080u & mask);
-            if(want_total) total = (int)__dp4a(q7 & mask, 0x01010101u, (uint32_t)total);
+        uint4 v = lds128(qa + 16 * c);
+        const int p = 16 * c;
+        if(p < start || p + 16 > end){                                 // edge chunk: zero the bytes outside the read part
+            v.x &= byte_range_mask(p, start, end); v.y &= byte_range_mask(p + 4, start, end);
+            v.z &= byte_range_mask(p + 8, start, end); v.w &= byte_range_mask(p + 12, start, end);
+        }
+        const uint32_t nf = (v.x | v.y | v.z | v.w) & 0x80808080u;
+        if(nf){
+            nn += __popc(v.x & 0x80808080u) + __popc(v.y & 0x80808080u) + __popc(v.z & 0x80808080u) + __popc(v.w & 0x80808080u);
+            v.x &= 0x7F7F7F7Fu; v.y &= 0x7F7F7F7Fu; v.z &= 0x7F7F7F7Fu; v.w &= 0x7F7F7F7Fu;
+        }
+        const uint32_t g = ((v.x + k) & 0x80808080u) | (((v.y + k) & 0x80808080u) >> 1) |
+                           (((v.z + k) & 0x80808080u) >> 2) | (((v.w + k) & 0x80808080u) >> 3);
+        ge_bytes += __popc(g);
+        if(want_total){
+            total = (int)__dp4a(v.x, 0x01010101u, (uint32_t)total); total = (int)__dp4a(v.y, 0x01010101u, (uint32_t)total);
+            total = (int)__dp4a(v.z, 0x01010101u, (uint32_t)total); total = (int)__dp4a(v.w, 0x01010101u, (uint32_t)total);
         }
     }
+    lowq = len - ge_bytes;                                             // zeroed bytes never reach the limit (limit >= 33)
     total -= 33 * len;
 }
 
@@ -363,7 +376,7 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
                 else{
                     if(P.qual_filter_enabled){
                         int lowq, nn, total;
-                        swar_counts(reinterpret_cast<const uint4*>(Sq + doff), v.start, v.len, P.low_quality_limit,
+                        swar_counts(smem_u32(Sq + doff), v.start, v.len, P.low_quality_limit,
                                     P.average_quality_limit > 0, lowq, nn, total);
                         if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
                         else if(P.average_quality_limit > 0 && P.average_quality_limit > (double)total / v.len) result = FQK_FAIL_QUALITY;
@@ -447,6 +460,257 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
     counters_flush(bc, D.L, flat);
 }
 
+
+// ===========================================================================
+// Warp-specialised variant (the default): 12 statistics warps + 4 trim warps per block.
+//   trim warps (threads 384..511): bulk-copy producer, phase 1 of tile k+1 (records, per-tile lists of
+//       "common" and "other" reads) while the statistics warps reduce tile k;
+//   statistics warps (threads 0..383): phase 2 over the lists, no block-wide barrier in steady state.
+// Three staging buffers; mbarriers: full[s] (bulk copies landed), ready[s] (lists written), free[s]
+// (statistics done with the stage).  Register budget split with setmaxnreg (144 / 80).
+// ===========================================================================
+constexpr int WS_STATS = 384, WS_TRIM = 128, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
+static_assert(WS_STATS == THREADS, "level-2 slot layout is shared with the single-role kernel");
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar){
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_trim(){ asm volatile("bar.sync 1, %0;" :: "n"(WS_TRIM) : "memory"); }
+
+// phase 1 of one read staged in shared memory: the per-read sequence of processSingleEnd
+// (src/seprocessor.cpp:313-340); returns the record
+__device__ __forceinline__ fq_read_result phase1_read(const DevParams& D, const uint8_t* q, const uint8_t* b2, int len,
+                                                      bool fast_filter, Tally& tl){
+    const fq_params& P = D.P;
+    ReadView v; v.q = q; v.b2 = b2; v.start = 0; v.len = len;
+    fq_read_result rec = {};
+    if(!fast_filter){ se_read(D, v, rec, tl); return rec; }
+    const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
+    if(alive){
+        if(P.polyg_enabled) dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
+        if(P.adapter_trim_enabled && P.adapter_r1_len > 0) dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
+        if(P.polyx_enabled) dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
+        if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
+    }
+    int result = FQK_PASS_FILTER;
+    if(!alive || v.len == 0) result = FQK_FAIL_LENGTH;
+    else{
+        if(P.qual_filter_enabled){
+            int lowq, nn, total;
+            swar_counts(smem_u32(q), v.start, v.len, P.low_quality_limit,
+                        P.average_quality_limit > 0, lowq, nn, total);
+            if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
+            else if(P.average_quality_limit > 0 && P.average_quality_limit > (double)total / v.len) result = FQK_FAIL_QUALITY;
+            else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
+        }
+        if(result == FQK_PASS_FILTER && P.length_filter_enabled){
+            if(v.len < P.min_read_length) result = FQK_FAIL_LENGTH;
+            else if(P.max_read_length > 0 && v.len > P.max_read_length) result = FQK_FAIL_TOO_LONG;
+        }
+    }
+    rec.result = (uint8_t)result;
+    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
+    else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
+    return rec;
+}
+
+__global__ void __launch_bounds__(WS_THREADS, 1)
+k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
+              uint64_t* __restrict__ flat, int W, int T, int reads_per_block){
+    extern __shared__ __align__(128) uint8_t smraw[];
+    const fq_params& P = D.P;
+    const int C = 4 * W, Cp = (C + 15) & ~15;
+    const int statw = 4 * NSETS * C + C + 1;
+    uint32_t* smPre = reinterpret_cast<uint32_t*>(smraw);
+    uint32_t* smPost = smPre + statw;
+    BlockCounters* bc = reinterpret_cast<BlockCounters*>(smPost + statw);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bc + 1) + 7) & ~uintptr_t(7));
+    uint64_t* full = mbar; uint64_t* ready = mbar + NS; uint64_t* freeb = mbar + 2 * NS;
+    uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
+    uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 2) + 15) & ~uintptr_t(15));
+    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * WS_STATS);
+    // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
+    const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
+    const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
+    const uint32_t o_b = qcap, o_off = o_b + bcap, o_len = o_off + mo, o_cl = o_len + ml, o_ol = o_cl + mo, o_cnt = o_ol + 2 * mo;
+    const uint32_t stage_bytes = o_cnt + 16;
+    const uint32_t sp32 = smem_u32(sp), zero_addr = smem_u32(zero_word);
+
+    for(int i = threadIdx.x; i < 2 * statw; i += WS_THREADS) smPre[i] = 0;
+    for(int i = threadIdx.x; i < L2_SLOTS * WS_STATS; i += WS_THREADS) l2base[i] = 0;
+    counters_zero(bc);
+    if(threadIdx.x == 0){
+        for(int s = 0; s < NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], WS_TRIM); mbar_init(&freeb[s], WS_STATS); }
+        zero_word[0] = 0; zero_word[1] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t lo = (uint32_t)min((uint64_t)B.n, (uint64_t)blockIdx.x * reads_per_block);
+    const uint32_t hi = (uint32_t)min((uint64_t)B.n, (uint64_t)lo + reads_per_block);
+    const int ntiles = (int)((hi - lo + T - 1) / T);
+
+    if(threadIdx.x >= WS_STATS){
+        // ============================== trim warps ==============================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;\n");
+        const int tt = threadIdx.x - WS_STATS;
+        Tally tl = {};
+        const bool fast_filter = !P.complexity_enabled;
+        // stage metadata, reset the list counters, then one thread issues the two bulk copies of tile k
+        auto prefetch = [&](int k){
+            const int s = k % NS;
+            uint8_t* S = sp + (size_t)s * stage_bytes;
+            uint32_t* so = reinterpret_cast<uint32_t*>(S + o_off); uint16_t* sl = reinterpret_cast<uint16_t*>(S + o_len);
+            const uint32_t t0 = lo + (uint32_t)k * T;
+            const int nt = (int)min((uint32_t)T, hi - t0);
+            for(int i = tt; i < nt; i += WS_TRIM){ so[i] = B.offsets[t0 + i]; sl[i] = B.lengths[t0 + i]; }
+            if(tt == 0){ uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; }
+            bar_trim();
+            if(tt == 0){
+                const uint32_t a = so[0];
+                uint64_t e = (uint64_t)so[nt - 1] + ((sl[nt - 1] + 15u) & ~15u);
+                const bool bad = (a & 15u) || e < a || e - a > qcap || e > B.total;
+                if(bad){ atomicOr(D.err, 2u); e = a; }
+                const uint32_t qbytes = (uint32_t)(e - a);
+                const uint32_t b0 = (a >> 2) & ~15u;
+                const uint32_t bbytes = qbytes ? (((uint32_t)(e >> 2) + 15u) & ~15u) - b0 : 0u;
+                mbar_expect_tx(&full[s], qbytes + bbytes);
+                if(qbytes){
+                    bulk_g2s(S, B.qual + a, qbytes, &full[s]);
+                    bulk_g2s(S + o_b, B.bases2 + b0, bbytes, &full[s]);
+                }
+            }
+        };
+        for(int k = 0; k < min(2, ntiles); ++k) prefetch(k);
+        for(int k = 0; k < ntiles; ++k){
+            const int s = k % NS;
+            uint8_t* S = sp + (size_t)s * stage_bytes;
+            const uint32_t* So = reinterpret_cast<const uint32_t*>(S + o_off);
+            const uint16_t* Sl = reinterpret_cast<const uint16_t*>(S + o_len);
+            uint32_t* clist = reinterpret_cast<uint32_t*>(S + o_cl);
+            uint2* olist = reinterpret_cast<uint2*>(S + o_ol);
+            uint32_t* cnt = reinterpret_cast<uint32_t*>(S + o_cnt);
+            const uint32_t t0 = lo + (uint32_t)k * T;
+            const int nt = (int)min((uint32_t)T, hi - t0);
+            mbar_wait(&full[s], (uint32_t)(k / NS) & 1u);
+            const uint32_t a0 = So[0];
+            const uint32_t bshift = (a0 >> 2) & 15u;
+            for(int i = tt; i < nt; i += WS_TRIM){
+                uint32_t doff = So[i] - a0, dlen = Sl[i];
+                const uint32_t padded = (dlen + 15u) & ~15u;
+                bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
+                if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
+                if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
+                const fq_read_result rec = phase1_read(D, S + doff, S + o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
+                out[t0 + i] = rec;
+                atomicAdd(&bc->filter[rec.result], 1u);
+                const bool pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
+                atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
+                if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
+                if(pass && rec.start == 0 && rec.len == dlen){
+                    clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                }else{
+                    const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
+                    olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                }
+            }
+            mbar_arrive(&ready[s]);
+            if(k + 2 < ntiles){
+                const int k2 = k + 2, n2 = k2 / NS;
+                if(n2 >= 1) mbar_wait(&freeb[k2 % NS], (uint32_t)(n2 - 1) & 1u);
+                prefetch(k2);
+            }
+        }
+        counters_add_tally(bc, tl);
+    }else{
+        // ============================ statistics warps ============================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 144;\n");
+        const int G = WS_STATS / W;
+        const int g = threadIdx.x / W, w = threadIdx.x - g * W;
+        const bool active = g < G;
+        const uint32_t l2 = smem_u32(l2base) + 4 * threadIdx.x;
+        Acc1 common, preo, posto;
+        common.zero(); preo.zero(); posto.zero();
+        int usedC = 0, leftO = 255;
+        for(int k = 0; k < ntiles; ++k){
+            const int s = k % NS;
+            const uint32_t S32 = sp32 + (uint32_t)s * stage_bytes;
+            mbar_wait(&ready[s], (uint32_t)(k / NS) & 1u);
+            if(active){
+                const uint32_t a0 = lds32(S32 + o_off);
+                const uint32_t bshift = (a0 >> 2) & 15u;
+                const uint32_t sq0 = S32, sb0 = S32 + o_b + bshift;
+                const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;
+                const int nc = (int)lds32(S32 + o_cnt), no = (int)lds32(S32 + o_cnt + 4);
+                const int mine = nc > g ? (nc - g + G - 1) / G : 0;
+                if(usedC + mine > 255){ fold(common, l2); usedC = 0; }
+                usedC += mine;
+                // ---- common reads: contribute identically to pre1 and post1 ----
+                {
+                    const uint32_t cl = S32 + o_cl;
+                    uint32_t qraw = 0, b = 0;
+                    auto fetch = [&](int i, uint32_t& q, uint32_t& bb){
+                        const uint32_t e = lds32(cl + 4 * i);
+                        const uint32_t off = (e & 0x1FFFFu) << 4, len = e >> 17;
+                        const bool in = (uint32_t)(4 * w) < len;
+                        q = lds32(in ? sqw + off : zero_addr);
+                        bb = in ? lds8(sbw + (off >> 2)) : 0u;
+                    };
+                    if(g < nc) fetch(g, qraw, b);
+                    for(int i = g; i < nc; i += G){
+                        const uint32_t qc = qraw, bcur = b;
+                        if(i + G < nc) fetch(i + G, qraw, b);
+                        acc_word(common, qc, bcur);
+                    }
+                }
+                // ---- other reads: raw part -> pre1, shifted kept part of passing reads -> post1 ----
+                const uint32_t ol = S32 + o_ol;
+                for(int i = g; i < no; i += G){
+                    const uint2 dc = lds64(ol + 8 * i);
+                    const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = dc.y >> 26;
+                    if((uint32_t)(4 * w) < len) acc_word(preo, lds32(sqw + off), lds8(sbw + (off >> 2)));
+                    if(kind == 2){
+                        const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
+                        const int nv = (int)plen - 4 * w;
+                        if(nv > 0){
+                            const uint32_t p = off + start + 4 * w;
+                            const uint32_t a1 = p & ~3u, sh = p & 3u;
+                            const uint32_t w0 = lds32(sq0 + a1);
+                            const uint32_t w1 = sh ? lds32(sq0 + a1 + 4) : 0u;
+                            uint32_t q2 = __funnelshift_r(w0, w1, sh * 8);
+                            const uint32_t c0 = lds8(sb0 + (p >> 2)), c1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
+                            uint32_t b2 = ((c0 | (c1 << 8)) >> (2 * sh)) & 0xFF;
+                            if(nv < 4){ q2 &= (1u << (8 * nv)) - 1u; b2 &= (1u << (2 * nv)) - 1u; }
+                            acc_word(posto, q2, b2);
+                        }
+                    }
+                    if(--leftO == 0){ drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w); leftO = 255; }
+                }
+            }
+            mbar_arrive(&freeb[s]);
+        }
+        if(active){
+            fold(common, l2);
+            drain_l2(l2, smPre, smPost, C, w);
+            drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w);
+        }
+    }
+    __syncthreads();
+    retire(smPre, C, D.L, flat + D.L.stats_off[0]);
+    retire(smPost, C, D.L, flat + D.L.stats_off[2]);
+    counters_flush(bc, D.L, flat);
+}
+
+size_t ws_smem_bytes(int W, int T){
+    const int C = 4 * W, Cp = (C + 15) & ~15;
+    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 8 + 16;
+    s += (size_t)L2_SLOTS * WS_STATS * 4;
+    const size_t qcap = (size_t)T * Cp, bcap = ((qcap / 4 + 15) & ~(size_t)15) + 16;
+    const size_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
+    s += NS * (qcap + bcap + mo + ml + mo + 2 * mo + 16);
+    return s + 128;
+}
+
 size_t g_smem_optin = 0;
 
 size_t fused_smem_bytes(int W, int T){
@@ -470,6 +734,7 @@ int fused_tile(int W){
 void fused_configure(const cudaDeviceProp& prop){
     g_smem_optin = prop.sharedMemPerBlockOptin;
     cudaFuncSetAttribute(k_fused_se, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -481,9 +746,26 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B){
     return fused_tile(W) >= THREADS / W;
 }
 
-int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, uint64_t* flat, int sms, cudaStream_t st){
+static int ws_tile(int W){
+    const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 2048 : 0;
+    for(int T = 256; T >= 32; T -= 16)
+        if(ws_smem_bytes(W, T) <= budget) return T;
+    return 0;
+}
+
+int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, uint64_t* flat, int sms, cudaStream_t st,
+                    int variant){
     const int W = (int)(D.L.max_cycles + 3) / 4;
     const int G = THREADS / W;
+    if(variant == 0 && ws_tile(W) > 0){
+        const int T = ws_tile(W);
+        int rpb = (int)((B.n + sms - 1) / sms);
+        rpb = std::min(rpb, 60000 * G);
+        rpb = (rpb + T - 1) / T * T;
+        const int grid = (int)((B.n + rpb - 1) / rpb);
+        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb);
+        return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    }
     const int T = fused_tile(W);
     int rpb = (int)((B.n + sms - 1) / sms);
     rpb = std::min(rpb, 60000 * G);                        // 16-bit level-2 count lanes: < 65536 reads per thread

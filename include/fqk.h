@@ -256,7 +256,7 @@ uint64_t fqk_launch_count(const fqk_ctx* ctx);    /* kernels launched so far    
 int  fqk_set_kernel_timing(fqk_ctx* ctx, int enabled);
 int  fqk_kernel_times(fqk_ctx* ctx, double ms[FQK_T_SLOTS], uint64_t launches[FQK_T_SLOTS]);
 /* implementation selector for A/B tests: 0 = automatic (fused kernel when the
- * configuration allows), 1 = generic kernels only */
+ * configuration allows), 1 = generic kernels only, 2 = single-role fused kernel */
 int  fqk_set_impl(fqk_ctx* ctx, int impl);
 
 /* zero every accumulator (Stats, FilterResult counters, insert histogram, dup table) */
