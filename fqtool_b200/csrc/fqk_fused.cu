@@ -469,8 +469,8 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
 // Three staging buffers; mbarriers: full[s] (bulk copies landed), ready[s] (lists written), free[s]
 // (statistics done with the stage).  Register budget split with setmaxnreg (144 / 80).
 // ===========================================================================
-constexpr int WS_STATS = 384, WS_TRIM = 128, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
-static_assert(WS_STATS == THREADS, "level-2 slot layout is shared with the single-role kernel");
+constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
+static_assert(WS_STATS <= THREADS, "level-2 slot layout (stride THREADS) is shared with the single-role kernel");
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar){
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
@@ -528,7 +528,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     uint64_t* full = mbar; uint64_t* ready = mbar + NS; uint64_t* freeb = mbar + 2 * NS;
     uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
     uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 2) + 15) & ~uintptr_t(15));
-    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * WS_STATS);
+    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * THREADS);
     // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
     const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
     const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
@@ -537,7 +537,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     const uint32_t sp32 = smem_u32(sp), zero_addr = smem_u32(zero_word);
 
     for(int i = threadIdx.x; i < 2 * statw; i += WS_THREADS) smPre[i] = 0;
-    for(int i = threadIdx.x; i < L2_SLOTS * WS_STATS; i += WS_THREADS) l2base[i] = 0;
+    for(int i = threadIdx.x; i < L2_SLOTS * THREADS; i += WS_THREADS) l2base[i] = 0;
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], WS_TRIM); mbar_init(&freeb[s], WS_STATS); }
@@ -552,7 +552,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 
     if(threadIdx.x >= WS_STATS){
         // ============================== trim warps ==============================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;\n");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
         const int tt = threadIdx.x - WS_STATS;
         Tally tl = {};
         const bool fast_filter = !P.complexity_enabled;
@@ -624,7 +624,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         counters_add_tally(bc, tl);
     }else{
         // ============================ statistics warps ============================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 144;\n");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 152;\n");
         const int G = WS_STATS / W;
         const int g = threadIdx.x / W, w = threadIdx.x - g * W;
         const bool active = g < G;
@@ -704,7 +704,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 size_t ws_smem_bytes(int W, int T){
     const int C = 4 * W, Cp = (C + 15) & ~15;
     size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 8 + 16;
-    s += (size_t)L2_SLOTS * WS_STATS * 4;
+    s += (size_t)L2_SLOTS * THREADS * 4;
     const size_t qcap = (size_t)T * Cp, bcap = ((qcap / 4 + 15) & ~(size_t)15) + 16;
     const size_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
     s += NS * (qcap + bcap + mo + ml + mo + 2 * mo + 16);
@@ -760,7 +760,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
     if(variant == 0 && ws_tile(W) > 0){
         const int T = ws_tile(W);
         int rpb = (int)((B.n + sms - 1) / sms);
-        rpb = std::min(rpb, 60000 * G);
+        rpb = std::min(rpb, 60000 * (WS_STATS / W));           // 16-bit level-2 count lanes: < 65536 reads per thread
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb);
