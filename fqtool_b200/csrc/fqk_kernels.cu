@@ -5,6 +5,7 @@
 //   k_dup                 : duplication table, order-independent (min, count, first) monoid
 // The specialised fused SE kernel lives in fqk_fused.cu.
 #include "fqk_trim.cuh"
+#include "fqk_pe.cuh"
 #include "fqk_kernels.h"
 
 __global__ void __launch_bounds__(256) k_trim_se(const __grid_constant__ DevParams D, DevBatch B,
@@ -41,6 +42,14 @@ struct MergedGet {
     }
 };
 
+// OverlapAnalysis::analyze: bit-parallel on packed words when both reads fit, else the scalar closed form
+__device__ inline OvRes analyze_pair(const ReadView& a, const ReadView& b, int limit, int require){
+    if(a.start + a.len > 16 * PE_MAXW || b.start + b.len > 16 * PE_MAXW) return dev_analyze(a, b, limit, require);
+    PackedSeq pa, pb, pr;
+    pack_view(a, pa); pack_view(b, pb); revcomp_packed(pb, pr);
+    return dev_analyze_packed(pa, pr, limit, require);
+}
+
 __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                                                   fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
                                                   fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat){
@@ -66,7 +75,7 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
         bool have_ov = false; OvRes ov = {0, 0, 0, 0};
         if(both){
             // first analyze(): :303 when -a/-c, else :330 (insert size only); identical inputs either way
-            ov = dev_analyze(a, b, P.overlap_diff_limit, P.overlap_require);
+            ov = analyze_pair(a, b, P.overlap_diff_limit, P.overlap_require);
             have_ov = true;
             pr.flags |= FQK_P_OV1_DONE | (ov.overlapped ? FQK_P_OV1_OVERLAP : 0);
             pr.ov1_offset = (int16_t)ov.offset; pr.ov1_len = (uint16_t)ov.len; pr.ov1_diff = (uint16_t)ov.diff;
@@ -102,7 +111,7 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
         bool merge_processed = false; int res1 = 0, res2 = 0;
         if(P.merge_enabled && both){
             // second analyze(), :354: same answer as the first when neither read changed
-            OvRes ov2 = (have_ov && !modified) ? ov : dev_analyze(a, b, P.overlap_diff_limit, P.overlap_require);
+            OvRes ov2 = (have_ov && !modified) ? ov : analyze_pair(a, b, P.overlap_diff_limit, P.overlap_require);
             pr.flags |= FQK_P_OV2_DONE | (ov2.overlapped ? FQK_P_OV2_OVERLAP : 0);
             pr.ov2_offset = (int16_t)ov2.offset; pr.ov2_len = (uint16_t)ov2.len; pr.ov2_diff = (uint16_t)ov2.diff;
             if(ov2.overlapped){
@@ -112,8 +121,18 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
                     const int len1 = ov2.len + max(0, ov2.offset);
                     const int len2 = ov2.offset > 0 ? b.len - ov2.len : 0;
                     pr.merge_len1 = (uint16_t)len1; pr.merge_len2 = (uint16_t)len2;
-                    MergedGet mg{a, b, len1, ov2.len};
-                    result = dev_pass_filter(P, len1 + len2, false, mg);
+                    if(P.complexity_enabled){
+                        MergedGet mg{a, b, len1, ov2.len};
+                        result = dev_pass_filter(P, len1 + len2, false, mg);
+                    }else{
+                        // counts of the merged read = read1 prefix + the part of read2 that is appended (order is irrelevant)
+                        int l1 = 0, n1 = 0, t1 = 0, l2 = 0, n2 = 0, t2 = 0;
+                        if(P.qual_filter_enabled){
+                            swar_counts_global(a.q, a.start, len1, P.low_quality_limit, l1, n1, t1);
+                            swar_counts_global(b.q, b.start + (b.len - ov2.len - len2), len2, P.low_quality_limit, l2, n2, t2);
+                        }
+                        result = (len1 + len2 == 0) ? FQK_FAIL_LENGTH : filter_from_counts(P, len1 + len2, l1 + l2, n1 + n2, t1 + t2);
+                    }
                     if(result == FQK_PASS_FILTER){ pr.flags |= FQK_P_MERGED; atomicAdd(&bc.merged_pairs, 1u); }
                 }
                 atomicAdd(&bc.filter[result], 2u);                      // :358
@@ -121,15 +140,15 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
                 res1 = res2 = result;
                 merge_processed = true;
             }else if(!P.merge_discard_unmerged){
-                res1 = dev_pass_filter_view(P, a, false); atomicAdd(&bc.filter[res1], 1u);
-                res2 = dev_pass_filter_view(P, b, false); atomicAdd(&bc.filter[res2], 1u);
+                res1 = pass_filter_fast(P, a, false); atomicAdd(&bc.filter[res1], 1u);
+                res2 = pass_filter_fast(P, b, false); atomicAdd(&bc.filter[res2], 1u);
                 merge_processed = true;
             }
             if(merge_processed) pr.flags |= FQK_P_MERGE_PROC;
         }
         if(!merge_processed){
-            res1 = dev_pass_filter_view(P, a, !a1);
-            res2 = dev_pass_filter_view(P, b, !a2);
+            res1 = pass_filter_fast(P, a, !a1);
+            res2 = pass_filter_fast(P, b, !a2);
             atomicAdd(&bc.filter[max(res1, res2)], 2u);                 // :390, mPaired == true
         }
         rec1.result = (uint8_t)res1; rec2.result = (uint8_t)res2;

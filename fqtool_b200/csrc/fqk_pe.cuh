@@ -1,0 +1,193 @@
+// fqk_pe.cuh -- bit-parallel paired-end helpers (one thread per pair).
+//
+// OverlapAnalysis::analyze (/root/reference/src/overlapanalysis.cpp:7-72) on 2-bit packed words:
+// 16 bases per 32-bit word, mismatches of an alignment = popcount of the folded XOR of the
+// shifted words (funnel shifts), N handled with 1-bit-per-base masks (N vs N matches, N vs
+// A/C/G/T mismatches: the reference compares characters and revcomp(N) = N, src/seq.h:41-43).
+// Same closed form as dev_analyze; a first-word quick reject removes
+// almost every wrong offset with ~15 instructions.
+#pragma once
+#include "fqk_trim.cuh"
+
+constexpr int PE_MAXW = 33;                 // words per read handled bit-parallel (528 bases); longer reads use dev_analyze
+
+struct PackedSeq {
+    uint32_t c[PE_MAXW + 2];                // 2-bit codes, base i of the view in bits 2*(i%16) of word i/16; N and padding are 0
+    uint32_t n[PE_MAXW + 2];                // N flags at the even bit of each base
+    int len;
+    bool hasN;
+};
+
+__device__ __forceinline__ uint32_t rev2(uint32_t x){      // reverse the order of the sixteen 2-bit groups
+    const uint32_t y = __brev(x);
+    return ((y >> 1) & 0x55555555u) | ((y & 0x55555555u) << 1);
+}
+__device__ __forceinline__ uint32_t valid_mask(int v){     // even-bit mask of the first v bases of a word
+    return v >= 16 ? 0x55555555u : (v <= 0 ? 0u : (((1u << (2 * v)) - 1u) & 0x55555555u));
+}
+// N flags of 16 bases starting at quality byte p (4-byte aligned) as even bits
+__device__ __forceinline__ uint32_t nflags16(const uint32_t* q32){
+    uint32_t bits = 0;
+#pragma unroll
+    for(int k = 0; k < 4; ++k){
+        const uint32_t y = (q32[k] >> 7) & 0x01010101u;
+        bits |= ((y * 0x00204081u) >> 21 & 0xFu) << (4 * k);         // gather the four flags
+    }
+    uint32_t x = bits;                                                 // spread 16 bits to the even positions
+    x = (x | (x << 8)) & 0x00FF00FFu; x = (x | (x << 4)) & 0x0F0F0F0Fu;
+    x = (x | (x << 2)) & 0x33333333u; x = (x | (x << 1)) & 0x55555555u;
+    return x;
+}
+
+// pack the current view of a read (start/len inside the original, 16-base aligned original storage)
+__device__ inline void pack_view(const ReadView& v, PackedSeq& s){
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(v.b2);
+    const uint32_t* q32 = reinterpret_cast<const uint32_t*>(v.q);
+    const int nw = (v.len + 15) >> 4;
+    const int w0 = v.start >> 4, sh = 2 * (v.start & 15);
+    s.len = v.len;
+    // any N in the words that cover the view?
+    uint32_t any = 0;
+    if(v.len > 0) for(int i = (v.start >> 2); i <= ((v.start + v.len - 1) >> 2); ++i) any |= q32[i];
+    s.hasN = (any & 0x80808080u) != 0;
+    const int nsrc = ((v.start + v.len + 15) >> 4);                    // source words that exist for this view
+    for(int j = 0; j < nw; ++j){
+        const uint32_t lo = w32[w0 + j], hi = (w0 + j + 1 < nsrc) ? w32[w0 + j + 1] : 0u;
+        uint32_t c = __funnelshift_r(lo, hi, sh);
+        uint32_t n = 0;
+        if(s.hasN){
+            const uint32_t nlo = nflags16(q32 + 4 * (w0 + j));
+            const uint32_t nhi = (w0 + j + 1 < nsrc) ? nflags16(q32 + 4 * (w0 + j + 1)) : 0u;
+            n = __funnelshift_r(nlo, nhi, sh);
+        }
+        const uint32_t vm = valid_mask(v.len - 16 * j);
+        n &= vm;
+        c &= (vm | (vm << 1)) & ~(n | (n << 1));                       // bases outside the view and N bases carry code 0
+        s.c[j] = c; s.n[j] = n;
+    }
+    for(int j = nw; j < PE_MAXW + 2; ++j){ s.c[j] = 0; s.n[j] = 0; }
+}
+
+// reverse complement (Seq::reverseComplement, src/seq.h:24-48) of a packed view
+__device__ inline void revcomp_packed(const PackedSeq& b, PackedSeq& r){
+    const int len = b.len, nw = (len + 15) >> 4;
+    const int pad = (16 - (len & 15)) & 15;                            // dummy bases in front so that the length is 16*nw
+    r.len = len; r.hasN = b.hasN;
+    for(int j = 0; j < nw; ++j){
+        const int k = nw - 1 - j;                                      // source word of B' = [pad zeros] + b
+        const uint32_t lo = k > 0 ? b.c[k - 1] : 0u, hi = b.c[k];
+        const uint32_t nlo = k > 0 ? b.n[k - 1] : 0u, nhi = b.n[k];
+        const uint32_t cw = pad ? __funnelshift_r(lo, hi, 32 - 2 * pad) : hi;
+        const uint32_t nwd = pad ? __funnelshift_r(nlo, nhi, 32 - 2 * pad) : nhi;
+        const uint32_t vm = valid_mask(len - 16 * j);
+        const uint32_t rn = rev2(nwd) & vm;
+        uint32_t rc = (rev2(cw) ^ 0x55555555u) & (vm | (vm << 1));     // complement: A<->T, C<->G is code ^ 1
+        rc &= ~(rn | (rn << 1));                                       // N stays N (code 0)
+        r.c[j] = rc; r.n[j] = rn;
+    }
+    for(int j = nw; j < PE_MAXW + 2; ++j){ r.c[j] = 0; r.n[j] = 0; }
+}
+
+// mismatches between x[xo + i] and y[yo + i] for i in [from, to) ; from is a multiple of 16
+__device__ __forceinline__ int mism_range(const PackedSeq& x, int xo, const PackedSeq& y, int yo, int from, int to){
+    int d = 0;
+    const int xs = 2 * (xo & 15), ys = 2 * (yo & 15);
+    for(int i = from; i < to; i += 16){
+        const int xw = (xo + i) >> 4, yw = (yo + i) >> 4;
+        const uint32_t xc = __funnelshift_r(x.c[xw], x.c[xw + 1], xs), yc = __funnelshift_r(y.c[yw], y.c[yw + 1], ys);
+        const uint32_t xn = __funnelshift_r(x.n[xw], x.n[xw + 1], xs), yn = __funnelshift_r(y.n[yw], y.n[yw + 1], ys);
+        const uint32_t t = xc ^ yc;
+        const uint32_t mm = (((t | (t >> 1)) & 0x55555555u) | (xn ^ yn)) & valid_mask(to - i);
+        d += __popc(mm);
+    }
+    return d;
+}
+
+// one alignment: a[ao + i] vs r[ro + i], i < ol.  Returns true (and diff) when the reference accepts it.
+__device__ __forceinline__ bool try_offset(const PackedSeq& a, int ao, const PackedSeq& r, int ro, int ol, int limit, int brk,
+                                           int& diff){
+    const int n16 = min(ol, 16);
+    int d = mism_range(a, ao, r, ro, 0, n16);                          // quick reject on the first word
+    if(d >= brk) return false;
+    const int n50 = min(ol, 50);
+    if(n50 > 16){
+        d += mism_range(a, ao, r, ro, 16, n50);
+        if(d >= brk) return false;                                     // the reference's scan breaks inside the first 50
+    }
+    if(ol > 50){
+        // positions 50.. : the word holding 48,49 was counted up to 50; count its tail then whole words
+        const int xs = 2 * (ao & 15), ys = 2 * (ro & 15);
+        const int xw = (ao + 48) >> 4, yw = (ro + 48) >> 4;
+        const uint32_t xc = __funnelshift_r(a.c[xw], a.c[xw + 1], xs), yc = __funnelshift_r(r.c[yw], r.c[yw + 1], ys);
+        const uint32_t xn = __funnelshift_r(a.n[xw], a.n[xw + 1], xs), yn = __funnelshift_r(r.n[yw], r.n[yw + 1], ys);
+        const uint32_t t = xc ^ yc;
+        const uint32_t mm = (((t | (t >> 1)) & 0x55555555u) | (xn ^ yn)) & valid_mask(ol - 48) & ~valid_mask(2);
+        d += __popc(mm);
+        if(ol > 64) d += mism_range(a, ao, r, ro, 64, ol);
+    }
+    diff = d;
+    return d < limit || ol > 50;
+}
+
+// OverlapAnalysis::analyze on packed views; r = revcomp of read2's view
+__device__ inline OvRes dev_analyze_packed(const PackedSeq& a, const PackedSeq& r, int limit, int require){
+    const int len1 = a.len, len2 = r.len;
+    const int brk = max(limit, 1);
+    OvRes o; int diff = 0;
+    for(int offset = 0; offset < len1 - require; ++offset){           // src/overlapanalysis.cpp:20-41
+        const int ol = min(len1 - offset, len2);
+        if(try_offset(a, offset, r, 0, ol, limit, brk, diff)){ o.overlapped = 1; o.offset = offset; o.len = ol; o.diff = diff; return o; }
+    }
+    for(int d = 0; -d > require - len2; ++d){                          // src/overlapanalysis.cpp:44-67 (offset = -d)
+        const int ol = min(len1, len2 - d);
+        if(try_offset(a, 0, r, d, ol, limit, brk, diff)){ o.overlapped = 1; o.offset = -d; o.len = ol; o.diff = diff; return o; }
+    }
+    o.overlapped = 0; o.offset = 0; o.len = 0; o.diff = 0;
+    return o;
+}
+
+// Filter::passFilter counts (src/filter.cpp:15-25) over [start, start+len) of a read in global memory
+__device__ inline void swar_counts_global(const uint8_t* q, int start, int len, int lim, int& lowq, int& nn, int& total){
+    lowq = nn = total = 0;
+    if(len <= 0) return;
+    const uint32_t* q32 = reinterpret_cast<const uint32_t*>(q);
+    const int end = start + len;
+    const uint32_t k = (uint32_t)(0x80 - lim) * 0x01010101u;
+    int ge = 0;
+    for(int wi = start >> 2; wi <= (end - 1) >> 2; ++wi){
+        uint32_t v = q32[wi];
+        const int p = 4 * wi;
+        if(p < start || p + 4 > end){
+            const int nlo = min(4, max(0, start - p)), nhi = min(4, max(0, p + 4 - end));
+            v &= (nlo + nhi >= 4) ? 0u : ((0xFFFFFFFFu << (8 * nlo)) & (0xFFFFFFFFu >> (8 * nhi)));
+        }
+        nn += __popc(v & 0x80808080u);
+        v &= 0x7F7F7F7Fu;
+        ge += __popc((v + k) & 0x80808080u);
+        total = (int)__dp4a(v, 0x01010101u, (uint32_t)total);
+    }
+    lowq = len - ge;
+    total -= 33 * len;
+}
+
+// passFilter decision from the counts (same priority order as src/filter.cpp:26-45)
+__device__ __forceinline__ int filter_from_counts(const fq_params& P, int rlen, int lowq, int nn, int total){
+    if(P.qual_filter_enabled){
+        if(lowq > P.low_quality_base_limit) return FQK_FAIL_QUALITY;
+        if(P.average_quality_limit > 0 && P.average_quality_limit > (double)total / rlen) return FQK_FAIL_QUALITY;
+        if(nn > P.n_base_limit) return FQK_FAIL_N_BASE;
+    }
+    if(P.length_filter_enabled){
+        if(rlen < P.min_read_length) return FQK_FAIL_LENGTH;
+        if(P.max_read_length > 0 && rlen > P.max_read_length) return FQK_FAIL_TOO_LONG;
+    }
+    return FQK_PASS_FILTER;
+}
+__device__ inline int pass_filter_fast(const fq_params& P, const ReadView& v, bool isnull){
+    if(isnull || v.len == 0) return FQK_FAIL_LENGTH;
+    if(P.complexity_enabled) return dev_pass_filter_view(P, v, false);
+    if(!P.qual_filter_enabled && !P.length_filter_enabled) return FQK_PASS_FILTER;
+    int lowq = 0, nn = 0, total = 0;
+    if(P.qual_filter_enabled) swar_counts_global(v.q, v.start, v.len, P.low_quality_limit, lowq, nn, total);
+    return filter_from_counts(P, v.len, lowq, nn, total);
+}
