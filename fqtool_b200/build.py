@@ -36,5 +36,25 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST = os.path.join(HERE, "host")
+HOST_EXE = os.path.join(HOST, "fqk_run")
+
+
+def build_host(force=False, verbose=False):
+    """C++ host adapter + command-line harness (g++), linked against libfqk.so."""
+    build(force=False)
+    srcs = [os.path.join(HOST, f) for f in ("fqk_host.cpp", "fqk_run.cpp")]
+    deps = srcs + [os.path.join(HOST, "fqk_host.hpp"), LIB, os.path.join(HERE, "..", "include", "fqk.h")]
+    if not force and os.path.exists(HOST_EXE) and all(os.path.getmtime(d) <= os.path.getmtime(HOST_EXE) for d in deps):
+        return HOST_EXE
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(HERE, "..", "include")] + srcs + \
+          ["-o", HOST_EXE, "-L" + CSRC, "-lfqk", "-lz", "-Wl,-rpath,$ORIGIN/../csrc"]
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.run(cmd, check=True)
+    return HOST_EXE
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+    print(build_host(force="--force" in sys.argv, verbose=True))

@@ -17,5 +17,6 @@ def _built():
     """Build the CUDA library (nvcc cross-compiles without a GPU) and the oracle once per session."""
     from fqtool_b200 import build
     build.build()
+    build.build_host()
     from oracle import pyoracle
     pyoracle.build()
