@@ -62,6 +62,7 @@ struct fqk_ctx {
     cudaStream_t stream = nullptr;
     uint64_t* flat = nullptr;                 // device accumulators (fq_stats_layout)
     uint32_t* err = nullptr;                  // device error flag
+    uint32_t* maxlen2 = nullptr;              // device: longest raw read of each mate in the current PE batch
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
     StagedBatch st[2];
@@ -219,6 +220,7 @@ extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal,
     if(cudaMalloc(&c->flat, c->D.L.total_u64 * sizeof(uint64_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "accumulator alloc failed");
     if(cudaMalloc(&c->err, sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "flag alloc failed");
     c->D.err = c->err;
+    if(cudaMalloc(&c->maxlen2, 2 * sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "scalar alloc failed");
     if(c->D.L.dup_bins){
         const uint64_t n = c->D.L.dup_bins;
         if(cudaMalloc(&c->tab128, n * 16) != cudaSuccess || cudaMalloc(&c->first64, n * 8) != cudaSuccess ||
@@ -254,7 +256,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(auto& e : c->evpool) cudaEventDestroy(e);
     for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
     c->res1.release(); c->res2.release(); c->resp.release();
-    cudaFree(c->flat); cudaFree(c->err); cudaFree(c->tab128); cudaFree(c->first64);
+    cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
     if(c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -325,11 +327,19 @@ static int launch_pe(fqk_ctx* c, const DevBatch& B1, const DevBatch& B2, fq_read
     if(B1.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
     { Timer t(c, FQK_T_TRIM);
-      k_trim_pe<<<grid_for(c, B1.n, 128, 8), 128, 0, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat); c->launches++; }
-    { Timer t(c, FQK_T_STATS);
-      const int Cs = c->stats_cs_pe;
-      k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs);
-      c->launches++; }
+      cudaMemsetAsync(c->maxlen2, 0, 2 * sizeof(uint32_t), c->stream);
+      k_trim_pe<<<grid_for(c, B1.n, 128, 8), 128, 0, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, c->maxlen2); c->launches++; }
+    if(c->impl != 1 && ws_stats_supported_pe(c->D, B1, B2)){
+        Timer t(c, FQK_T_FUSED);
+        int nl = ws_stats_launch_pe(c->D, B1, B2, o1, o2, op, c->flat, c->sms, c->stream, c->maxlen2);
+        if(nl < 0) return fail(c, FQK_E_CUDA, "PE statistics launch failed");
+        c->launches += nl;
+    }else{
+        Timer t(c, FQK_T_STATS);
+        const int Cs = c->stats_cs_pe;
+        k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs);
+        c->launches++;
+    }
     if(c->D.P.dup_enabled){
         Timer t(c, FQK_T_DUP);
         k_dup<<<grid_for(c, B1.n, 256, 8), 256, 0, c->stream>>>(c->D, B1, B2, 1, c->tab128, c->first64); c->launches++;

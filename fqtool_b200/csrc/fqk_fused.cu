@@ -160,46 +160,47 @@ __device__ __forceinline__ void drain_l2(uint32_t l2, uint32_t* smA, uint32_t* s
     drain2(vals, smA, smB, C, w);
 }
 
-// block retirement: sets -> bins, raw quality chars -> Phred (minus 33 per base), add to the global u64 arrays
+// block retirement: sets -> bins, raw quality chars -> Phred (minus 33 per base), add to the global u64 arrays.
+// Everything is linear and evaluated in wrapping signed arithmetic, so a block may hold a partial view
+// (e.g. only the tail of merged reads: length histogram entries +1 at the end, -1 at the start of the range).
 __device__ void retire(const uint32_t* sm, int C, const fq_stats_layout& L, uint64_t* S){
     const uint32_t* lenhist = sm + 4 * NSETS * C;
     const uint64_t GC = L.max_cycles;
     for(int i = threadIdx.x; i < C; i += blockDim.x){
-        uint32_t nall = 0;                                // reads longer than i
-        for(int l = i + 1; l <= C; ++l) nall += lenhist[l];
-        if(!nall) continue;
-        uint32_t v[4][NSETS];
+        int32_t nall = 0;                                 // reads covering cycle i
+        for(int l = i + 1; l <= C; ++l) nall += (int32_t)lenhist[l];
+        uint32_t v[4][NSETS]; uint32_t any = (uint32_t)nall;
 #pragma unroll
         for(int k = 0; k < 4; ++k)
 #pragma unroll
-            for(int s = 0; s < NSETS; ++s) v[k][s] = sm[(k * NSETS + s) * C + i];
-        v[KN][S_ALL] = nall;
-        uint64_t tb = 0, tq = 0;
+            for(int s = 0; s < NSETS; ++s){ v[k][s] = sm[(k * NSETS + s) * C + i]; any |= v[k][s]; }
+        if(!any) continue;
+        int64_t tb = 0, tq = 0;
 #pragma unroll
         for(int cls = 0; cls < 5; ++cls){
             int64_t r[4];
 #pragma unroll
             for(int k = 0; k < 4; ++k){
-                const int64_t all = v[k][S_ALL], b0 = v[k][S_B0], b1 = v[k][S_B1], b01 = v[k][S_B01], nn = v[k][S_N];
+                const int64_t all = k == KN ? (int64_t)nall : (int64_t)v[k][S_ALL];
+                const int64_t b0 = v[k][S_B0], b1 = v[k][S_B1], b01 = v[k][S_B01], nn = v[k][S_N];
                 r[k] = cls == 0 ? all - b0 - b1 + b01 - nn : cls == 1 ? b0 - b01 : cls == 2 ? b1 - b01 : cls == 3 ? b01 : nn;
             }
-            if(!r[KN]) continue;
             const int64_t qs = r[KQS] - 33 * r[KN];
             const int bin = cls_to_bin(cls);
-            add_u64(S + L.s_content + bin * GC + i, (uint64_t)r[KN]);
+            if(r[KN]) add_u64(S + L.s_content + bin * GC + i, (uint64_t)r[KN]);
             if(r[KN20]) add_u64(S + L.s_q20 + bin * GC + i, (uint64_t)r[KN20]);
             if(r[KN30]) add_u64(S + L.s_q30 + bin * GC + i, (uint64_t)r[KN30]);
             if(qs) add_u64(S + L.s_qualsum + bin * GC + i, (uint64_t)qs);
-            tb += (uint64_t)r[KN]; tq += (uint64_t)qs;
+            tb += r[KN]; tq += qs;
         }
-        add_u64(S + L.s_total_base + i, tb);
-        add_u64(S + L.s_total_qual + i, tq);
+        if(tb) add_u64(S + L.s_total_base + i, (uint64_t)tb);
+        if(tq) add_u64(S + L.s_total_qual + i, (uint64_t)tq);
     }
-    uint64_t nr = 0, ls = 0;                              // reads / length_sum from the histogram
-    for(int l = threadIdx.x; l <= C; l += blockDim.x){ nr += lenhist[l]; ls += (uint64_t)lenhist[l] * l; }
+    int64_t nr = 0, ls = 0;                               // reads / length_sum from the histogram
+    for(int l = threadIdx.x; l <= C; l += blockDim.x){ const int64_t h = (int32_t)lenhist[l]; nr += h; ls += h * l; }
 #pragma unroll
     for(int o = 16; o; o >>= 1){ nr += __shfl_xor_sync(0xffffffffu, nr, o); ls += __shfl_xor_sync(0xffffffffu, ls, o); }
-    if((threadIdx.x & 31) == 0 && nr){ add_u64(S + L.s_reads, nr); add_u64(S + L.s_length_sum, ls); }
+    if((threadIdx.x & 31) == 0){ if(nr) add_u64(S + L.s_reads, (uint64_t)nr); if(ls) add_u64(S + L.s_length_sum, (uint64_t)ls); }
 }
 
 // ------------------------------------------------------------- async staging
@@ -514,9 +515,22 @@ __device__ __forceinline__ fq_read_result phase1_read(const DevParams& D, const 
     return rec;
 }
 
+// What the kernel does with a batch.  mode 0: single-end, records are computed here (phase 1).
+// mode 1: statistics of one mate of a paired-end batch from the records k_trim_pe wrote (pre = raw read,
+// post = the mate's own contribution following src/peprocessor.cpp:353-429).  mode 2: read2's batch once
+// more, only the reverse-complemented tails that OverlapAnalysis::merge appends to merged reads
+// (src/overlapanalysis.cpp:80-93), which belong to post1 at cycles [len1, len1+len2).
+struct StatsMode {
+    int mode, mate, merge_enabled, pre_obj, post_obj;
+    const fq_read_result* recA;      // records of this mate
+    const fq_read_result* recB;      // records of the other mate
+    const fq_pair_result* recP;
+    const uint32_t* maxlen;          // device scalar: longest raw read of this mate's batch (or nullptr)
+};
+
 __global__ void __launch_bounds__(WS_THREADS, 1)
 k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
-              uint64_t* __restrict__ flat, int W, int T, int reads_per_block){
+              uint64_t* __restrict__ flat, int W, int T, int reads_per_block, const StatsMode M){
     extern __shared__ __align__(128) uint8_t smraw[];
     const fq_params& P = D.P;
     const int C = 4 * W, Cp = (C + 15) & ~15;
@@ -601,17 +615,49 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
                 if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
                 if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
-                const fq_read_result rec = phase1_read(D, S + doff, S + o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
-                out[t0 + i] = rec;
-                atomicAdd(&bc->filter[rec.result], 1u);
-                const bool pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
-                atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
-                if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
-                if(pass && rec.start == 0 && rec.len == dlen){
-                    clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                if(M.mode == 0){
+                    const fq_read_result rec = phase1_read(D, S + doff, S + o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
+                    out[t0 + i] = rec;
+                    atomicAdd(&bc->filter[rec.result], 1u);
+                    const bool pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
+                    atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
+                    if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
+                    if(pass && rec.start == 0 && rec.len == dlen){
+                        clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                    }else{
+                        const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
+                        olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                    }
                 }else{
-                    const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
-                    olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                    const fq_read_result ra = M.recA[t0 + i], rb = M.recB[t0 + i];
+                    const fq_pair_result pr = M.recP[t0 + i];
+                    const bool alive = !(ra.flags & FQK_F_DROPPED) && !(rb.flags & FQK_F_DROPPED);
+                    if(M.mode == 1){
+                        bool own = false; uint32_t start = ra.start, plen = ra.len;
+                        if(alive){
+                            if(!M.merge_enabled) own = ra.result == FQK_PASS_FILTER && rb.result == FQK_PASS_FILTER;   // :392-401
+                            else if(pr.flags & FQK_P_OV2_OVERLAP){                                                      // :355-366
+                                if((pr.flags & FQK_P_MERGED) && M.mate == 0){ own = true; plen = pr.merge_len1; }       // read1 prefix of the merged read
+                            }else if(pr.flags & FQK_P_MERGE_PROC) own = ra.result == FQK_PASS_FILTER;                  // :367-380
+                        }
+                        atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
+                        if(own) atomicAdd(smPost + 4 * NSETS * C + plen, 1u);
+                        if(own && start == 0 && plen == dlen){
+                            clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                        }else{
+                            const Desc d = make_desc(doff, dlen, start, plen, own ? 2u : 1u);
+                            olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                        }
+                    }else if(alive && (pr.flags & FQK_P_MERGED) && pr.merge_len2 > 0){
+                        // tail of the merged read: revcomp(read2 kept part)[ol, ol+len2) lands on cycles [len1, len1+len2);
+                        // cycle c reads original position pmax - c of read2
+                        const uint32_t len1 = pr.merge_len1, len2 = pr.merge_len2;
+                        const uint32_t pmax = (uint32_t)ra.start + ra.len - 1u - pr.ov2_len + len1;
+                        atomicAdd(smPost + 4 * NSETS * C + len1 + len2, 1u);
+                        atomicAdd(smPost + 4 * NSETS * C + len1, 0xFFFFFFFFu);          // -1: the tail does not cover [0, len1)
+                        const Desc d = make_desc(doff, pmax, len1, len2, 3u);
+                        olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                    }
                 }
             }
             mbar_arrive(&ready[s]);
@@ -625,8 +671,12 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     }else{
         // ============================ statistics warps ============================
         asm volatile("setmaxnreg.inc.sync.aligned.u32 152;\n");
-        const int G = WS_STATS / W;
-        const int g = threadIdx.x / W, w = threadIdx.x - g * W;
+        // threads per read: enough words for the longest raw read of the batch when it is known
+        // (paired-end: max_cycles also has to hold merged reads, twice the raw length)
+        int Wr = W;
+        if(M.maxlen && M.mode == 1) Wr = min(W, max(8, (int)((*M.maxlen + 3u) >> 2)));
+        const int G = WS_STATS / Wr;
+        const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
         const uint32_t l2 = smem_u32(l2base) + 4 * threadIdx.x;
         Acc1 common, preo, posto;
@@ -668,6 +718,30 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 for(int i = g; i < no; i += G){
                     const uint2 dc = lds64(ol + 8 * i);
                     const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = dc.y >> 26;
+                    if(kind == 3){
+                        const int len1 = (int)(dc.y & 0x1FFFu), len2 = (int)((dc.y >> 13) & 0x1FFFu), pmax = (int)len;
+                        const int c0 = 4 * w, lo = max(len1, c0), hi = min(len1 + len2, c0 + 4);
+                        if(lo < hi){
+                            const int addr = (int)off + pmax - c0 - 3;                  // tile position of the byte for cycle c0+3
+                            const int a1 = addr & ~3, sh = addr & 3;
+                            const uint32_t q4 = __funnelshift_r(lds32(sq0 + a1), lds32(sq0 + a1 + 4), sh * 8);
+                            uint32_t q2 = __byte_perm(q4, 0, 0x0123);                  // reversed: byte j <-> cycle c0+j
+                            const uint32_t cb = lds8(sb0 + (addr >> 2)) | (lds8(sb0 + (addr >> 2) + 1) << 8);
+                            uint32_t b2 = (cb >> (2 * sh)) & 0xFF;
+                            b2 = ((b2 & 0x03) << 6) | ((b2 & 0x0C) << 2) | ((b2 & 0x30) >> 2) | ((b2 & 0xC0) >> 6);
+                            b2 ^= 0x55;                                                 // complement: A<->T, C<->G
+                            const int jlo = lo - c0, jhi = hi - c0;
+                            const uint32_t bm = (jhi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * jhi)) - 1u)) & ~((1u << (8 * jlo)) - 1u);
+                            q2 &= bm;
+                            const uint32_t f = ((((q2 >> 7) & 0x01010101u) * 0x00204081u) >> 21) & 0xFu;   // N flags of the 4 bytes
+                            uint32_t sp = (f & 1u) | ((f & 2u) << 1) | ((f & 4u) << 2) | ((f & 8u) << 3);
+                            sp |= sp << 1;
+                            b2 &= ((1u << (2 * jhi)) - 1u) & ~((1u << (2 * jlo)) - 1u) & ~sp;   // N keeps code 0
+                            acc_word(posto, q2, b2);
+                        }
+                        if(--leftO == 0){ drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w); leftO = 255; }
+                        continue;
+                    }
                     if((uint32_t)(4 * w) < len) acc_word(preo, lds32(sqw + off), lds8(sbw + (off >> 2)));
                     if(kind == 2){
                         const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
@@ -696,8 +770,8 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         }
     }
     __syncthreads();
-    retire(smPre, C, D.L, flat + D.L.stats_off[0]);
-    retire(smPost, C, D.L, flat + D.L.stats_off[2]);
+    if(M.mode != 2) retire(smPre, C, D.L, flat + D.L.stats_off[M.pre_obj]);
+    retire(smPost, C, D.L, flat + D.L.stats_off[M.post_obj]);
     counters_flush(bc, D.L, flat);
 }
 
@@ -763,7 +837,8 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         rpb = std::min(rpb, 60000 * (WS_STATS / W));           // 16-bit level-2 count lanes: < 65536 reads per thread
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
-        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb);
+        const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
+        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb, M);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     const int T = fused_tile(W);
@@ -773,4 +848,28 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
     const int grid = (int)((B.n + rpb - 1) / rpb);
     k_fused_se<<<grid, THREADS, fused_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// paired-end statistics from the records of k_trim_pe: read1 pass, read2 pass and (with -m) the merged tails
+bool ws_stats_supported_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2){
+    return fused_supported_se(D, B1) && fused_supported_se(D, B2) && ws_tile((int)(D.L.max_cycles + 3) / 4) > 0;
+}
+
+int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2, const fq_read_result* r1,
+                       const fq_read_result* r2, const fq_pair_result* rp, uint64_t* flat, int sms, cudaStream_t st,
+                       const uint32_t* maxlen2){
+    const int W = (int)(D.L.max_cycles + 3) / 4;
+    const int T = ws_tile(W);
+    int rpb = (int)((B1.n + sms - 1) / sms);
+    rpb = std::min(rpb, 60000 * (WS_STATS / W));
+    rpb = (rpb + T - 1) / T * T;
+    const int grid = (int)((B1.n + rpb - 1) / rpb);
+    const int merge = D.P.merge_enabled;
+    const StatsMode M1{1, 0, merge, 0, 2, r1, r2, rp, maxlen2}, M2{1, 1, merge, 1, 3, r2, r1, rp, maxlen2 ? maxlen2 + 1 : nullptr},
+                    M3{2, 1, merge, 1, 2, r2, r1, rp, nullptr};
+    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+    int n = 2;
+    if(merge){ k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
+    return cudaGetLastError() == cudaSuccess ? n : -1;
 }

@@ -7,3 +7,9 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B);
 // variant 0: warp-specialised kernel (default), 2: single-role kernel
 int  fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, uint64_t* flat, int sms, cudaStream_t st,
                      int variant);
+
+// paired-end per-cycle statistics (SWAR kernel in statistics-only mode) from the records of k_trim_pe
+bool ws_stats_supported_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2);
+int  ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2, const fq_read_result* r1,
+                        const fq_read_result* r2, const fq_pair_result* rp, uint64_t* flat, int sms, cudaStream_t st,
+                        const uint32_t* maxlen2 /* device: longest raw read of each mate, or nullptr */);

@@ -52,14 +52,19 @@ __device__ inline OvRes analyze_pair(const ReadView& a, const ReadView& b, int l
 
 __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                                                   fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
-                                                  fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat){
+                                                  fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
+                                                  uint32_t* __restrict__ maxlen2){
     __shared__ BlockCounters bc;
+    __shared__ uint32_t smax[2];
     counters_zero(&bc);
+    if(threadIdx.x < 2) smax[threadIdx.x] = 0;
     __syncthreads();
     const fq_params& P = D.P;
     Tally tl = {};
+    uint32_t m1 = 0, m2 = 0;
     for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B1.n; r += gridDim.x * blockDim.x){
         ReadView a = make_view(B1, r), b = make_view(B2, r);
+        m1 = max(m1, (uint32_t)a.len); m2 = max(m2, (uint32_t)b.len);
         fq_read_result rec1 = {}, rec2 = {};
         fq_pair_result pr = {};
         pr.insert_size = 0xFFFF;
@@ -157,8 +162,10 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
         out1[r] = rec1; out2[r] = rec2; outp[r] = pr;
     }
     counters_add_tally(&bc, tl);
+    atomicMax(&smax[0], m1); atomicMax(&smax[1], m2);
     __syncthreads();
     counters_flush(&bc, D.L, flat);
+    if(threadIdx.x < 2 && maxlen2) atomicMax(&maxlen2[threadIdx.x], smax[threadIdx.x]);   // longest raw read of each mate
 }
 
 // -------------------------------------------------------------------- stats

@@ -6,7 +6,7 @@ __global__ void k_trim_se(const __grid_constant__ DevParams D, DevBatch B,
                           fq_read_result* __restrict__ out, uint64_t* __restrict__ flat);
 __global__ void k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                           fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
-                          fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat);
+                          fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat, uint32_t* __restrict__ maxlen2);
 __global__ void k_stats_se(const __grid_constant__ DevParams D, DevBatch B,
                            const fq_read_result* __restrict__ res, uint64_t* __restrict__ flat, int Cs);
 __global__ void k_stats_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
