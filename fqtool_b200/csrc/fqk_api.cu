@@ -210,6 +210,14 @@ extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal,
     if(c->D.P.max_cycles == 0) c->D.P.max_cycles = 512;
     for(int i = 0; i < p->adapter_r1_len; ++i) c->D.ad1[i] = (uint8_t)cls_of_char(p->adapter_r1[i]);
     for(int i = 0; i < p->adapter_r2_len; ++i) c->D.ad2[i] = (uint8_t)cls_of_char(p->adapter_r2[i]);
+    for(int i = 0; i < p->adapter_r1_len; ++i){
+        const int cl = c->D.ad1[i];
+        if(cl == 4) c->D.adn1[i >> 4] |= 1u << (2 * (i & 15)); else c->D.adc1[i >> 4] |= (uint32_t)cl << (2 * (i & 15));
+    }
+    for(int i = 0; i < p->adapter_r2_len; ++i){
+        const int cl = c->D.ad2[i];
+        if(cl == 4) c->D.adn2[i >> 4] |= 1u << (2 * (i & 15)); else c->D.adc2[i >> 4] |= (uint32_t)cl << (2 * (i & 15));
+    }
     fqk_stats_layout(&c->D.P, &c->D.L);
     auto bail = [&](int code, const std::string& m){ std::string mm = m; fqk_destroy(c); return fail(nullptr, code, mm); };
     if(cudaSetDevice(device_ordinal) != cudaSuccess) return bail(FQK_E_CUDA, "cudaSetDevice failed");

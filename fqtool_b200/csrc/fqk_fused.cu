@@ -31,6 +31,7 @@
 // (raw part for pre1, shifted kept part for post1) drained with shared atomics.
 #include <algorithm>
 #include "fqk_fused.h"
+#include "fqk_pe.cuh"
 
 namespace {
 
@@ -368,7 +369,7 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
                 const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
                 if(alive){
                     if(P.polyg_enabled) dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
-                    if(P.adapter_trim_enabled && P.adapter_r1_len > 0) dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
+                    if(P.adapter_trim_enabled && P.adapter_r1_len > 0) trim_by_sequence_any(D, v, 0, rec, tl);
                     if(P.polyx_enabled) dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
                     if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
                 }
@@ -471,6 +472,7 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
 // (statistics done with the stage).  Register budget split with setmaxnreg (144 / 80).
 // ===========================================================================
 constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
+constexpr int KMER_SMEM_MAX = 6;
 static_assert(WS_STATS <= THREADS, "level-2 slot layout (stride THREADS) is shared with the single-role kernel");
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar){
@@ -489,7 +491,7 @@ __device__ __forceinline__ fq_read_result phase1_read(const DevParams& D, const 
     const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
     if(alive){
         if(P.polyg_enabled) dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
-        if(P.adapter_trim_enabled && P.adapter_r1_len > 0) dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
+        if(P.adapter_trim_enabled && P.adapter_r1_len > 0) trim_by_sequence_any(D, v, 0, rec, tl);
         if(P.polyx_enabled) dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
         if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
     }
@@ -513,6 +515,37 @@ __device__ __forceinline__ fq_read_result phase1_read(const DevParams& D, const 
     if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
     else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
     return rec;
+}
+
+// k-mers ending at view indices 4w .. 4w+3 of the view [vstart, vstart+vlen) of a staged read (tile offset off).
+// The 16 bases ending at the thread's last position are one unaligned 32-bit window of the packed bases;
+// reversing its 2-bit groups puts earlier bases at higher bits = Evaluator::seq2int's key order
+// (src/evaluator.cpp:3-49).  A k-mer counts iff all k bases are A/T/C/G: reads without N skip the check.
+__device__ __forceinline__ void kmers_word(uint32_t sq0, uint32_t sb0, uint32_t off, uint32_t vstart, uint32_t vlen, uint32_t hasN,
+                                           int w, int K, uint64_t* histA, uint64_t* histB, uint32_t smhist = 0){
+    if((uint32_t)(4 * w) >= vlen) return;
+    const int e = (int)(off + vstart) + 4 * w + 3;                   // tile position of view index 4w+3
+    const int s0 = e - 15, bi = s0 >> 2;
+    const int a = bi & ~3, sh = 8 * (bi & 3) + 2 * (s0 & 3);
+    const uint32_t win = __funnelshift_r(lds32(sb0 + a), lds32(sb0 + a + 4), sh);
+    uint32_t rw = __brev(win);
+    rw = ((rw >> 1) & 0x55555555u) | ((rw & 0x55555555u) << 1);
+    const uint32_t mask = (K >= 16) ? 0xFFFFFFFFu : ((1u << (2 * K)) - 1u);
+#pragma unroll
+    for(int j = 0; j < 4; ++j){
+        const int i = 4 * w + j;
+        if(i < K - 1 || (uint32_t)i >= vlen) continue;
+        bool ok = true;
+        if(hasN){
+            const uint32_t qa = sq0 + off + vstart + (uint32_t)i;
+            for(int t = 0; t < K; ++t) ok &= !(lds8(qa - t) & 0x80u);
+        }
+        if(ok){
+            const uint32_t key = (rw >> (2 * (3 - j))) & mask;
+            if(smhist) asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(smhist + 4 * key) : "memory");
+            else { add_u64(histA + key, 1); if(histB) add_u64(histB + key, 1); }
+        }
+    }
 }
 
 // What the kernel does with a batch.  mode 0: single-end, records are computed here (phase 1).
@@ -542,7 +575,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     uint64_t* full = mbar; uint64_t* ready = mbar + NS; uint64_t* freeb = mbar + 2 * NS;
     uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
     uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 2) + 15) & ~uintptr_t(15));
-    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * THREADS);
+    // k-mer histograms privatised per block when 3 x 4^k counters fit (k <= 6): common / pre-only / post-only
+    const uint32_t kbins = (P.kmer_len > 0 && P.kmer_len <= KMER_SMEM_MAX) ? (1u << (2 * P.kmer_len)) : 0u;
+    uint32_t* khist = l2base + L2_SLOTS * THREADS;
+    uint8_t* sp = reinterpret_cast<uint8_t*>(khist + 3 * kbins);
     // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
     const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
     const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
@@ -552,6 +588,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 
     for(int i = threadIdx.x; i < 2 * statw; i += WS_THREADS) smPre[i] = 0;
     for(int i = threadIdx.x; i < L2_SLOTS * THREADS; i += WS_THREADS) l2base[i] = 0;
+    for(int i = threadIdx.x; i < (int)(3 * kbins); i += WS_THREADS) khist[i] = 0;
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], WS_TRIM); mbar_init(&freeb[s], WS_STATS); }
@@ -615,6 +652,13 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
                 if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
                 if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
+                uint32_t hasN = 0;                                    // k-mer validity needs to know whether the raw read holds any N
+                if(P.kmer_len){
+                    uint32_t any = 0;
+                    const uint32_t qa = smem_u32(S + doff);
+                    for(uint32_t c = 0; c < padded; c += 16){ const uint4 v = lds128(qa + c); any |= v.x | v.y | v.z | v.w; }
+                    hasN = (any & 0x80808080u) ? 1u : 0u;
+                }
                 if(M.mode == 0){
                     const fq_read_result rec = phase1_read(D, S + doff, S + o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
                     out[t0 + i] = rec;
@@ -623,10 +667,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
                     if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
                     if(pass && rec.start == 0 && rec.len == dlen){
-                        clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                        clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17) | hasN << 30;
                     }else{
                         const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
-                        olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                        olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y | hasN << 28);
                     }
                 }else{
                     const fq_read_result ra = M.recA[t0 + i], rb = M.recB[t0 + i];
@@ -643,10 +687,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                         atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
                         if(own) atomicAdd(smPost + 4 * NSETS * C + plen, 1u);
                         if(own && start == 0 && plen == dlen){
-                            clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17);
+                            clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17) | hasN << 30;
                         }else{
                             const Desc d = make_desc(doff, dlen, start, plen, own ? 2u : 1u);
-                            olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y);
+                            olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y | hasN << 28);
                         }
                     }else if(alive && (pr.flags & FQK_P_MERGED) && pr.merge_len2 > 0){
                         // tail of the merged read: revcomp(read2 kept part)[ol, ol+len2) lands on cycles [len1, len1+len2);
@@ -701,7 +745,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     uint32_t qraw = 0, b = 0;
                     auto fetch = [&](int i, uint32_t& q, uint32_t& bb){
                         const uint32_t e = lds32(cl + 4 * i);
-                        const uint32_t off = (e & 0x1FFFFu) << 4, len = e >> 17;
+                        const uint32_t off = (e & 0x1FFFFu) << 4, len = (e >> 17) & 0x1FFFu;
                         const bool in = (uint32_t)(4 * w) < len;
                         q = lds32(in ? sqw + off : zero_addr);
                         bb = in ? lds8(sbw + (off >> 2)) : 0u;
@@ -717,7 +761,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 const uint32_t ol = S32 + o_ol;
                 for(int i = g; i < no; i += G){
                     const uint2 dc = lds64(ol + 8 * i);
-                    const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = dc.y >> 26;
+                    const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = (dc.y >> 26) & 3u;
                     if(kind == 3){
                         const int len1 = (int)(dc.y & 0x1FFFu), len2 = (int)((dc.y >> 13) & 0x1FFFu), pmax = (int)len;
                         const int c0 = 4 * w, lo = max(len1, c0), hi = min(len1 + len2, c0 + 4);
@@ -760,6 +804,25 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     }
                     if(--leftO == 0){ drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w); leftO = 255; }
                 }
+                // ---- k-mer histograms (Stats::statRead, src/stats.cpp:266-274): a separate sweep over the two lists ----
+                if(P.kmer_len){
+                    uint64_t* kpre = flat + D.L.stats_off[M.pre_obj] + D.L.s_kmer;
+                    uint64_t* kpost = flat + D.L.stats_off[M.post_obj] + D.L.s_kmer;
+                    const uint32_t cl = S32 + o_cl;
+                    const uint32_t kh32 = kbins ? smem_u32(khist) : 0u;
+                    for(int i = g; i < nc; i += G){
+                        const uint32_t e = lds32(cl + 4 * i);
+                        kmers_word(sq0, sb0, (e & 0x1FFFFu) << 4, 0, (e >> 17) & 0x1FFFu, (e >> 30) & 1u, w, P.kmer_len, kpre, kpost, kh32);
+                    }
+                    for(int i = g; i < no; i += G){
+                        const uint2 dc = lds64(ol + 8 * i);
+                        const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = (dc.y >> 26) & 3u, hn = (dc.y >> 28) & 1u;
+                        if(kind == 3) continue;
+                        kmers_word(sq0, sb0, off, 0, len, hn, w, P.kmer_len, kpre, nullptr, kh32 ? kh32 + 4 * kbins : 0u);
+                        if(kind == 2) kmers_word(sq0, sb0, off, dc.y & 0x1FFFu, (dc.y >> 13) & 0x1FFFu, hn, w, P.kmer_len, kpost, nullptr,
+                                                 kh32 ? kh32 + 8 * kbins : 0u);
+                    }
+                }
             }
             mbar_arrive(&freeb[s]);
         }
@@ -770,15 +833,25 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         }
     }
     __syncthreads();
+    if(kbins){
+        uint64_t* kpre = flat + D.L.stats_off[M.pre_obj] + D.L.s_kmer;
+        uint64_t* kpost = flat + D.L.stats_off[M.post_obj] + D.L.s_kmer;
+        for(uint32_t i = threadIdx.x; i < kbins; i += WS_THREADS){
+            const uint32_t c = khist[i], a = khist[kbins + i], b = khist[2 * kbins + i];
+            if(c + a) add_u64(kpre + i, (uint64_t)c + a);
+            if(c + b) add_u64(kpost + i, (uint64_t)c + b);
+        }
+    }
     if(M.mode != 2) retire(smPre, C, D.L, flat + D.L.stats_off[M.pre_obj]);
     retire(smPost, C, D.L, flat + D.L.stats_off[M.post_obj]);
     counters_flush(bc, D.L, flat);
 }
 
-size_t ws_smem_bytes(int W, int T){
+size_t ws_smem_bytes(int W, int T, int K = 0){
     const int C = 4 * W, Cp = (C + 15) & ~15;
     size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 8 + 16;
     s += (size_t)L2_SLOTS * THREADS * 4;
+    if(K > 0 && K <= KMER_SMEM_MAX) s += (size_t)3 * 4 * ((size_t)1 << (2 * K));
     const size_t qcap = (size_t)T * Cp, bcap = ((qcap / 4 + 15) & ~(size_t)15) + 16;
     const size_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
     s += NS * (qcap + bcap + mo + ml + mo + 2 * mo + 16);
@@ -805,6 +878,8 @@ int fused_tile(int W){
 
 } // namespace
 
+static int ws_tile(int W, int K = 0);
+
 void fused_configure(const cudaDeviceProp& prop){
     g_smem_optin = prop.sharedMemPerBlockOptin;
     cudaFuncSetAttribute(k_fused_se, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
@@ -812,18 +887,19 @@ void fused_configure(const cudaDeviceProp& prop){
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
-    if(D.P.kmer_len != 0) return false;                    // k-mer histogram: generic kernels
+    if(D.P.kmer_len > 13) return false;                    // k-mers longer than the 16-base window: generic kernels
     const int W = (int)(D.L.max_cycles + 3) / 4;
+    if(D.P.kmer_len && ws_tile(W, D.P.kmer_len) <= 0) return false;   // only the warp-specialised kernel counts k-mers
     if(W < 8 || W > THREADS) return false;
     if((reinterpret_cast<uintptr_t>(B.qual) | reinterpret_cast<uintptr_t>(B.bases2)) & 15) return false;
     if(B.total % FQK_BATCH_PAD) return false;
     return fused_tile(W) >= THREADS / W;
 }
 
-static int ws_tile(int W){
+static int ws_tile(int W, int K){
     const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 2048 : 0;
     for(int T = 256; T >= 32; T -= 16)
-        if(ws_smem_bytes(W, T) <= budget) return T;
+        if(ws_smem_bytes(W, T, K) <= budget) return T;
     return 0;
 }
 
@@ -831,14 +907,14 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
                     int variant){
     const int W = (int)(D.L.max_cycles + 3) / 4;
     const int G = THREADS / W;
-    if(variant == 0 && ws_tile(W) > 0){
-        const int T = ws_tile(W);
+    if((variant == 0 || D.P.kmer_len) && ws_tile(W, D.P.kmer_len) > 0){
+        const int T = ws_tile(W, D.P.kmer_len);
         int rpb = (int)((B.n + sms - 1) / sms);
         rpb = std::min(rpb, 60000 * (WS_STATS / W));           // 16-bit level-2 count lanes: < 65536 reads per thread
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
-        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb, M);
+        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, D.P.kmer_len), st>>>(D, B, out, flat, W, T, rpb, M);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     const int T = fused_tile(W);
@@ -852,14 +928,16 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
 
 // paired-end statistics from the records of k_trim_pe: read1 pass, read2 pass and (with -m) the merged tails
 bool ws_stats_supported_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2){
-    return fused_supported_se(D, B1) && fused_supported_se(D, B2) && ws_tile((int)(D.L.max_cycles + 3) / 4) > 0;
+    if(D.P.kmer_len && D.P.merge_enabled) return false;    // k-mers across the junction of a merged read: generic kernel
+    return fused_supported_se(D, B1) && fused_supported_se(D, B2) && ws_tile((int)(D.L.max_cycles + 3) / 4, D.P.kmer_len) > 0;
 }
 
 int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2, const fq_read_result* r1,
                        const fq_read_result* r2, const fq_pair_result* rp, uint64_t* flat, int sms, cudaStream_t st,
                        const uint32_t* maxlen2){
     const int W = (int)(D.L.max_cycles + 3) / 4;
-    const int T = ws_tile(W);
+    const int K = D.P.kmer_len;
+    const int T = ws_tile(W, K);
     int rpb = (int)((B1.n + sms - 1) / sms);
     rpb = std::min(rpb, 60000 * (WS_STATS / W));
     rpb = (rpb + T - 1) / T * T;
@@ -867,9 +945,9 @@ int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B
     const int merge = D.P.merge_enabled;
     const StatsMode M1{1, 0, merge, 0, 2, r1, r2, rp, maxlen2}, M2{1, 1, merge, 1, 3, r2, r1, rp, maxlen2 ? maxlen2 + 1 : nullptr},
                     M3{2, 1, merge, 1, 2, r2, r1, rp, nullptr};
-    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
-    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
     int n = 2;
-    if(merge){ k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
+    if(merge){ k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
     return cudaGetLastError() == cudaSuccess ? n : -1;
 }

@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
                 tl.adapter_reads += 2; tl.adapter_bases += (uint32_t)(t1 + t2);     // filterresult.cpp:159-161
                 modified = true;
             }else{
-                if(P.adapter_r1_len > 0) modified |= dev_trim_by_sequence(a, D.ad1, P.adapter_r1_len, rec1, tl);
-                if(P.adapter_r2_len > 0) modified |= dev_trim_by_sequence(b, D.ad2, P.adapter_r2_len, rec2, tl);
+                if(P.adapter_r1_len > 0) modified |= trim_by_sequence_any(D, a, 0, rec1, tl);
+                if(P.adapter_r2_len > 0) modified |= trim_by_sequence_any(D, b, 1, rec2, tl);
             }
         }
         if(both && P.polyx_enabled){

@@ -89,18 +89,22 @@ __device__ inline void revcomp_packed(const PackedSeq& b, PackedSeq& r){
 }
 
 // mismatches between x[xo + i] and y[yo + i] for i in [from, to) ; from is a multiple of 16
-__device__ __forceinline__ int mism_range(const PackedSeq& x, int xo, const PackedSeq& y, int yo, int from, int to){
+__device__ __forceinline__ int mism_words(const uint32_t* xcw, const uint32_t* xnw, int xo, const uint32_t* ycw, const uint32_t* ynw, int yo,
+                                          int from, int to){
     int d = 0;
     const int xs = 2 * (xo & 15), ys = 2 * (yo & 15);
     for(int i = from; i < to; i += 16){
         const int xw = (xo + i) >> 4, yw = (yo + i) >> 4;
-        const uint32_t xc = __funnelshift_r(x.c[xw], x.c[xw + 1], xs), yc = __funnelshift_r(y.c[yw], y.c[yw + 1], ys);
-        const uint32_t xn = __funnelshift_r(x.n[xw], x.n[xw + 1], xs), yn = __funnelshift_r(y.n[yw], y.n[yw + 1], ys);
+        const uint32_t xc = __funnelshift_r(xcw[xw], xcw[xw + 1], xs), yc = __funnelshift_r(ycw[yw], ycw[yw + 1], ys);
+        const uint32_t xn = __funnelshift_r(xnw[xw], xnw[xw + 1], xs), yn = __funnelshift_r(ynw[yw], ynw[yw + 1], ys);
         const uint32_t t = xc ^ yc;
         const uint32_t mm = (((t | (t >> 1)) & 0x55555555u) | (xn ^ yn)) & valid_mask(to - i);
         d += __popc(mm);
     }
     return d;
+}
+__device__ __forceinline__ int mism_range(const PackedSeq& x, int xo, const PackedSeq& y, int yo, int from, int to){
+    return mism_words(x.c, x.n, xo, y.c, y.n, yo, from, to);
 }
 
 // one alignment: a[ao + i] vs r[ro + i], i < ol.  Returns true (and diff) when the reference accepts it.
@@ -190,4 +194,63 @@ __device__ inline int pass_filter_fast(const fq_params& P, const ReadView& v, bo
     int lowq = 0, nn = 0, total = 0;
     if(P.qual_filter_enabled) swar_counts_global(v.q, v.start, v.len, P.low_quality_limit, lowq, nn, total);
     return filter_from_counts(P, v.len, lowq, nn, total);
+}
+
+// AdapterTrimmer::trimBySequence (src/adaptertrimmer.cpp:29-90) on packed words: the adapter is packed once on the
+// host (DevParams::adc/adn), the read view once per call; every candidate position is one or a few XOR/popcount steps,
+// with a first-word quick reject (the whole-alignment budget is cmplen/8 mismatches).
+__device__ inline bool dev_trim_by_sequence_packed(ReadView& v, const uint32_t* adc, const uint32_t* adn, int alen,
+                                                   fq_read_result& rec, Tally& tl){
+    const int rlen = v.len;
+    if(alen < 4) return false;
+    if(v.start + v.len > 16 * PE_MAXW) return false;                   // caller falls back to the scalar form
+    int start = 0;
+    if(alen >= 16) start = -4; else if(alen >= 12) start = -3; else if(alen >= 8) start = -2;
+    PackedSeq r;
+    pack_view(v, r);
+    int pos; bool found = false;
+    for(pos = start; pos < rlen - 4; ++pos){
+        const int cmplen = min(rlen - pos, alen);
+        const int allowed = cmplen / 8;
+        const int ao = max(0, -pos), ro = max(0, pos), n = cmplen - ao;
+        int d = mism_words(adc, adn, ao, r.c, r.n, ro, 0, min(n, 16));
+        if(d > allowed) continue;
+        if(n > 16) d += mism_words(adc, adn, ao, r.c, r.n, ro, 16, n);
+        if(d <= allowed){ found = true; break; }
+    }
+    if(!found) return false;
+    int textlen;
+    if(pos < 0){ textlen = alen + pos; v.len = 0; }
+    else { textlen = rlen - pos; v.len = pos; }
+    rec.flags |= FQK_F_ADAPTER_SEQ;
+    rec.adapter_pos = (int16_t)pos;
+    rec.adapter_len = (uint16_t)textlen;
+    if(textlen > 0){ tl.adapter_reads += 1; tl.adapter_bases += (uint32_t)textlen; }
+    return true;
+}
+// packed form when the read fits, scalar form otherwise
+__device__ inline bool trim_by_sequence_any(const DevParams& D, ReadView& v, int which, fq_read_result& rec, Tally& tl){
+    const int alen = which ? D.P.adapter_r2_len : D.P.adapter_r1_len;
+    if(v.start + v.len <= 16 * PE_MAXW)
+        return dev_trim_by_sequence_packed(v, which ? D.adc2 : D.adc1, which ? D.adn2 : D.adn1, alen, rec, tl);
+    return dev_trim_by_sequence(v, which ? D.ad2 : D.ad1, alen, rec, tl);
+}
+
+// ------------------------------------------------------------------ SE trim
+// loop body of SingleEndProcessor::processSingleEnd, src/seprocessor.cpp:313-340
+__device__ inline void se_read(const DevParams& D, ReadView& v, fq_read_result& rec, Tally& tl){
+    const fq_params& P = D.P;
+    const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
+    if(alive){
+        if(P.polyg_enabled)
+            dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
+        if(P.adapter_trim_enabled && P.adapter_r1_len > 0)
+            trim_by_sequence_any(D, v, 0, rec, tl);
+        if(P.polyx_enabled)
+            dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
+        if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
+    }
+    rec.result = (uint8_t)pass_filter_fast(P, v, !alive);
+    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
+    else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
 }

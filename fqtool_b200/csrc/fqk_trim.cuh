@@ -10,6 +10,8 @@ struct DevParams {
     fq_params P;
     uint8_t ad1[FQK_MAX_ADAPTER];   // adapter of read1 as base classes (0 A,1 T,2 C,3 G,4 N)
     uint8_t ad2[FQK_MAX_ADAPTER];
+    uint32_t adc1[FQK_MAX_ADAPTER / 16 + 2], adn1[FQK_MAX_ADAPTER / 16 + 2];   // the adapters packed like reads: 2-bit codes, N flags
+    uint32_t adc2[FQK_MAX_ADAPTER / 16 + 2], adn2[FQK_MAX_ADAPTER / 16 + 2];
     fq_stats_layout L;
     uint32_t* err;                  // device error flag: bit0 read longer than max_cycles, bit1 misaligned offset
 };
@@ -294,22 +296,4 @@ __device__ inline void counters_flush(const BlockCounters* bc, const fq_stats_la
     }
 }
 
-// ------------------------------------------------------------------ SE trim
-// loop body of SingleEndProcessor::processSingleEnd, src/seprocessor.cpp:313-340
-__device__ inline void se_read(const DevParams& D, ReadView& v, fq_read_result& rec, Tally& tl){
-    const fq_params& P = D.P;
-    const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
-    if(alive){
-        if(P.polyg_enabled)
-            dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
-        if(P.adapter_trim_enabled && P.adapter_r1_len > 0)
-            dev_trim_by_sequence(v, D.ad1, P.adapter_r1_len, rec, tl);
-        if(P.polyx_enabled)
-            dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
-        if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
-    }
-    rec.result = (uint8_t)dev_pass_filter_view(P, v, !alive);
-    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
-    else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
-}
 
