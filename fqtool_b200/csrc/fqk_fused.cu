@@ -561,6 +561,7 @@ struct StatsMode {
     const uint32_t* maxlen;          // device scalar: longest raw read of this mate's batch (or nullptr)
 };
 
+template <int MODE, bool KMER>
 __global__ void __launch_bounds__(WS_THREADS, 1)
 k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
               uint64_t* __restrict__ flat, int W, int T, int reads_per_block, const StatsMode M){
@@ -576,7 +577,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
     uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 2) + 15) & ~uintptr_t(15));
     // k-mer histograms privatised per block when 3 x 4^k counters fit (k <= 6): common / pre-only / post-only
-    const uint32_t kbins = (P.kmer_len > 0 && P.kmer_len <= KMER_SMEM_MAX) ? (1u << (2 * P.kmer_len)) : 0u;
+    const uint32_t kbins = (KMER && P.kmer_len <= KMER_SMEM_MAX) ? (1u << (2 * P.kmer_len)) : 0u;
     uint32_t* khist = l2base + L2_SLOTS * THREADS;
     uint8_t* sp = reinterpret_cast<uint8_t*>(khist + 3 * kbins);
     // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
@@ -653,13 +654,13 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
                 if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
                 uint32_t hasN = 0;                                    // k-mer validity needs to know whether the raw read holds any N
-                if(P.kmer_len){
+                if(KMER){
                     uint32_t any = 0;
                     const uint32_t qa = smem_u32(S + doff);
                     for(uint32_t c = 0; c < padded; c += 16){ const uint4 v = lds128(qa + c); any |= v.x | v.y | v.z | v.w; }
                     hasN = (any & 0x80808080u) ? 1u : 0u;
                 }
-                if(M.mode == 0){
+                if(MODE == 0){
                     const fq_read_result rec = phase1_read(D, S + doff, S + o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
                     out[t0 + i] = rec;
                     atomicAdd(&bc->filter[rec.result], 1u);
@@ -676,7 +677,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     const fq_read_result ra = M.recA[t0 + i], rb = M.recB[t0 + i];
                     const fq_pair_result pr = M.recP[t0 + i];
                     const bool alive = !(ra.flags & FQK_F_DROPPED) && !(rb.flags & FQK_F_DROPPED);
-                    if(M.mode == 1){
+                    if(MODE == 1){
                         bool own = false; uint32_t start = ra.start, plen = ra.len;
                         if(alive){
                             if(!M.merge_enabled) own = ra.result == FQK_PASS_FILTER && rb.result == FQK_PASS_FILTER;   // :392-401
@@ -718,7 +719,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         // threads per read: enough words for the longest raw read of the batch when it is known
         // (paired-end: max_cycles also has to hold merged reads, twice the raw length)
         int Wr = W;
-        if(M.maxlen && M.mode == 1) Wr = min(W, max(8, (int)((*M.maxlen + 3u) >> 2)));
+        if(M.maxlen && MODE == 1) Wr = min(W, max(8, (int)((*M.maxlen + 3u) >> 2)));
         const int G = WS_STATS / Wr;
         const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
@@ -805,7 +806,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     if(--leftO == 0){ drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w); leftO = 255; }
                 }
                 // ---- k-mer histograms (Stats::statRead, src/stats.cpp:266-274): a separate sweep over the two lists ----
-                if(P.kmer_len){
+                if(KMER){
                     uint64_t* kpre = flat + D.L.stats_off[M.pre_obj] + D.L.s_kmer;
                     uint64_t* kpost = flat + D.L.stats_off[M.post_obj] + D.L.s_kmer;
                     const uint32_t cl = S32 + o_cl;
@@ -842,7 +843,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             if(c + b) add_u64(kpost + i, (uint64_t)c + b);
         }
     }
-    if(M.mode != 2) retire(smPre, C, D.L, flat + D.L.stats_off[M.pre_obj]);
+    if(MODE != 2) retire(smPre, C, D.L, flat + D.L.stats_off[M.pre_obj]);
     retire(smPost, C, D.L, flat + D.L.stats_off[M.post_obj]);
     counters_flush(bc, D.L, flat);
 }
@@ -883,7 +884,11 @@ static int ws_tile(int W, int K = 0);
 void fused_configure(const cudaDeviceProp& prop){
     g_smem_optin = prop.sharedMemPerBlockOptin;
     cudaFuncSetAttribute(k_fused_se, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -914,7 +919,8 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
-        k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, D.P.kmer_len), st>>>(D, B, out, flat, W, T, rpb, M);
+        if(D.P.kmer_len) k_fused_se_ws<0, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, D.P.kmer_len), st>>>(D, B, out, flat, W, T, rpb, M);
+        else k_fused_se_ws<0, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B, out, flat, W, T, rpb, M);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     const int T = fused_tile(W);
@@ -945,9 +951,14 @@ int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B
     const int merge = D.P.merge_enabled;
     const StatsMode M1{1, 0, merge, 0, 2, r1, r2, rp, maxlen2}, M2{1, 1, merge, 1, 3, r2, r1, rp, maxlen2 ? maxlen2 + 1 : nullptr},
                     M3{2, 1, merge, 1, 2, r2, r1, rp, nullptr};
-    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
-    k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+    if(K){
+        k_fused_se_ws<1, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+        k_fused_se_ws<1, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+    }else{
+        k_fused_se_ws<1, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+        k_fused_se_ws<1, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+    }
     int n = 2;
-    if(merge){ k_fused_se_ws<<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
+    if(merge){ k_fused_se_ws<2, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
     return cudaGetLastError() == cudaSuccess ? n : -1;
 }
