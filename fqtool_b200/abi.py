@@ -92,7 +92,7 @@ assert READ_RESULT_DTYPE.itemsize == 16 and PAIR_RESULT_DTYPE.itemsize == 24
 
 EXPORTS = [
     "fqk_default_params", "fqk_stats_layout", "fqk_create", "fqk_destroy", "fqk_last_error",
-    "fqk_nccl_unique_id", "fqk_process_se", "fqk_process_pe", "fqk_process_se_device",
+    "fqk_nccl_unique_id", "fqk_process_se", "fqk_process_pe", "fqk_submit_se", "fqk_wait", "fqk_process_se_device",
     "fqk_process_pe_device", "fqk_sync", "fqk_stream", "fqk_launch_count",
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
@@ -121,6 +121,8 @@ def load():
     lib.fqk_nccl_unique_id.argtypes = [vp]; lib.fqk_nccl_unique_id.restype = i32
     lib.fqk_process_se.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se.restype = i32
     lib.fqk_process_pe.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp]; lib.fqk_process_pe.restype = i32
+    lib.fqk_submit_se.argtypes = [vp, P(FqBatch), vp, P(u64)]; lib.fqk_submit_se.restype = i32
+    lib.fqk_wait.argtypes = [vp, u64]; lib.fqk_wait.restype = i32
     lib.fqk_process_se_device.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se_device.restype = i32
     lib.fqk_process_pe_device.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp]
     lib.fqk_process_pe_device.restype = i32

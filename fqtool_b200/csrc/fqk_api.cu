@@ -67,6 +67,12 @@ struct fqk_ctx {
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
     StagedBatch st[2];
     DevBuf res1, res2, resp;
+    // pipelined single-end path (fqk_submit_se / fqk_wait): two slots, copies on their own streams
+    cudaStream_t h2d = nullptr, d2h = nullptr;
+    StagedBatch pst[2]; DevBuf pres[2];
+    cudaEvent_t evH2D[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr}, evD2H[2] = {nullptr, nullptr};
+    uint32_t* perr_host = nullptr;            // pinned: error flag snapshot of each slot
+    uint64_t submitted = 0;
     nccl::Comm comm = nullptr;
     uint64_t launches = 0;
     int impl = 0;
@@ -262,6 +268,15 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     if(c->comm) nccl::CommDestroy(c->comm);
     for(auto& e : c->evs){ cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for(auto& e : c->evpool) cudaEventDestroy(e);
+    for(int i = 0; i < 2; ++i){
+        c->pst[i].off.release(); c->pst[i].len.release(); c->pst[i].b2.release(); c->pst[i].q.release(); c->pres[i].release();
+        if(c->evH2D[i]) cudaEventDestroy(c->evH2D[i]);
+        if(c->evK[i]) cudaEventDestroy(c->evK[i]);
+        if(c->evD2H[i]) cudaEventDestroy(c->evD2H[i]);
+    }
+    if(c->h2d) cudaStreamDestroy(c->h2d);
+    if(c->d2h) cudaStreamDestroy(c->d2h);
+    if(c->perr_host) cudaFreeHost(c->perr_host);
     for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
     c->res1.release(); c->res2.release(); c->resp.release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
@@ -390,15 +405,16 @@ extern "C" int fqk_process_pe_device(fqk_ctx* c, const fq_batch* r1, const fq_ba
 }
 
 // host batch -> device staging (4 H2D copies on the context's stream)
-static int stage(fqk_ctx* c, StagedBatch& s, const fq_batch* b){
+static int stage(fqk_ctx* c, StagedBatch& s, const fq_batch* b, cudaStream_t st = nullptr){
+    if(!st) st = c->stream;
     const size_t n = b->n_reads;
     if(b->total_bases % FQK_BATCH_PAD) return fail(c, FQK_E_INVALID, "total_bases must be a multiple of FQK_BATCH_PAD");
     if(s.off.ensure(n * 4 + 16) || s.len.ensure(n * 2 + 16) || s.b2.ensure(b->total_bases / 4 + 16) || s.q.ensure(b->total_bases + 16))
         return fail(c, FQK_E_NOMEM, "device staging allocation failed");
-    CU(cudaMemcpyAsync(s.off.p, b->offsets, n * 4, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(s.len.p, b->lengths, n * 2, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(s.b2.p, b->bases2, b->total_bases / 4, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(s.q.p, b->qual, b->total_bases, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.off.p, b->offsets, n * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.len.p, b->lengths, n * 2, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.b2.p, b->bases2, b->total_bases / 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.q.p, b->qual, b->total_bases, cudaMemcpyHostToDevice, st));
     s.dev.n = b->n_reads; s.dev.first_index = b->first_index; s.dev.total = b->total_bases;
     s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
     s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
@@ -416,6 +432,54 @@ extern "C" int fqk_process_se(fqk_ctx* c, const fq_batch* in, fq_read_result* ou
     rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
     CU(cudaMemcpyAsync(out, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
     return check_err_flag(c);
+}
+
+// Pipelined form of fqk_process_se: the upload of pack k+1 overlaps the kernels and the download of pack k
+// (PCIe is full duplex).  At most two packs are in flight; buffers of a pack must stay valid until fqk_wait.
+extern "C" int fqk_submit_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out, uint64_t* ticket){
+    if(!c || !in || !ticket || (!out && in->n_reads)) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    CU(cudaSetDevice(c->device));
+    if(!c->h2d){
+        CU(cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+        for(int i = 0; i < 2; ++i){
+            CU(cudaEventCreateWithFlags(&c->evH2D[i], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&c->evK[i], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&c->evD2H[i], cudaEventDisableTiming));
+        }
+        CU(cudaHostAlloc((void**)&c->perr_host, 2 * sizeof(uint32_t), cudaHostAllocDefault));
+        c->perr_host[0] = c->perr_host[1] = 0;
+    }
+    const int s = (int)(c->submitted & 1);
+    *ticket = c->submitted++;
+    const size_t n = in->n_reads;
+    if(n == 0){ CU(cudaEventRecord(c->evD2H[s], c->d2h)); return 0; }
+    if(c->submitted > 2) CU(cudaEventSynchronize(c->evD2H[s]));        // the slot's previous pack has left the device
+    if(c->pres[s].ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    CU(cudaStreamWaitEvent(c->h2d, c->evK[s], 0));                      // staging of this slot is free again
+    int rc = stage(c, c->pst[s], in, c->h2d); if(rc) return rc;
+    CU(cudaEventRecord(c->evH2D[s], c->h2d));
+    CU(cudaStreamWaitEvent(c->stream, c->evH2D[s], 0));
+    rc = launch_se(c, c->pst[s].dev, (fq_read_result*)c->pres[s].p); if(rc) return rc;
+    CU(cudaEventRecord(c->evK[s], c->stream));
+    CU(cudaStreamWaitEvent(c->d2h, c->evK[s], 0));
+    CU(cudaMemcpyAsync(out, c->pres[s].p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaEventRecord(c->evD2H[s], c->d2h));
+    return 0;
+}
+
+extern "C" int fqk_wait(fqk_ctx* c, uint64_t ticket){
+    if(!c || ticket >= c->submitted) return FQK_E_INVALID;
+    if(ticket + 2 < c->submitted) return 0;                             // already recycled, hence complete
+    CU(cudaSetDevice(c->device));
+    const int s = (int)(ticket & 1);
+    CU(cudaEventSynchronize(c->evD2H[s]));
+    const uint32_t e = c->perr_host[s];
+    if(e & 1) return fail(c, FQK_E_LIMIT, "a read (or merged read) is longer than max_cycles");
+    if(e & 2) return fail(c, FQK_E_INVALID, "batch is not dense/ordered/16-byte aligned (see fq_batch)");
+    return 0;
 }
 
 extern "C" int fqk_process_pe(fqk_ctx* c, const fq_batch* r1, const fq_batch* r2, fq_read_result* o1,

@@ -60,6 +60,16 @@ class Engine:
         self._check(self.lib.fqk_process_se(self.h, C.byref(b), abi.ptr(out)), "fqk_process_se")
         return out
 
+    def submit_se(self, batch, out):
+        """Pipelined fqk_process_se: returns a ticket; `batch` and `out` must stay alive until wait(ticket)."""
+        b = batch.c_struct()
+        t = C.c_uint64(0)
+        self._check(self.lib.fqk_submit_se(self.h, C.byref(b), abi.ptr(out), C.byref(t)), "fqk_submit_se")
+        return t.value
+
+    def wait(self, ticket):
+        self._check(self.lib.fqk_wait(self.h, ticket), "fqk_wait")
+
     def process_pe(self, batch1, batch2, out=None):
         n = batch1.n
         if out is None:

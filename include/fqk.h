@@ -231,6 +231,16 @@ int  fqk_process_pe(fqk_ctx* ctx, const fq_batch* r1, const fq_batch* r2,
                     fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp);
 
 /*
+ * Pipelined form of fqk_process_se for hosts that keep two packs in flight: fqk_submit_se enqueues
+ * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's
+ * records are in `out`.  The upload of pack k+1 overlaps the kernels and the download of pack k.
+ * Buffers of a pack (pinned host memory) must stay valid until its fqk_wait returns.  Do not mix
+ * with fqk_process_se on the same context without waiting for every ticket first.
+ */
+int  fqk_submit_se(fqk_ctx* ctx, const fq_batch* in, fq_read_result* out, uint64_t* ticket);
+int  fqk_wait(fqk_ctx* ctx, uint64_t ticket);
+
+/*
  * Device-resident entry points (all pointers are device pointers of the
  * context's GPU, fq_batch itself is a host struct): kernels only, launched on
  * the context's stream without synchronising.  fqk_sync waits for them.

@@ -52,3 +52,26 @@ def test_read_longer_than_max_cycles_is_an_error():
     opt = configs.options("cfg2", max_cycles=64)
     with pytest.raises(FqkError):
         util.run_cuda(opt, synth.se_hiseq(10, 100, seed=1))
+
+
+def test_pipelined_submit_wait_matches_sync():
+    """fqk_submit_se / fqk_wait (two packs in flight) give the same records and accumulators as fqk_process_se."""
+    from fqtool_b200 import abi, batch
+    from fqtool_b200.engine import Engine
+    opt = configs.options("cfg2", max_cycles=256)
+    reads = synth.ragged(9000, seed=77)
+    want = util.run_cuda(opt, reads, chunks=6)
+    e = Engine(opt.to_params())
+    bounds = np.linspace(0, 9000, 7).astype(int)
+    packs = [batch.pack(batch.slice_reads(reads, lo, hi), int(lo)) for lo, hi in zip(bounds[:-1], bounds[1:])]
+    outs = [np.zeros(p.n, dtype=abi.READ_RESULT_DTYPE) for p in packs]
+    pending = None
+    for p, o in zip(packs, outs):
+        t = e.submit_se(p, o)
+        if pending is not None:
+            e.wait(pending)
+        pending = t
+    e.wait(pending)
+    got = (np.concatenate(outs),), e.finalize(), None
+    util.assert_same(got, want)
+    e.close()
