@@ -75,7 +75,8 @@ class FqStatsLayout(C.Structure):
             "stats_stride", "s_q20", "s_q30", "s_content", "s_qualsum", "s_total_base",
             "s_total_qual", "s_reads", "s_length_sum", "s_kmer", "filter_off",
             "adapter_reads_off", "adapter_bases_off", "polyx_reads_off", "polyx_bases_off",
-            "merged_pairs_off", "insert_hist_off", "insert_hist_len", "dup_bins")]
+            "merged_pairs_off", "insert_hist_off", "insert_hist_len", "dup_bins", "correction_off",
+            "corrected_reads_off")]
 
 
 # numpy views of the result records (same memory layout as the C structs)
@@ -88,13 +89,14 @@ PAIR_RESULT_DTYPE = np.dtype([
     ("ov2_offset", "<i2"), ("ov2_len", "<u2"), ("ov2_diff", "<u2"),
     ("merge_len1", "<u2"), ("merge_len2", "<u2"),
     ("flags", "u1"), ("merged_result", "u1"), ("insert_size", "<u2"), ("reserved", "<u4")])
-assert READ_RESULT_DTYPE.itemsize == 16 and PAIR_RESULT_DTYPE.itemsize == 24
+CORRECTION_DTYPE = np.dtype([("pair", "<u4"), ("pos", "<u2"), ("mate_base", "u1"), ("qual", "u1")])
+assert READ_RESULT_DTYPE.itemsize == 16 and PAIR_RESULT_DTYPE.itemsize == 24 and CORRECTION_DTYPE.itemsize == 8
 
 EXPORTS = [
     "fqk_default_params", "fqk_stats_layout", "fqk_create", "fqk_destroy", "fqk_last_error",
     "fqk_nccl_unique_id", "fqk_process_se", "fqk_process_pe", "fqk_submit_se", "fqk_wait", "fqk_process_se_device",
     "fqk_process_pe_device", "fqk_sync", "fqk_stream", "fqk_launch_count",
-    "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_reset", "fqk_finalize",
+    "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
 ]
 
@@ -132,6 +134,7 @@ def load():
     lib.fqk_set_kernel_timing.argtypes = [vp, i32]; lib.fqk_set_kernel_timing.restype = i32
     lib.fqk_kernel_times.argtypes = [vp, P(C.c_double), P(u64)]; lib.fqk_kernel_times.restype = i32
     lib.fqk_set_impl.argtypes = [vp, i32]; lib.fqk_set_impl.restype = i32
+    lib.fqk_get_corrections.argtypes = [vp, vp, u32, P(u32)]; lib.fqk_get_corrections.restype = i32
     lib.fqk_reset.argtypes = [vp]; lib.fqk_reset.restype = i32
     lib.fqk_finalize.argtypes = [vp, vp]; lib.fqk_finalize.restype = i32
     lib.fqk_dup_table.argtypes = [vp, vp, vp, vp]; lib.fqk_dup_table.restype = i32

@@ -62,7 +62,8 @@ struct fqk_ctx {
     cudaStream_t stream = nullptr;
     uint64_t* flat = nullptr;                 // device accumulators (fq_stats_layout)
     uint32_t* err = nullptr;                  // device error flag
-    uint32_t* maxlen2 = nullptr;              // device: longest raw read of each mate in the current PE batch
+    uint32_t* maxlen2 = nullptr;              // device: [0..1] longest raw read of each mate, [2] number of corrections
+    DevBuf corr; uint32_t corr_cap = 0;       // device list of fq_correction of the current PE batch
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
     StagedBatch st[2];
@@ -144,6 +145,8 @@ extern "C" int fqk_stats_layout(const fq_params* p, fq_stats_layout* L){
     L->polyx_reads_off = o; o += 5; L->polyx_bases_off = o; o += 5;
     L->merged_pairs_off = o++;
     L->insert_hist_off = o; L->insert_hist_len = (uint64_t)p->insert_size_max + 1; o += L->insert_hist_len;
+    L->correction_off = o; o += 64;
+    L->corrected_reads_off = o; o += 1;
     L->total_u64 = o;
     L->dup_bins = p->dup_enabled ? (1ull << (2 * p->dup_keylen)) : 0;
     return 0;
@@ -155,7 +158,6 @@ static int cls_of_char(char ch){
 
 static int validate_params(const fq_params* p, std::string& why){
     if(p->abi_version != FQK_ABI_VERSION){ why = "abi_version mismatch"; return FQK_E_INVALID; }
-    if(p->correction_enabled){ why = "PE base correction (-c) is not on the hot path yet"; return FQK_E_INVALID; }
     if((p->cut_front_enabled && p->cut_front_window < 1) || (p->cut_tail_enabled && p->cut_tail_window < 1) ||
        (p->cut_right_enabled && p->cut_right_window < 1)){ why = "cut window must be >= 1"; return FQK_E_INVALID; }
     if(p->polyg_enabled && (p->polyg_one_mismatch_each < 1 || (p->is_paired && p->polyg_min_len < 1))){ why = "polyG one_mismatch_each must be >= 1"; return FQK_E_INVALID; }
@@ -179,6 +181,23 @@ extern "C" int fqk_nccl_unique_id(void* out128){
     nccl::UniqueId id;
     if(nccl::GetUniqueId(&id) != 0) return FQK_E_NCCL;
     memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+extern "C" int fqk_get_corrections(fqk_ctx* c, fq_correction* out, uint32_t cap, uint32_t* n){
+    if(!c || !n) return FQK_E_INVALID;
+    *n = 0;
+    if(!c->D.P.correction_enabled || !c->corr.p) return 0;
+    CU(cudaSetDevice(c->device));
+    uint32_t cnt = 0;
+    CU(cudaMemcpyAsync(&cnt, c->maxlen2 + 2, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *n = cnt;
+    const uint32_t m = cnt < cap ? cnt : cap;
+    if(out && m){
+        CU(cudaMemcpyAsync(out, c->corr.p, (size_t)m * sizeof(fq_correction), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
     return 0;
 }
 
@@ -234,7 +253,7 @@ extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal,
     if(cudaMalloc(&c->flat, c->D.L.total_u64 * sizeof(uint64_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "accumulator alloc failed");
     if(cudaMalloc(&c->err, sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "flag alloc failed");
     c->D.err = c->err;
-    if(cudaMalloc(&c->maxlen2, 2 * sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "scalar alloc failed");
+    if(cudaMalloc(&c->maxlen2, 4 * sizeof(uint32_t)) != cudaSuccess) return bail(FQK_E_NOMEM, "scalar alloc failed");
     if(c->D.L.dup_bins){
         const uint64_t n = c->D.L.dup_bins;
         if(cudaMalloc(&c->tab128, n * 16) != cudaSuccess || cudaMalloc(&c->first64, n * 8) != cudaSuccess ||
@@ -278,7 +297,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     if(c->d2h) cudaStreamDestroy(c->d2h);
     if(c->perr_host) cudaFreeHost(c->perr_host);
     for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
-    c->res1.release(); c->res2.release(); c->resp.release();
+    c->res1.release(); c->res2.release(); c->resp.release(); c->corr.release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
     if(c->stream) cudaStreamDestroy(c->stream);
@@ -349,24 +368,36 @@ static int launch_pe(fqk_ctx* c, const DevBatch& B1, const DevBatch& B2, fq_read
                      fq_pair_result* op){
     if(B1.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
+    const bool correct = c->D.P.correction_enabled != 0;
+    const int Cs = c->stats_cs_pe;
+    // everything that reads the RAW pair runs before k_trim_pe when -c corrects the batch in place
+    if(c->D.P.dup_enabled){
+        Timer t(c, FQK_T_DUP);
+        k_dup<<<grid_for(c, B1.n, 256, 8), 256, 0, c->stream>>>(c->D, B1, B2, 1, c->tab128, c->first64); c->launches++;
+        c->dup_final = false;
+    }
+    if(correct){
+        if(c->corr.ensure((size_t)5 * B1.n * sizeof(fq_correction) + 16)) return fail(c, FQK_E_NOMEM, "correction list allocation failed");
+        c->corr_cap = 5u * B1.n;
+        Timer t(c, FQK_T_STATS);
+        k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs, 1);
+        c->launches++;
+    }
     { Timer t(c, FQK_T_TRIM);
-      cudaMemsetAsync(c->maxlen2, 0, 2 * sizeof(uint32_t), c->stream);
-      k_trim_pe<<<grid_for(c, B1.n, 128, 8), 128, 0, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, c->maxlen2); c->launches++; }
-    if(c->impl != 1 && ws_stats_supported_pe(c->D, B1, B2)){
+      cudaMemsetAsync(c->maxlen2, 0, 3 * sizeof(uint32_t), c->stream);       // [0..1] longest raw reads, [2] corrections
+      k_trim_pe<<<grid_for(c, B1.n, 128, 8), 128, 0, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, c->maxlen2,
+                                                                  correct ? (fq_correction*)c->corr.p : nullptr, c->maxlen2 + 2, c->corr_cap);
+      c->launches++; }
+    if(!correct && c->impl != 1 && ws_stats_supported_pe(c->D, B1, B2)){
         Timer t(c, FQK_T_FUSED);
         int nl = ws_stats_launch_pe(c->D, B1, B2, o1, o2, op, c->flat, c->sms, c->stream, c->maxlen2);
         if(nl < 0) return fail(c, FQK_E_CUDA, "PE statistics launch failed");
         c->launches += nl;
     }else{
         Timer t(c, FQK_T_STATS);
-        const int Cs = c->stats_cs_pe;
-        k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs);
+        k_stats_pe<<<grid_for(c, B1.n, 8, Cs ? 1 : 4), 256, (size_t)4 * 20 * Cs * 4, c->stream>>>(c->D, B1, B2, o1, o2, op, c->flat, Cs,
+                                                                                                  correct ? 2 : 3);
         c->launches++;
-    }
-    if(c->D.P.dup_enabled){
-        Timer t(c, FQK_T_DUP);
-        k_dup<<<grid_for(c, B1.n, 256, 8), 256, 0, c->stream>>>(c->D, B1, B2, 1, c->tab128, c->first64); c->launches++;
-        c->dup_final = false;
     }
     CU(cudaGetLastError());
     return 0;

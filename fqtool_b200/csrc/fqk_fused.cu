@@ -935,6 +935,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
 // paired-end statistics from the records of k_trim_pe: read1 pass, read2 pass and (with -m) the merged tails
 bool ws_stats_supported_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2){
     if(D.P.kmer_len && D.P.merge_enabled) return false;    // k-mers across the junction of a merged read: generic kernel
+    if(D.P.correction_enabled) return false;               // -c: pre statistics must see the batch before it is corrected
     return fused_supported_se(D, B1) && fused_supported_se(D, B2) && ws_tile((int)(D.L.max_cycles + 3) / 4, D.P.kmer_len) > 0;
 }
 

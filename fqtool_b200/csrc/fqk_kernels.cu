@@ -42,6 +42,49 @@ struct MergedGet {
     }
 };
 
+// in-place edits of the packed batch (a thread owns its pair; a base byte never spans two reads)
+__device__ __forceinline__ void write_base_qual(const ReadView& v, int pos, int cls, int q){
+    uint8_t* qp = const_cast<uint8_t*>(v.q) + v.start + pos;
+    *qp = (uint8_t)((q & 0x7F) | (cls == CLS_N ? 0x80 : 0));
+    const int p = v.start + pos;
+    uint8_t* bp = const_cast<uint8_t*>(v.b2) + (p >> 2);
+    const int sh = (p & 3) * 2;
+    *bp = (uint8_t)((*bp & ~(3 << sh)) | ((cls == CLS_N ? 0 : cls) << sh));
+}
+
+// BaseCorrector::correctByOverlapAnalysis, src/basecorrector.cpp:14-70: inside the overlap a mismatching base
+// with quality <= 14 is overwritten by the complement of its partner when that one has quality >= 30.
+// The batch is corrected in place (the reference mutates its Reads); every edit is appended to `corr` for the host.
+// addCorrection(from, to) runs after the overwrite through the same buffer (:40-45, :47-52), so from == to.
+__device__ inline bool dev_correct(const DevParams& D, const ReadView& a, const ReadView& b, const OvRes& ov, uint32_t pair,
+                                   fq_correction* corr, uint32_t* ncorr, uint32_t cap, uint64_t* flat){
+    if(ov.diff == 0 || ov.diff > 5) return false;
+    const int start1 = max(0, ov.offset), start2 = b.len - max(0, -ov.offset) - 1;
+    int corrected = 0; bool r1c = false, r2c = false;
+    for(int i = 0; i < ov.len; ++i){
+        const int p1 = start1 + i, p2 = start2 - i;
+        const int c1 = a.cls(p1), c2 = b.cls(p2);
+        const int k1 = c1 == CLS_N ? CLS_N : (c1 ^ 1), k2 = c2 == CLS_N ? CLS_N : (c2 ^ 1);   // complements
+        if(c1 == k2) continue;
+        const int q1 = a.qual(p1), q2 = b.qual(p2);
+        int mate, pos, ncls, nq;
+        if(q1 >= 63 && q2 <= 47){ mate = 1; pos = p2; ncls = k1; nq = q1; r2c = true; write_base_qual(b, p2, ncls, nq); }
+        else if(q2 >= 63 && q1 <= 47){ mate = 0; pos = p1; ncls = k2; nq = q2; r1c = true; write_base_qual(a, p1, ncls, nq); }
+        else continue;
+        ++corrected;
+        const int bin = cls_to_bin(ncls);
+        add_u64(flat + D.L.correction_off + bin * 8 + bin, 1);
+        const uint32_t slot = atomicAdd(ncorr, 1u);
+        if(slot < cap){
+            fq_correction e; e.pair = pair; e.pos = (uint16_t)((mate ? b.start : a.start) + pos);
+            e.mate_base = (uint8_t)((mate << 7) | "ATCGN"[ncls]); e.qual = (uint8_t)nq;
+            corr[slot] = e;
+        }
+    }
+    if(corrected) add_u64(flat + D.L.corrected_reads_off, (r1c && r2c) ? 2 : 1);
+    return corrected > 0;
+}
+
 // OverlapAnalysis::analyze: bit-parallel on packed words when both reads fit, else the scalar closed form
 __device__ inline OvRes analyze_pair(const ReadView& a, const ReadView& b, int limit, int require){
     if(a.start + a.len > 16 * PE_MAXW || b.start + b.len > 16 * PE_MAXW) return dev_analyze(a, b, limit, require);
@@ -53,7 +96,8 @@ __device__ inline OvRes analyze_pair(const ReadView& a, const ReadView& b, int l
 __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                                                   fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
                                                   fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
-                                                  uint32_t* __restrict__ maxlen2){
+                                                  uint32_t* __restrict__ maxlen2, fq_correction* __restrict__ corr,
+                                                  uint32_t* __restrict__ ncorr, uint32_t corr_cap){
     __shared__ BlockCounters bc;
     __shared__ uint32_t smax[2];
     counters_zero(&bc);
@@ -89,6 +133,8 @@ __global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevPara
             add_u64(flat + D.L.insert_hist_off + isize, 1);
         }
         bool modified = false;                            // reads changed since the first analyze()
+        if(both && P.correction_enabled && corr)          // :310-312, before adapter trimming
+            modified |= dev_correct(D, a, b, ov, r, corr, ncorr, corr_cap, flat);
         if(both && P.adapter_trim_enabled){
             // AdapterTrimmer::trimByOverlapAnalysis, src/adaptertrimmer.cpp:14-27
             if(ov.diff <= 5 && ov.overlapped && ov.offset < 0 && ov.len > a.len / 3){
@@ -307,7 +353,7 @@ __global__ void __launch_bounds__(256) k_stats_pe(const __grid_constant__ DevPar
                                                    const fq_read_result* __restrict__ res1,
                                                    const fq_read_result* __restrict__ res2,
                                                    const fq_pair_result* __restrict__ resp,
-                                                   uint64_t* __restrict__ flat, int Cs){
+                                                   uint64_t* __restrict__ flat, int Cs, int phase){
     extern __shared__ uint32_t sm[];
     __shared__ unsigned long long cnt[8];
     StatsAcc A{Cs ? sm : nullptr, flat, Cs, &D.L, D.err, 0, cnt};
@@ -319,8 +365,11 @@ __global__ void __launch_bounds__(256) k_stats_pe(const __grid_constant__ DevPar
     const bool merge = D.P.merge_enabled;
     for(uint32_t r = blockIdx.x * warps + w; r < B1.n; r += gridDim.x * warps){
         ReadView a = make_view(B1, r), b = make_view(B2, r);
-        stat_stream(A, 0, a.len, k, ViewGet{a});
-        stat_stream(A, 1, b.len, k, ViewGet{b});
+        if(phase & 1){                                                // pre: raw reads (before -c corrects the batch in place)
+            stat_stream(A, 0, a.len, k, ViewGet{a});
+            stat_stream(A, 1, b.len, k, ViewGet{b});
+        }
+        if(!(phase & 2)) continue;
         const fq_read_result r1 = res1[r], r2 = res2[r];
         const fq_pair_result pr = resp[r];
         const bool alive = !(r1.flags & FQK_F_DROPPED) && !(r2.flags & FQK_F_DROPPED);

@@ -6,12 +6,13 @@ __global__ void k_trim_se(const __grid_constant__ DevParams D, DevBatch B,
                           fq_read_result* __restrict__ out, uint64_t* __restrict__ flat);
 __global__ void k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                           fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
-                          fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat, uint32_t* __restrict__ maxlen2);
+                          fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat, uint32_t* __restrict__ maxlen2,
+                          fq_correction* __restrict__ corr, uint32_t* __restrict__ ncorr, uint32_t corr_cap);
 __global__ void k_stats_se(const __grid_constant__ DevParams D, DevBatch B,
                            const fq_read_result* __restrict__ res, uint64_t* __restrict__ flat, int Cs);
 __global__ void k_stats_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                            const fq_read_result* __restrict__ res1, const fq_read_result* __restrict__ res2,
-                           const fq_pair_result* __restrict__ resp, uint64_t* __restrict__ flat, int Cs);
+                           const fq_pair_result* __restrict__ resp, uint64_t* __restrict__ flat, int Cs, int phase);
 __global__ void k_dup(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, int paired,
                       unsigned long long* tab128, unsigned long long* first64);
 __global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, const unsigned long long* first64,

@@ -88,6 +88,15 @@ class Engine:
         self._check(self.lib.fqk_process_pe_device(self.h, C.byref(dev_batch1), C.byref(dev_batch2), out1_ptr, out2_ptr,
                                                    outp_ptr), "fqk_process_pe_device")
 
+    def corrections(self):
+        """Bases rewritten by -c in the last process_pe call, sorted (pair, mate, pos)."""
+        n = C.c_uint32(0)
+        self._check(self.lib.fqk_get_corrections(self.h, None, 0, C.byref(n)), "fqk_get_corrections")
+        out = np.zeros(n.value, dtype=abi.CORRECTION_DTYPE)
+        if n.value:
+            self._check(self.lib.fqk_get_corrections(self.h, abi.ptr(out), n.value, C.byref(n)), "fqk_get_corrections")
+        return np.sort(out, order=["pair", "mate_base", "pos"])
+
     def sync(self):
         self._check(self.lib.fqk_sync(self.h), "fqk_sync")
 

@@ -141,6 +141,16 @@ void HotPath::processPairEnd(std::vector<Read>& p1, std::vector<Read>& p2, PEOut
     if(fqk_process_pe(mCtx, &b1, &b2, mBuf[0]->results, mBuf[1]->results, mPairRes.data()) != FQK_OK)
         throw std::runtime_error(std::string("fqk_process_pe: ") + fqk_last_error(mCtx));
     mFirstIndex += p1.size();
+    if(mParams.correction_enabled){                                                  // BaseCorrector edits (src/peprocessor.cpp:310-312)
+        uint32_t n = 0;
+        if(fqk_get_corrections(mCtx, nullptr, 0, &n) != FQK_OK) throw std::runtime_error(std::string("fqk_get_corrections: ") + fqk_last_error(mCtx));
+        std::vector<fq_correction> ed(n);
+        if(n && fqk_get_corrections(mCtx, ed.data(), n, &n) != FQK_OK) throw std::runtime_error(std::string("fqk_get_corrections: ") + fqk_last_error(mCtx));
+        for(const fq_correction& e : ed){
+            Read& r = (e.mate_base & 0x80) ? p2[e.pair] : p1[e.pair];
+            r.seq[e.pos] = (char)(e.mate_base & 0x7F); r.quality[e.pos] = (char)e.qual;
+        }
+    }
     const int PASS = FQK_PASS_FILTER;
     for(size_t i = 0; i < p1.size(); ++i){
         Read& or1 = p1[i]; Read& or2 = p2[i];

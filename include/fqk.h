@@ -87,7 +87,7 @@ typedef struct fq_params {
     char    adapter_r2[FQK_MAX_ADAPTER];
     /* Options::overlapRequire / overlapDiffLimit / insertSizeMax options.cpp:17-19 */
     int32_t overlap_require, overlap_diff_limit, insert_size_max;
-    /* CorrectionOptions: must be 0 (PE base correction is a section-8f "next" row) */
+    /* CorrectionOptions options.h:163-169: PE base correction by overlap analysis (-c) */
     int32_t correction_enabled;
     /* MergePEReadsOptions options.h:27-36 */
     int32_t merge_enabled, merge_discard_unmerged;
@@ -199,7 +199,20 @@ typedef struct fq_stats_layout {
     uint64_t insert_hist_off;      /* mInsertSizeHist[insert_size_max+1]        */
     uint64_t insert_hist_len;
     uint64_t dup_bins;             /* 4^keylen or 0 (table is returned apart)   */
+    uint64_t correction_off;       /* mCorrectionMatrix[64] filterresult.h      */
+    uint64_t corrected_reads_off;  /* mCorrectedReads                           */
 } fq_stats_layout;
+
+/*
+ * fq_correction: one base rewritten by BaseCorrector::correctByOverlapAnalysis
+ * (src/basecorrector.cpp:14-70).  The host applies it to its own strings before slicing.
+ */
+typedef struct fq_correction {
+    uint32_t pair;        /* index of the pair inside the batch                         */
+    uint16_t pos;         /* position in the ORIGINAL (untrimmed) read                  */
+    uint8_t  mate_base;   /* bit 7: 0 = read1, 1 = read2; bits 0-6: new base (ASCII)    */
+    uint8_t  qual;        /* new quality character                                      */
+} fq_correction;
 
 typedef struct fqk_ctx fqk_ctx;
 
@@ -268,6 +281,10 @@ int  fqk_kernel_times(fqk_ctx* ctx, double ms[FQK_T_SLOTS], uint64_t launches[FQ
 /* implementation selector for A/B tests: 0 = automatic (fused kernel when the
  * configuration allows), 1 = generic kernels only, 2 = single-role fused kernel */
 int  fqk_set_impl(fqk_ctx* ctx, int impl);
+
+/* corrections made by the last fqk_process_pe / fqk_process_pe_device call (synchronises);
+ * *n receives the total, at most cap entries are written (unordered) */
+int  fqk_get_corrections(fqk_ctx* ctx, fq_correction* out, uint32_t cap, uint32_t* n);
 
 /* zero every accumulator (Stats, FilterResult counters, insert histogram, dup table) */
 int  fqk_reset(fqk_ctx* ctx);

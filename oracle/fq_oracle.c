@@ -19,6 +19,8 @@ struct fqo_ctx {
     uint64_t* flat;
     uint64_t* dups; uint32_t* counts; uint8_t* gc;   /* src/duplicate.h:64-66 */
     char* tmp; int tmp_cap;                          /* revcomp scratch       */
+    char* cbuf; size_t cbuf_cap;                     /* mutable copy of a pair (base correction) */
+    fq_correction* corr; uint32_t ncorr, corr_cap;   /* edits of the last process_pe call */
 };
 
 /* ------------------------------------------------------------------ layout */
@@ -40,6 +42,8 @@ int fqo_layout(const fq_params* p, fq_stats_layout* L){
     L->polyx_bases_off = o;   o += 5;
     L->merged_pairs_off = o;  o += 1;
     L->insert_hist_off = o;   L->insert_hist_len = (uint64_t)p->insert_size_max + 1; o += L->insert_hist_len;
+    L->correction_off = o; o += 64;
+    L->corrected_reads_off = o; o += 1;
     L->total_u64 = o;
     L->dup_bins = p->dup_enabled ? (1ull << (2 * p->dup_keylen)) : 0;
     return 0;
@@ -63,7 +67,7 @@ fqo_ctx* fqo_create(const fq_params* p){
 
 void fqo_destroy(fqo_ctx* c){
     if(!c) return;
-    free(c->flat); free(c->dups); free(c->counts); free(c->gc); free(c->tmp); free(c);
+    free(c->flat); free(c->dups); free(c->counts); free(c->gc); free(c->tmp); free(c->cbuf); free(c->corr); free(c);
 }
 
 static inline int imin(int a, int b){ return a < b ? a : b; }
@@ -495,6 +499,57 @@ int fqo_process_se(fqo_ctx* c, uint32_t n, uint64_t first_index,
     return 0;
 }
 
+/* ------------------------------------------------------------ BaseCorrector */
+/* util::complement, src/util.h:438-451 */
+static char complement(char b){
+    switch(b){ case 'A': case 'a': return 'T'; case 'T': case 't': return 'A';
+               case 'C': case 'c': return 'G'; case 'G': case 'g': return 'C'; default: return 'N'; }
+}
+static void push_corr(fqo_ctx* c, uint32_t pair, int pos, int mate, char base, char qual){
+    if(c->ncorr == c->corr_cap){
+        c->corr_cap = c->corr_cap ? c->corr_cap * 2 : 1024;
+        c->corr = (fq_correction*)realloc(c->corr, c->corr_cap * sizeof(fq_correction));
+    }
+    fq_correction e; e.pair = pair; e.pos = (uint16_t)pos; e.mate_base = (uint8_t)((mate << 7) | (base & 0x7F)); e.qual = (uint8_t)qual;
+    c->corr[c->ncorr++] = e;
+}
+/* BaseCorrector::correctByOverlapAnalysis, src/basecorrector.cpp:14-70.  seq/qual are the mutable current
+ * views; o1/o2 = offset of each view inside the original read.  addCorrection(from, to) is called AFTER the
+ * base was overwritten through the same buffer (:40-45, :47-52), so `from` already equals `to`. */
+static void correct_by_overlap(fqo_ctx* c, char* seq1, char* qual1, int len1, char* seq2, char* qual2, int len2,
+                               const ovres* ov, uint32_t pair, int o1, int o2){
+    (void)len1;
+    if(ov->diff == 0 || ov->diff > 5) return;
+    const int ol = ov->overlapLen;
+    const int start1 = imax(0, ov->offset);
+    const int start2 = len2 - imax(0, -ov->offset) - 1;
+    const char GOOD = 30 + 33, BAD = 14 + 33;
+    int corrected = 0, r1c = 0, r2c = 0;
+    for(int i = 0; i < ol; ++i){
+        const int p1 = start1 + i, p2 = start2 - i;
+        if(seq1[p1] != complement(seq2[p2])){
+            if(qual1[p1] >= GOOD && qual2[p2] <= BAD){
+                seq2[p2] = complement(seq1[p1]); qual2[p2] = qual1[p1];
+                ++corrected; r2c = 1;
+                c->flat[c->L.correction_off + (seq2[p2] & 7) * 8 + (complement(seq1[p1]) & 7)]++;
+                push_corr(c, pair, o2 + p2, 1, seq2[p2], qual2[p2]);
+            }else if(qual2[p2] >= GOOD && qual1[p1] <= BAD){
+                seq1[p1] = complement(seq2[p2]); qual1[p1] = qual2[p2];
+                ++corrected; r1c = 1;
+                c->flat[c->L.correction_off + (seq1[p1] & 7) * 8 + (complement(seq2[p2]) & 7)]++;
+                push_corr(c, pair, o1 + p1, 0, seq1[p1], qual1[p1]);
+            }
+        }
+    }
+    if(corrected > 0) c->flat[c->L.corrected_reads_off] += (r1c && r2c) ? 2 : 1;
+}
+
+int fqo_get_corrections(fqo_ctx* c, fq_correction* out, uint32_t cap, uint32_t* n){
+    *n = c->ncorr;
+    if(out) memcpy(out, c->corr, (size_t)(c->ncorr < cap ? c->ncorr : cap) * sizeof(fq_correction));
+    return 0;
+}
+
 /* ---------------------------------------------------------------- PE flow */
 /* PairEndProcessor::statInsertSize, src/peprocessor.cpp:510-523 */
 static int stat_insert_size(fqo_ctx* c, const rview* r1, const rview* r2, const ovres* ov){
@@ -516,10 +571,17 @@ int fqo_process_pe(fqo_ctx* c, uint32_t n, uint64_t first_index,
                    fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp){
     (void)first_index;
     const fq_params* P = &c->P;
+    c->ncorr = 0;
     for(uint32_t p = 0; p < n; ++p){
         const char* s1 = seq1 + off1[p]; const char* q1 = qual1 + off1[p];
         const char* s2 = seq2 + off2[p]; const char* q2 = qual2 + off2[p];
         int l1 = (int)(off1[p + 1] - off1[p]), l2 = (int)(off2[p + 1] - off2[p]);
+        if(P->correction_enabled){                                    /* the reference corrects its Reads in place */
+            const size_t need = 2 * ((size_t)l1 + l2) + 4;
+            if(need > c->cbuf_cap){ c->cbuf_cap = need * 2; c->cbuf = (char*)realloc(c->cbuf, c->cbuf_cap); }
+            char* m = c->cbuf;
+            memcpy(m, s1, l1); memcpy(m + l1 + 1, q1, l1); memcpy(m + 2 * l1 + 2, s2, l2); memcpy(m + 2 * l1 + l2 + 3, q2, l2);
+        }
         fq_read_result* rec1 = &out1[p]; fq_read_result* rec2 = &out2[p];
         fq_pair_result* pr = &outp[p];
         rec_init(rec1); rec_init(rec2); memset(pr, 0, sizeof(*pr));
@@ -528,6 +590,7 @@ int fqo_process_pe(fqo_ctx* c, uint32_t n, uint64_t first_index,
         if((rc = stat_read(c, 0, s1, q1, l1))) return rc;             /* :276 */
         if((rc = stat_read(c, 1, s2, q2, l2))) return rc;             /* :277 */
         if(P->dup_enabled) dup_stat_pair(c, s1, l1, s2, l2);          /* :279-281 */
+        if(P->correction_enabled){ char* m = c->cbuf; s1 = m; q1 = m + l1 + 1; s2 = m + 2 * l1 + 2; q2 = m + 2 * l1 + l2 + 3; }
         rview r1 = { s1, q1, l1 }, r2 = { s2, q2, l2 };
         int a1 = trim_and_cut(P, &r1, P->trim_front1, P->trim_tail1); /* :292 */
         int a2 = trim_and_cut(P, &r2, P->trim_front2, P->trim_tail2); /* :293 */
@@ -543,6 +606,9 @@ int fqo_process_pe(fqo_ctx* c, uint32_t n, uint64_t first_index,
             pr->ov1_offset = (int16_t)ov.offset; pr->ov1_len = (uint16_t)ov.overlapLen; pr->ov1_diff = (uint16_t)ov.diff;
             pr->insert_size = (uint16_t)stat_insert_size(c, &r1, &r2, &ov);   /* :305-308 */
             insertEvaluated = 1;
+            if(P->correction_enabled)                                 /* :310-312 */
+                correct_by_overlap(c, (char*)r1.seq, (char*)r1.qual, r1.len, (char*)r2.seq, (char*)r2.qual, r2.len, &ov, p,
+                                   (int)(r1.seq - s1), (int)(r2.seq - s2));
             if(P->adapter_trim_enabled){                              /* :314-326 */
                 int trimmed = 0;
                 int ol = ov.overlapLen;

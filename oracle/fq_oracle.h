@@ -36,6 +36,8 @@ int  fqo_process_pe(fqo_ctx* c, uint32_t n, uint64_t first_index,
                     const char* seq1, const char* qual1, const uint64_t* off1,
                     const char* seq2, const char* qual2, const uint64_t* off2,
                     fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp);
+/* bases rewritten by the last fqo_process_pe call (BaseCorrector, -c) */
+int  fqo_get_corrections(fqo_ctx* c, fq_correction* out, uint32_t cap, uint32_t* n);
 /* copy accumulators (fq_stats_layout.total_u64 entries) */
 int  fqo_finalize(fqo_ctx* c, uint64_t* flat);
 int  fqo_dup_table(fqo_ctx* c, uint64_t* dups, uint32_t* counts, uint8_t* gc);

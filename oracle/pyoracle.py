@@ -46,6 +46,7 @@ def _load(kind):
     f = getattr(lib, pre + "process_pe"); f.argtypes = [vp, u32, u64, vp, vp, vp, vp, vp, vp, vp, vp, vp]; f.restype = C.c_int
     f = getattr(lib, pre + "finalize"); f.argtypes = [vp, vp]; f.restype = C.c_int
     f = getattr(lib, pre + "dup_table"); f.argtypes = [vp, vp, vp, vp]; f.restype = C.c_int
+    f = getattr(lib, pre + "get_corrections"); f.argtypes = [vp, vp, u32, C.POINTER(u32)]; f.restype = C.c_int
     lib.fqo_layout.argtypes = [C.POINTER(abi.FqParams), C.POINTER(abi.FqStatsLayout)]
     lib.fqo_layout.restype = C.c_int
     if kind == "reference":
@@ -107,6 +108,15 @@ class Oracle:
         if rc:
             raise RuntimeError(f"oracle process_pe rc={rc}")
         return out1, out2, outp
+
+    def corrections(self):
+        """Edits of the last process_pe call, sorted (pair, mate, pos)."""
+        n = C.c_uint32(0)
+        f = getattr(self.lib, self.pre + "get_corrections")
+        f(self.h, None, 0, C.byref(n))
+        out = np.zeros(n.value, dtype=abi.CORRECTION_DTYPE)
+        f(self.h, abi.ptr(out) if n.value else None, n.value, C.byref(n))
+        return np.sort(out, order=["pair", "mate_base", "pos"])
 
     def finalize(self):
         flat = np.zeros(self.layout.total_u64, dtype=np.uint64)

@@ -47,6 +47,7 @@
 #include "adaptertrimmer.h"
 #include "overlapanalysis.h"
 #include "filterresult.h"
+#include "basecorrector.h"
 #include "fq_oracle.h"
 
 namespace {
@@ -61,6 +62,7 @@ struct RefCtx {
     Duplicate* dup;
     std::vector<uint64_t> insertHist;
     std::string adapter1, adapter2;
+    std::vector<fq_correction> corr;
 };
 
 void fill_options(Options* o, const fq_params* p){
@@ -94,7 +96,7 @@ void fill_options(Options* o, const fq_params* p){
     o->adapter.adapterSeqR2Provided = p->adapter_r2_len > 0;
     o->overlapRequire = p->overlap_require; o->overlapDiffLimit = p->overlap_diff_limit;
     o->insertSizeMax = p->insert_size_max;
-    o->correction.enabled = false;
+    o->correction.enabled = p->correction_enabled;
     o->mergePE.enabled = p->merge_enabled; o->mergePE.discardUnmerged = p->merge_discard_unmerged;
     o->kmer.enabled = p->kmer_len > 0; o->kmer.kmerLen = p->kmer_len;
     o->duplicate.enabled = p->dup_enabled; o->duplicate.keylen = p->dup_keylen;
@@ -266,6 +268,7 @@ int fqr_process_pe(void* h, uint32_t n, uint64_t first_index,
                    fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp){
     (void)first_index;
     RefCtx* c = (RefCtx*)h; Options* o = c->opt;
+    c->corr.clear();
     for(uint32_t p = 0; p < n; ++p){
         size_t l1 = off1[p + 1] - off1[p], l2 = off2[p + 1] - off2[p];
         Read* or1 = new Read("@r 1", std::string(seq1 + off1[p], l1), "+", std::string(qual1 + off1[p], l1));
@@ -289,6 +292,19 @@ int fqr_process_pe(void* h, uint32_t n, uint64_t first_index,
             set_ov(pr, ov, true);
             pr->insert_size = (uint16_t)stat_insert(c, r1, r2, ov);
             insertSizeEvaluated = true;
+            if(o->correction.enabled){
+                // BaseCorrector mutates the reads in place; the edits are found by comparing before/after
+                const std::string s1b = r1->seq.seqStr, s2b = r2->seq.seqStr, q1b = r1->quality, q2b = r2->quality;
+                BaseCorrector::correctByOverlapAnalysis(r1, r2, c->fr, ov);
+                for(size_t i = 0; i < s1b.size(); ++i) if(s1b[i] != r1->seq.seqStr[i] || q1b[i] != r1->quality[i]){
+                    fq_correction e; e.pair = p; e.pos = (uint16_t)(start1 + i); e.mate_base = (uint8_t)(r1->seq.seqStr[i] & 0x7F); e.qual = (uint8_t)r1->quality[i];
+                    c->corr.push_back(e);
+                }
+                for(size_t i = 0; i < s2b.size(); ++i) if(s2b[i] != r2->seq.seqStr[i] || q2b[i] != r2->quality[i]){
+                    fq_correction e; e.pair = p; e.pos = (uint16_t)(start2 + i); e.mate_base = (uint8_t)(0x80 | (r2->seq.seqStr[i] & 0x7F)); e.qual = (uint8_t)r2->quality[i];
+                    c->corr.push_back(e);
+                }
+            }
             if(o->adapter.enableTriming){
                 int b1 = r1->length(), b2 = r2->length();
                 bool trimmed = AdapterTrimmer::trimByOverlapAnalysis(r1, r2, c->fr, ov);
@@ -395,6 +411,15 @@ int fqr_finalize(void* h, uint64_t* flat){
     }
     flat[L->merged_pairs_off] = c->fr->mMergedPairs;
     for(uint64_t i = 0; i < L->insert_hist_len; ++i) flat[L->insert_hist_off + i] = c->insertHist[i];
+    for(int i = 0; i < 64; ++i) flat[L->correction_off + i] = c->fr->getCorrectionMatrix()[i];
+    flat[L->corrected_reads_off] = c->fr->mCorrectedReads;
+    return 0;
+}
+
+int fqr_get_corrections(void* h, fq_correction* out, uint32_t cap, uint32_t* n){
+    RefCtx* c = (RefCtx*)h;
+    *n = (uint32_t)c->corr.size();
+    if(out) memcpy(out, c->corr.data(), std::min<size_t>(cap, c->corr.size()) * sizeof(fq_correction));
     return 0;
 }
 

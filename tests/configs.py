@@ -34,6 +34,10 @@ PE = {
     "pe_overlap_params": "-a -m --min_overlap_len 20 --max_diff_for_overlap 2 -q",
     "pe_overlap_limit0": "-a -m --max_diff_for_overlap 0",
     "pe_merge_cut": "-m -a -g -x --enable_cut_front --enable_cut_right -q -l --min_length 40",
+    # PE base correction (BaseCorrector, src/basecorrector.cpp)
+    "pe_correct": "-c -a -q",
+    "pe_correct_only": "-c --enable_cut_front",
+    "pe_correct_merge": f"-c -m -a -g -q --adapter_of_read1 {ADAPTER1} -x",
 }
 
 

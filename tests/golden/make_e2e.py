@@ -34,6 +34,8 @@ CASES = {
     "pe_merge_keep": (True, "-m -a -q -l --min_length 50 --enable_cut_right"),
     "pe_merge_discard": (True, "-m --discard_unmerged -q"),
     "se_failed": (False, "-q -l --min_length 100 -f 2 -t 3 -g -y -Y 0.35"),
+    "pe_correct": (True, "-c -a -q"),
+    "pe_correct_merge": (True, "-c -m -a -g -q"),
 }
 
 

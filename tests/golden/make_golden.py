@@ -60,6 +60,8 @@ def save(name, cfg, r1, r2=None, kind="reference"):
     else:
         d["seq2"], d["qual2"], d["off2"] = r2
         d["rec1"], d["rec2"], d["recp"] = o.process_pe(r1, r2)
+        if opt.correction.enabled:
+            d["corr"] = o.corrections()
     d["flat"] = o.finalize()
     if opt.duplicate.enabled:
         dups, counts, gc = o.dup_table()
@@ -81,7 +83,7 @@ def main():
     save("hiseq_cfg2", "cfg2", synth.se_hiseq(800, 150, seed=102))
     save("adapter_cfg4", "cfg4", synth.se_adapter_polyx(800, 100, seed=103))
     p1, p2 = synth.pe_novaseq(500, 150, seed=104, frag_mean=200, frag_sd=80)
-    for cfg in ("cfg1", "cfg3", "cfg5", "pe_adapters", "pe_dup_kmer", "pe_overlap_limit0", "pe_merge_cut"):
+    for cfg in ("cfg1", "cfg3", "cfg5", "pe_adapters", "pe_dup_kmer", "pe_overlap_limit0", "pe_merge_cut", "pe_correct", "pe_correct_merge"):
         save(f"novaseq_{cfg}", cfg, p1, p2)
     a, b = synth.ragged(500, seed=105), synth.ragged(500, seed=106)
     for cfg in ("cfg1", "cfg3", "pe_merge_discard", "pe_merge_cut"):
@@ -95,6 +97,7 @@ def main():
         r2 = batch.slice_reads(batch.read_fastq(f"{TD}/r2.fq.gz"), 0, 1500)
         save("testdata_cfg1", "cfg1", r1, r2)
         save("testdata_cfg3", "cfg3", r1, r2)
+        save("testdata_pe_correct_merge", "pe_correct_merge", r1, r2)
         save("testdata_cfg2", "cfg2", r1)
         save("testdata_cfg4", "cfg4", r1)
         g1, g2 = batch.read_fastq(f"{TD}/polygr1.fq"), batch.read_fastq(f"{TD}/polygr2.fq")

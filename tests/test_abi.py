@@ -105,7 +105,7 @@ def test_product_does_not_import_oracle():
 def test_invalid_params_rejected():
     lib = abi.load()
     h = C.c_void_p()
-    for mut in (dict(correction_enabled=1), dict(kmer_len=16), dict(dup_enabled=1, dup_keylen=20),
+    for mut in (dict(kmer_len=16), dict(dup_enabled=1, dup_keylen=20),
                 dict(cut_front_enabled=1, cut_front_window=0), dict(abi_version=99)):
         p = Options().to_params()
         for k, v in mut.items():

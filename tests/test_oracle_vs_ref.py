@@ -9,42 +9,17 @@ import pytest
 
 from fqtool_b200 import batch, synth
 from oracle import pyoracle
-from tests import configs
+from tests import configs, util
 
 REF_TESTDATA = "/root/reference/testdata"
 needs_ref = pytest.mark.skipif(not pyoracle.have_reference(), reason="oracle/_ref not built (no /root/reference)")
 
 
 def run(kind, opt, r1, r2=None, chunks=1):
-    o = pyoracle.Oracle(opt.to_params(), kind)
-    n = len(r1[2]) - 1
-    recs = []
-    bounds = np.linspace(0, n, chunks + 1).astype(int)
-    for lo, hi in zip(bounds[:-1], bounds[1:]):
-        if r2 is None:
-            recs.append((o.process_se(batch.slice_reads(r1, lo, hi), lo),))
-        else:
-            recs.append(o.process_pe(batch.slice_reads(r1, lo, hi), batch.slice_reads(r2, lo, hi), lo))
-    out = tuple(np.concatenate([r[i] for r in recs]) for i in range(len(recs[0])))
-    flat = o.finalize()
-    dup = o.dup_table() if opt.duplicate.enabled else None
-    o.close()
-    return out, flat, dup
+    return util.run_oracle(opt, r1, r2, kind=kind, chunks=chunks)
 
 
-def assert_same(a, b):
-    (ra, fa, da), (rb, fb, db) = a, b
-    for x, y in zip(ra, rb):
-        for name in x.dtype.names:
-            if name == "reserved":
-                continue
-            bad = np.nonzero(x[name] != y[name])[0]
-            assert bad.size == 0, f"field {name}: first mismatch at read {bad[0]}: {x[bad[0]]} vs {y[bad[0]]}"
-    bad = np.nonzero(fa != fb)[0]
-    assert bad.size == 0, f"flat accumulators differ at {bad[:8]}"
-    if da is not None:
-        for x, y, nm in zip(da, db, ("dups", "counts", "gc")):
-            assert np.array_equal(x, y), f"dup {nm} differ"
+assert_same = util.assert_same
 
 
 @needs_ref

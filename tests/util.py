@@ -26,10 +26,19 @@ def load_golden(path):
 def run_oracle(opt, r1, r2=None, kind="port", chunks=1):
     from oracle import pyoracle
     o = pyoracle.Oracle(opt.to_params(), kind)
-    out = _run_chunks(lambda a, i: (o.process_se(a, i),), lambda a, b, i: o.process_pe(a, b, i), r1, r2, chunks)
+    o._corr = []
+
+    def pe(a, b, i):
+        r = o.process_pe(a, b, i)
+        if opt.correction.enabled:
+            o._corr.append((i, o.corrections()))
+        return r
+    out = _run_chunks(lambda a, i: (o.process_se(a, i),), pe, r1, r2, chunks)
     flat = o.finalize()
     dup = o.dup_table() if opt.duplicate.enabled else None
     o.close()
+    if opt.correction.enabled:
+        return out, flat, dup, _merge_corr(o._corr)
     return out, flat, dup
 
 
@@ -38,12 +47,31 @@ def run_cuda(opt, r1, r2=None, chunks=1, impl=0, device=0):
     from fqtool_b200.engine import Engine
     e = Engine(opt.to_params(), device=device)
     e.set_impl(impl)
-    out = _run_chunks(lambda a, i: (e.process_se(batch.pack(a, i)),),
-                      lambda a, b, i: e.process_pe(batch.pack(a, i), batch.pack(b, i)), r1, r2, chunks)
+    corr = []
+
+    def pe(a, b, i):
+        r = e.process_pe(batch.pack(a, i), batch.pack(b, i))
+        if opt.correction.enabled:
+            corr.append((i, e.corrections()))
+        return r
+    out = _run_chunks(lambda a, i: (e.process_se(batch.pack(a, i)),), pe, r1, r2, chunks)
     flat = e.finalize()
     dup = e.dup_table() if opt.duplicate.enabled else None
     e.close()
+    if opt.correction.enabled:
+        return out, flat, dup, _merge_corr(corr)
     return out, flat, dup
+
+
+def _merge_corr(parts):
+    """Per-chunk edit lists -> one list with global pair indices, sorted."""
+    from fqtool_b200 import abi
+    if not parts:
+        return np.zeros(0, dtype=abi.CORRECTION_DTYPE)
+    out = []
+    for first, c in parts:
+        c = c.copy(); c["pair"] += np.uint32(first); out.append(c)
+    return np.sort(np.concatenate(out), order=["pair", "mate_base", "pos"])
 
 
 def _run_chunks(se, pe, r1, r2, chunks):
@@ -69,7 +97,9 @@ def assert_records(x, y, what=""):
 
 def assert_same(a, b):
     """(records, flat, dup) bit-exact."""
-    (ra, fa, da), (rb, fb, db) = a, b
+    (ra, fa, da), (rb, fb, db) = a[:3], b[:3]
+    if len(a) > 3 or len(b) > 3:
+        assert len(a[3]) == len(b[3]) and np.array_equal(a[3], b[3]), f"base corrections differ: {len(a[3])} vs {len(b[3])}"
     for i, (x, y) in enumerate(zip(ra, rb)):
         assert_records(x, y, f"records[{i}]")
     bad = np.nonzero(fa != fb)[0]
@@ -81,7 +111,9 @@ def assert_same(a, b):
 
 
 def assert_matches_golden(res, g):
-    recs, flat, dup = res
+    recs, flat, dup = res[:3]
+    if "corr" in g:
+        assert np.array_equal(res[3], g["corr"]), "base corrections differ from the reference"
     assert_records(recs[0], g["rec1"], "rec1")
     if g["r2"] is not None:
         assert_records(recs[1], g["rec2"], "rec2")
