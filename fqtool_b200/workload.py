@@ -89,6 +89,8 @@ def generate(cfg, n, first_index, device, stream_ptr):
     c = CONFIGS[cfg]
     b1 = DeviceBatch(n, c["L"], first_index, device)
     b2 = DeviceBatch(n, c["L"], first_index, device) if c["paired"] else None
+    # the buffers were zero-filled on torch's stream; the generator runs on the caller's (non-blocking) stream
+    torch.cuda.current_stream(device).synchronize()
     a2 = [b2.offsets.data_ptr(), b2.lengths.data_ptr(), b2.bases2.data_ptr(), b2.qual.data_ptr()] if b2 else [None] * 4
     rc = lib.fqk_synth_generate(stream_ptr, c["model"], c["seed"], first_index, n, c["L"], c["frag"][0], c["frag"][1],
                                 b1.offsets.data_ptr(), b1.lengths.data_ptr(), b1.bases2.data_ptr(), b1.qual.data_ptr(), *a2)
