@@ -323,6 +323,27 @@ def main():
            "ms_per_step": float(tt.item()) * 1e3 / a.e2e_steps,
            "note": f"{nb} fqk_submit_se/fqk_wait (SE, two packs in flight) or fqk_process_pe calls per step over {n_host} distinct pinned host batches of {BATCH_READS} reads"}
 
+    # ---- the same through the ASCII entry point (FASTQ characters in, packing on the GPU) ----
+    e2e_ascii = None
+    if not c["paired"]:
+        from fqtool_b200 import batch as fbatch
+        seq, qual, off = fbatch.unpack(hbs[0][0])
+        pseq = torch.empty(len(seq), dtype=torch.uint8, pin_memory=True); pseq.numpy()[:] = seq
+        pqual = torch.empty(len(qual), dtype=torch.uint8, pin_memory=True); pqual.numpy()[:] = qual
+        areads = (pseq.numpy(), pqual.numpy(), off)
+        eng.process_se_ascii(areads)
+        eng.reset(); barrier()
+        t0 = time.perf_counter()
+        reps = min(nb, 8)
+        for _ in range(reps):
+            eng.process_se_ascii(areads)
+        eng.finalize(); barrier()
+        dta = time.perf_counter() - t0
+        e2e_ascii = {"value": reps * hbs[0][0].n * c["L"] / dta / 1e9, "unit": "Gbases/s",
+                     "h2d_bytes_per_call": int(2 * len(seq) + 10 * hbs[0][0].n), "calls": reps,
+                     "note": "fqk_process_se_ascii: FASTQ characters over PCIe (2 B/base), 2-bit packing by k_pack_ascii on the GPU"}
+        del pseq, pqual
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         del batches, outs
@@ -338,7 +359,7 @@ def main():
                            "read_length": c["L"], "batches_per_step": nb, "batch_reads": BATCH_READS,
                            "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit / 1e9),
                            "impl": a.impl},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
+                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu_baseline}
         print(json.dumps(line))
     if world > 1:

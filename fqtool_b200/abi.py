@@ -68,6 +68,11 @@ class FqBatch(C.Structure):
     ]
 
 
+class FqAsciiBatch(C.Structure):
+    _fields_ = [("n_reads", C.c_uint32), ("reserved", C.c_uint32), ("first_index", C.c_uint64),
+                ("off", C.c_void_p), ("seq", C.c_void_p), ("qual", C.c_void_p)]
+
+
 class FqStatsLayout(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "total_u64", "max_cycles", "kmer_bins")] + [("stats_off", C.c_uint64 * 4)] + [
@@ -94,7 +99,7 @@ assert READ_RESULT_DTYPE.itemsize == 16 and PAIR_RESULT_DTYPE.itemsize == 24 and
 
 EXPORTS = [
     "fqk_default_params", "fqk_stats_layout", "fqk_create", "fqk_destroy", "fqk_last_error",
-    "fqk_nccl_unique_id", "fqk_process_se", "fqk_process_pe", "fqk_submit_se", "fqk_wait", "fqk_process_se_device",
+    "fqk_nccl_unique_id", "fqk_process_se", "fqk_process_pe", "fqk_submit_se", "fqk_wait", "fqk_process_se_ascii", "fqk_process_pe_ascii", "fqk_process_se_device",
     "fqk_process_pe_device", "fqk_sync", "fqk_stream", "fqk_launch_count",
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
@@ -123,6 +128,8 @@ def load():
     lib.fqk_nccl_unique_id.argtypes = [vp]; lib.fqk_nccl_unique_id.restype = i32
     lib.fqk_process_se.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se.restype = i32
     lib.fqk_process_pe.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp]; lib.fqk_process_pe.restype = i32
+    lib.fqk_process_se_ascii.argtypes = [vp, P(FqAsciiBatch), vp]; lib.fqk_process_se_ascii.restype = i32
+    lib.fqk_process_pe_ascii.argtypes = [vp, P(FqAsciiBatch), P(FqAsciiBatch), vp, vp, vp]; lib.fqk_process_pe_ascii.restype = i32
     lib.fqk_submit_se.argtypes = [vp, P(FqBatch), vp, P(u64)]; lib.fqk_submit_se.restype = i32
     lib.fqk_wait.argtypes = [vp, u64]; lib.fqk_wait.restype = i32
     lib.fqk_process_se_device.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se_device.restype = i32

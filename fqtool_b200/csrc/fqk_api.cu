@@ -64,6 +64,9 @@ struct fqk_ctx {
     uint32_t* err = nullptr;                  // device error flag
     uint32_t* maxlen2 = nullptr;              // device: [0..1] longest raw read of each mate, [2] number of corrections
     DevBuf corr; uint32_t corr_cap = 0;       // device list of fq_correction of the current PE batch
+    // ASCII ingest staging (fqk_process_*_ascii): raw characters and source offsets per mate, pinned index arrays
+    DevBuf aseq[2], aqual[2], asrc[2];
+    std::vector<uint32_t> hsrc[2], hdst[2]; std::vector<uint16_t> hlen[2];
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
     StagedBatch st[2];
@@ -298,6 +301,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     if(c->perr_host) cudaFreeHost(c->perr_host);
     for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
     c->res1.release(); c->res2.release(); c->resp.release(); c->corr.release();
+    for(int i = 0; i < 2; ++i){ c->aseq[i].release(); c->aqual[i].release(); c->asrc[i].release(); }
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
     if(c->stream) cudaStreamDestroy(c->stream);
@@ -409,6 +413,7 @@ static int check_err_flag(fqk_ctx* c){
     CU(cudaStreamSynchronize(c->stream));
     if(e & 1) return fail(c, FQK_E_LIMIT, "a read (or merged read) is longer than max_cycles");
     if(e & 2) return fail(c, FQK_E_INVALID, "batch offsets must be multiples of FQK_PAD");
+    if(e & 4) return fail(c, FQK_E_ALPHABET, "base outside {A,C,G,T,N} or quality >= 128 in an ASCII batch");
     return 0;
 }
 
@@ -462,6 +467,79 @@ extern "C" int fqk_process_se(fqk_ctx* c, const fq_batch* in, fq_read_result* ou
     if(c->res1.ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
     rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
     CU(cudaMemcpyAsync(out, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    return check_err_flag(c);
+}
+
+// ASCII batch -> staged packed batch: index arrays on the host (O(reads)), characters packed by k_pack_ascii
+static int stage_ascii(fqk_ctx* c, int m, const fq_ascii_batch* b){
+    const uint32_t n = b->n_reads;
+    StagedBatch& s = c->st[m];
+    const uint64_t chars = b->off[n] - b->off[0];
+    if(chars > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "ASCII batch larger than 2^32 characters");
+    c->hsrc[m].resize(n); c->hdst[m].resize(n); c->hlen[m].resize(n);
+    uint64_t pos = 0;
+    for(uint32_t r = 0; r < n; ++r){
+        const uint64_t l = b->off[r + 1] - b->off[r];
+        if(l > FQK_MAX_READ_LEN) return fail(c, FQK_E_LIMIT, "read longer than FQK_MAX_READ_LEN");
+        c->hsrc[m][r] = (uint32_t)(b->off[r] - b->off[0]); c->hdst[m][r] = (uint32_t)pos; c->hlen[m][r] = (uint16_t)l;
+        pos += (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD;
+        if(pos > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "batch larger than 2^32 padded bases");
+    }
+    const uint64_t total = (pos + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
+    if(s.off.ensure((size_t)n * 4 + 16) || s.len.ensure((size_t)n * 2 + 16) || s.b2.ensure(total / 4 + 16) || s.q.ensure(total + 16) ||
+       c->aseq[m].ensure(chars + 16) || c->aqual[m].ensure(chars + 16) || c->asrc[m].ensure((size_t)n * 4 + 16))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    CU(cudaMemcpyAsync(c->aseq[m].p, b->seq + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->aqual[m].p, b->qual + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->asrc[m].p, c->hsrc[m].data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.off.p, c->hdst[m].data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(s.len.p, c->hlen[m].data(), (size_t)n * 2, cudaMemcpyHostToDevice, c->stream));
+    if(total > pos){                                                      // zero tail of the batch
+        CU(cudaMemsetAsync((uint8_t*)s.q.p + pos, 0, total - pos, c->stream));
+        CU(cudaMemsetAsync((uint8_t*)s.b2.p + pos / 4, 0, (total - pos) / 4, c->stream));
+    }
+    if(n){
+        k_pack_ascii<<<grid_for(c, n, 8, 8), 256, 0, c->stream>>>(n, (const char*)c->aseq[m].p, (const char*)c->aqual[m].p,
+            (const uint32_t*)c->asrc[m].p, (const uint32_t*)s.off.p, (const uint16_t*)s.len.p, (uint8_t*)s.b2.p, (uint8_t*)s.q.p, c->err);
+        c->launches++;
+    }
+    s.dev.n = n; s.dev.first_index = b->first_index; s.dev.total = total;
+    s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
+    s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
+    return 0;
+}
+
+extern "C" int fqk_process_se_ascii(fqk_ctx* c, const fq_ascii_batch* in, fq_read_result* out){
+    if(!c || !in || !in->off || (!out && in->n_reads)) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    if(in->n_reads == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    int rc = stage_ascii(c, 0, in); if(rc) return rc;
+    const size_t n = in->n_reads;
+    if(c->res1.ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
+    CU(cudaMemcpyAsync(out, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    return check_err_flag(c);
+}
+
+extern "C" int fqk_process_pe_ascii(fqk_ctx* c, const fq_ascii_batch* r1, const fq_ascii_batch* r2, fq_read_result* o1,
+                                    fq_read_result* o2, fq_pair_result* op){
+    if(!c || !r1 || !r2 || !r1->off || !r2->off) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    if(r1->n_reads != r2->n_reads) return fail(c, FQK_E_INVALID, "read1/read2 batches differ in size");
+    if(r1->n_reads == 0) return 0;
+    if(!o1 || !o2 || !op) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    int rc = stage_ascii(c, 0, r1); if(rc) return rc;
+    rc = stage_ascii(c, 1, r2); if(rc) return rc;
+    const size_t n = r1->n_reads;
+    if(c->res1.ensure(n * sizeof(fq_read_result)) || c->res2.ensure(n * sizeof(fq_read_result)) ||
+       c->resp.ensure(n * sizeof(fq_pair_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_pe(c, c->st[0].dev, c->st[1].dev, (fq_read_result*)c->res1.p, (fq_read_result*)c->res2.p, (fq_pair_result*)c->resp.p);
+    if(rc) return rc;
+    CU(cudaMemcpyAsync(o1, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(o2, c->res2.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(op, c->resp.p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
     return check_err_flag(c);
 }
 

@@ -482,3 +482,38 @@ __global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, co
         gcs[k] = (cnt && (uint32_t)(f >> 8) == idx) ? (uint8_t)(f & 0xFF) : 0;
     }
 }
+
+
+// ---------------------------------------------------------------- ASCII ingest
+// FASTQ characters -> the packed batch layout, on the device (the host-side twin is fqk_pack_ascii).
+// One warp per read, a lane per 16-base chunk: 16 sequence and 16 quality characters become one 32-bit
+// word of 2-bit codes and one 16-byte quality vector (N flag in bit 7); padding is written as zeros.
+__global__ void __launch_bounds__(256) k_pack_ascii(uint32_t n, const char* __restrict__ seq, const char* __restrict__ qual,
+                                                     const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
+                                                     const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
+                                                     uint8_t* __restrict__ qout, uint32_t* __restrict__ err){
+    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    for(uint32_t r = blockIdx.x * warps + (threadIdx.x >> 5); r < n; r += gridDim.x * warps){
+        const uint32_t so = src_off[r], dof = dst_off[r], len = lengths[r];
+        const uint32_t chunks = (len + 15) >> 4;
+        for(uint32_t c = lane; c < chunks; c += 32){
+            uint32_t code = 0, q[4] = {0, 0, 0, 0};
+#pragma unroll
+            for(int j = 0; j < 16; ++j){
+                const uint32_t i = 16 * c + j;
+                if(i < len){
+                    const char ch = seq[so + i];
+                    const uint32_t qq = (uint8_t)qual[so + i];
+                    uint32_t cl;
+                    switch(ch){ case 'A': cl = 0; break; case 'T': cl = 1; break; case 'C': cl = 2; break; case 'G': cl = 3; break;
+                                case 'N': cl = 4; break; default: cl = 0; atomicOr(err, 4u); }
+                    if(qq & 0x80u) atomicOr(err, 4u);
+                    if(cl == 4) q[j >> 2] |= (qq | 0x80u) << (8 * (j & 3));
+                    else { q[j >> 2] |= qq << (8 * (j & 3)); code |= cl << (2 * j); }
+                }
+            }
+            *reinterpret_cast<uint4*>(qout + dof + 16 * c) = make_uint4(q[0], q[1], q[2], q[3]);
+            *reinterpret_cast<uint32_t*>(bases2 + ((dof + 16 * c) >> 2)) = code;
+        }
+    }
+}

@@ -17,3 +17,7 @@ __global__ void k_dup(const __grid_constant__ DevParams D, DevBatch B1, DevBatch
                       unsigned long long* tab128, unsigned long long* first64);
 __global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, const unsigned long long* first64,
                              uint64_t* dups, uint32_t* counts, uint8_t* gcs);
+__global__ void k_pack_ascii(uint32_t n, const char* __restrict__ seq, const char* __restrict__ qual,
+                             const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
+                             const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
+                             uint8_t* __restrict__ qout, uint32_t* __restrict__ err);

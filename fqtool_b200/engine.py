@@ -60,6 +60,30 @@ class Engine:
         self._check(self.lib.fqk_process_se(self.h, C.byref(b), abi.ptr(out)), "fqk_process_se")
         return out
 
+    @staticmethod
+    def _ascii(reads, first_index):
+        seq, qual, off = (np.ascontiguousarray(x) for x in reads)
+        b = abi.FqAsciiBatch()
+        b.n_reads = len(off) - 1; b.first_index = first_index
+        b.off, b.seq, b.qual = abi.ptr(off.astype(np.uint64, copy=False)), abi.ptr(seq), abi.ptr(qual)
+        return b, (seq, qual, off)
+
+    def process_se_ascii(self, reads, first_index=0):
+        """ASCII (seq, qual, off) straight to the GPU: packing runs on the device (fqk_process_se_ascii)."""
+        b, keep = self._ascii(reads, first_index)
+        out = np.zeros(b.n_reads, dtype=abi.READ_RESULT_DTYPE)
+        self._check(self.lib.fqk_process_se_ascii(self.h, C.byref(b), abi.ptr(out)), "fqk_process_se_ascii")
+        return out
+
+    def process_pe_ascii(self, reads1, reads2, first_index=0):
+        b1, k1 = self._ascii(reads1, first_index); b2, k2 = self._ascii(reads2, first_index)
+        n = b1.n_reads
+        out = (np.zeros(n, dtype=abi.READ_RESULT_DTYPE), np.zeros(n, dtype=abi.READ_RESULT_DTYPE),
+               np.zeros(n, dtype=abi.PAIR_RESULT_DTYPE))
+        self._check(self.lib.fqk_process_pe_ascii(self.h, C.byref(b1), C.byref(b2), abi.ptr(out[0]), abi.ptr(out[1]),
+                                                  abi.ptr(out[2])), "fqk_process_pe_ascii")
+        return out
+
     def submit_se(self, batch, out):
         """Pipelined fqk_process_se: returns a ticket; `batch` and `out` must stay alive until wait(ticket)."""
         b = batch.c_struct()

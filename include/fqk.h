@@ -244,6 +244,24 @@ int  fqk_process_pe(fqk_ctx* ctx, const fq_batch* r1, const fq_batch* r2,
                     fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp);
 
 /*
+ * ASCII entry points: the host hands over what a FASTQ parser holds (flat sequence and quality
+ * characters, read r at [off[r], off[r+1])) and the 2-bit packing runs on the GPU (k_pack_ascii),
+ * so the host does no per-base work at all.  PCIe carries 2 B/base instead of 1.25.  A base
+ * outside {A,C,G,T,N} or a quality >= 128 makes the call fail with FQK_E_ALPHABET.
+ */
+typedef struct fq_ascii_batch {
+    uint32_t        n_reads;
+    uint32_t        reserved;
+    uint64_t        first_index;
+    const uint64_t* off;           /* [n_reads + 1]                           */
+    const char*     seq;           /* [off[n_reads]]                          */
+    const char*     qual;          /* [off[n_reads]]                          */
+} fq_ascii_batch;
+int  fqk_process_se_ascii(fqk_ctx* ctx, const fq_ascii_batch* in, fq_read_result* out);
+int  fqk_process_pe_ascii(fqk_ctx* ctx, const fq_ascii_batch* r1, const fq_ascii_batch* r2,
+                          fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp);
+
+/*
  * Pipelined form of fqk_process_se for hosts that keep two packs in flight: fqk_submit_se enqueues
  * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's
  * records are in `out`.  The upload of pack k+1 overlaps the kernels and the download of pack k.

@@ -75,3 +75,23 @@ def test_pipelined_submit_wait_matches_sync():
     got = (np.concatenate(outs),), e.finalize(), None
     util.assert_same(got, want)
     e.close()
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg4", "cfg3", "pe_correct_merge"])
+def test_ascii_entry_points_match_packed_path(name):
+    """fqk_process_*_ascii (device-side packing) == host-packed path; foreign alphabet is an error."""
+    from fqtool_b200 import batch
+    from fqtool_b200.engine import Engine, FqkError
+    opt = configs.options(name)
+    paired = name in configs.PE
+    r1 = synth.ragged(5000, seed=91); r2 = synth.ragged(5000, seed=92) if paired else None
+    want = util.run_cuda(opt, r1, r2)
+    e = Engine(opt.to_params())
+    recs = e.process_pe_ascii(r1, r2) if paired else (e.process_se_ascii(r1),)
+    got = (tuple(recs), e.finalize(), e.dup_table() if opt.duplicate.enabled else None)
+    util.assert_same(got, want[:3])
+    if not paired:
+        bad = batch.from_strings(["ACGTNACGTRACGT"], ["IIIIIIIIIIIIII"])
+        with pytest.raises(FqkError):
+            e.process_se_ascii(bad)
+    e.close()
