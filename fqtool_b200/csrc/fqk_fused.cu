@@ -464,16 +464,16 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
 
 
 // ===========================================================================
-// Warp-specialised variant (the default): 12 statistics warps + 4 trim warps per block.
-//   trim warps (threads 384..511): bulk-copy producer, phase 1 of tile k+1 (records, per-tile lists of
+// Warp-specialised variant (the default): 8 statistics warps + 8 trim warps per block.
+//   trim warps (threads 256..511): bulk-copy producer, phase 1 of tile k+1 (records, per-tile lists of
 //       "common" and "other" reads) while the statistics warps reduce tile k;
-//   statistics warps (threads 0..383): phase 2 over the lists, no block-wide barrier in steady state.
+//   statistics warps (threads 0..255): phase 2 over the lists (common reads through the dp4a quad path),
+//       no block-wide barrier in steady state.
 // Three staging buffers; mbarriers: full[s] (bulk copies landed), ready[s] (lists written), free[s]
-// (statistics done with the stage).  Register budget split with setmaxnreg (144 / 80).
+// (statistics done with the stage).  Register budget split with setmaxnreg (168 / 80).
 // ===========================================================================
 constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
 constexpr int KMER_SMEM_MAX = 6;
-static_assert(WS_STATS <= THREADS, "level-2 slot layout (stride THREADS) is shared with the single-role kernel");
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar){
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
@@ -561,6 +561,106 @@ struct StatsMode {
     const uint32_t* maxlen;          // device scalar: longest raw read of this mate's batch (or nullptr)
 };
 
+// ---------------------------------------------------------------------------
+// Quad path of the statistics warps: four "common" reads at a time.  The thread's 4-cycle word of each of the
+// four reads is byte-transposed (8 PRMT), so that a register holds ONE cycle of FOUR reads; every per-cycle sum
+// is then a single dp4a into a 32-bit accumulator (no byte lanes, no folding):  sum over reads of a*b with
+// a = quality / threshold flag, b = class mask.  Flags and masks stay where they are in the byte (weights
+// 128 / 64 for q>20 / q>30, 4^j or 2*4^j for the code bits of cycle j); the weights are divided out when the
+// accumulators are drained.  Largest step: 4 bases * 128 * 128 = 2^16 per quad, so 2^15 quads fit in 32 bits.
+constexpr int QUAD_LIMIT = 30000;
+struct QuadAcc {
+    uint32_t a20[4], a30[4], aqs[4];                        // all bases of cycle j
+    uint32_t n[3][4], n20[3][4], n30[3][4], qs[3][4];       // code bit0, bit1, both
+    uint32_t nn[4], nn20[4], nn30[4], nqs[4];               // N bases
+    __device__ __forceinline__ void zero(){
+#pragma unroll
+        for(int j = 0; j < 4; ++j){
+            a20[j] = a30[j] = aqs[j] = nn[j] = nn20[j] = nn30[j] = nqs[j] = 0;
+#pragma unroll
+            for(int s = 0; s < 3; ++s) n[s][j] = n20[s][j] = n30[s][j] = qs[s][j] = 0;
+        }
+    }
+};
+__device__ __forceinline__ uint32_t dp4(uint32_t a, uint32_t b, uint32_t c){ return __dp4a(a, b, c); }
+
+// q0..q3: the thread's quality word of four reads (0 outside a read), b0..b3: their code bytes
+__device__ __forceinline__ void quad_accumulate(QuadAcc& A, uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3,
+                                                uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3){
+    const uint32_t t0 = __byte_perm(q0, q1, 0x5140), t1 = __byte_perm(q0, q1, 0x7362);
+    const uint32_t t2 = __byte_perm(q2, q3, 0x5140), t3 = __byte_perm(q2, q3, 0x7362);
+    uint32_t qT[4];                                           // qT[j]: byte r = cycle j of read r
+    qT[0] = __byte_perm(t0, t2, 0x5410); qT[1] = __byte_perm(t0, t2, 0x7632);
+    qT[2] = __byte_perm(t1, t3, 0x5410); qT[3] = __byte_perm(t1, t3, 0x7632);
+    const uint32_t wc = __byte_perm(__byte_perm(b0, b1, 0x3340), __byte_perm(b2, b3, 0x3340), 0x5410);   // byte r = codes of read r
+    const uint32_t wc1 = wc >> 1;
+    const uint32_t ones = 0x01010101u;
+    uint32_t q7[4], t7[4], s6[4];
+#pragma unroll
+    for(int j = 0; j < 4; ++j){
+        const uint32_t one = ones << (2 * j);
+        q7[j] = qT[j] & 0x7F7F7F7Fu;
+        t7[j] = (q7[j] + 0x4A4A4A4Au) & 0x80808080u;          // q >= 54 (q > '5')
+        s6[j] = q7[j] & 0x40404040u;                          // q >= 64 (q > '?')
+        uint32_t m[3];
+        m[0] = wc & one; m[1] = wc & (one << 1); m[2] = wc & wc1 & one;
+        A.a20[j] = dp4(t7[j], ones, A.a20[j]);
+        A.a30[j] = dp4(s6[j], ones, A.a30[j]);
+        A.aqs[j] = dp4(q7[j], ones, A.aqs[j]);
+#pragma unroll
+        for(int s = 0; s < 3; ++s){
+            A.n[s][j] = dp4(m[s], ones, A.n[s][j]);
+            A.n20[s][j] = dp4(t7[j], m[s], A.n20[s][j]);
+            A.n30[s][j] = dp4(s6[j], m[s], A.n30[s][j]);
+            A.qs[s][j] = dp4(q7[j], m[s], A.qs[s][j]);
+        }
+    }
+    if((qT[0] | qT[1] | qT[2] | qT[3]) & 0x80808080u){        // rare: N bases among the 16
+#pragma unroll
+        for(int j = 0; j < 4; ++j){
+            const uint32_t mn = (qT[j] >> 7) & ones;
+            A.nn[j] = dp4(mn, ones, A.nn[j]);
+            A.nn20[j] = dp4(t7[j], mn, A.nn20[j]);
+            A.nn30[j] = dp4(s6[j], mn, A.nn30[j]);
+            A.nqs[j] = dp4(q7[j], mn, A.nqs[j]);
+        }
+    }
+}
+// accumulators -> shared arrays of both Stats objects (cycles 4w .. 4w+3); v = the 76 accumulators, laid out by quad_drain
+__device__ __noinline__ void quad_drain1(const uint32_t* v, uint32_t* smA, uint32_t* smB, int C, int w){
+    for(int j = 0; j < 4; ++j){
+        const int c = 4 * w + j;
+        sm_add(smA, smB, C, KN20, S_ALL, c, v[0 + j] >> 7);
+        sm_add(smA, smB, C, KN30, S_ALL, c, v[4 + j] >> 6);
+        sm_add(smA, smB, C, KQS, S_ALL, c, v[8 + j]);
+        for(int s = 0; s < 3; ++s){
+            const int sh = 2 * j + (s == 1 ? 1 : 0);
+            sm_add(smA, smB, C, KN, S_B0 + s, c, v[12 + s * 4 + j] >> sh);
+            sm_add(smA, smB, C, KN20, S_B0 + s, c, v[24 + s * 4 + j] >> (7 + sh));
+            sm_add(smA, smB, C, KN30, S_B0 + s, c, v[36 + s * 4 + j] >> (6 + sh));
+            sm_add(smA, smB, C, KQS, S_B0 + s, c, v[48 + s * 4 + j] >> sh);
+        }
+        sm_add(smA, smB, C, KN, S_N, c, v[60 + j]);
+        sm_add(smA, smB, C, KN20, S_N, c, v[64 + j] >> 7);
+        sm_add(smA, smB, C, KN30, S_N, c, v[68 + j] >> 6);
+        sm_add(smA, smB, C, KQS, S_N, c, v[72 + j]);
+    }
+}
+__device__ __forceinline__ void quad_drain(QuadAcc& A, uint32_t* smA, uint32_t* smB, int C, int w){
+    uint32_t v[76];
+#pragma unroll
+    for(int j = 0; j < 4; ++j){
+        v[j] = A.a20[j]; v[4 + j] = A.a30[j]; v[8 + j] = A.aqs[j];
+#pragma unroll
+        for(int s = 0; s < 3; ++s){
+            v[12 + s * 4 + j] = A.n[s][j]; v[24 + s * 4 + j] = A.n20[s][j]; v[36 + s * 4 + j] = A.n30[s][j]; v[48 + s * 4 + j] = A.qs[s][j];
+        }
+        v[60 + j] = A.nn[j]; v[64 + j] = A.nn20[j]; v[68 + j] = A.nn30[j]; v[72 + j] = A.nqs[j];
+    }
+    quad_drain1(v, smA, smB, C, w);
+    A.zero();
+}
+
 template <int MODE, bool KMER>
 __global__ void __launch_bounds__(WS_THREADS, 1)
 k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
@@ -575,12 +675,13 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     uint64_t* mbar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bc + 1) + 7) & ~uintptr_t(7));
     uint64_t* full = mbar; uint64_t* ready = mbar + NS; uint64_t* freeb = mbar + 2 * NS;
     uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
-    uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 2) + 15) & ~uintptr_t(15));
+    uint32_t* blkmax = zero_word + 2;                                    // longest raw read of this block's share
     // k-mer histograms privatised per block when 3 x 4^k counters fit (k <= 6): common / pre-only / post-only
     const uint32_t kbins = (KMER && P.kmer_len <= KMER_SMEM_MAX) ? (1u << (2 * P.kmer_len)) : 0u;
-    uint32_t* khist = l2base + L2_SLOTS * THREADS;
+    uint32_t* khist = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 4) + 15) & ~uintptr_t(15));
     uint8_t* sp = reinterpret_cast<uint8_t*>(khist + 3 * kbins);
     // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
+    // clist: full-width common reads from the front, shorter common reads from the back
     const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
     const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
     const uint32_t o_b = qcap, o_off = o_b + bcap, o_len = o_off + mo, o_cl = o_len + ml, o_ol = o_cl + mo, o_cnt = o_ol + 2 * mo;
@@ -588,12 +689,11 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     const uint32_t sp32 = smem_u32(sp), zero_addr = smem_u32(zero_word);
 
     for(int i = threadIdx.x; i < 2 * statw; i += WS_THREADS) smPre[i] = 0;
-    for(int i = threadIdx.x; i < L2_SLOTS * THREADS; i += WS_THREADS) l2base[i] = 0;
     for(int i = threadIdx.x; i < (int)(3 * kbins); i += WS_THREADS) khist[i] = 0;
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], WS_TRIM); mbar_init(&freeb[s], WS_STATS); }
-        zero_word[0] = 0; zero_word[1] = 0;
+        zero_word[0] = 0; zero_word[1] = 0; blkmax[0] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -602,9 +702,23 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     const uint32_t hi = (uint32_t)min((uint64_t)B.n, (uint64_t)lo + reads_per_block);
     const int ntiles = (int)((hi - lo + T - 1) / T);
 
+    // threads per read (Wr): enough 4-cycle words for the longest raw read this block will see.  Paired-end:
+    // the batch maximum from k_trim_pe (max_cycles also has to hold merged reads, twice the raw length).
+    int Wr = W;
+    if(MODE == 0){
+        uint32_t mx = 0;
+        for(uint32_t i = lo + threadIdx.x; i < hi; i += WS_THREADS) mx = max(mx, (uint32_t)B.lengths[i]);
+#pragma unroll
+        for(int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if((threadIdx.x & 31) == 0) atomicMax(blkmax, mx);
+        __syncthreads();
+        Wr = min(W, max(8, (int)((blkmax[0] + 3u) >> 2)));
+    }else if(MODE == 1 && M.maxlen) Wr = min(W, max(8, (int)((*M.maxlen + 3u) >> 2)));
+    const uint32_t fullmin = 4u * (uint32_t)(Wr - 1);                    // a read longer than this has a byte in every word
+
     if(threadIdx.x >= WS_STATS){
         // ============================== trim warps ==============================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;\n");
         const int tt = threadIdx.x - WS_STATS;
         Tally tl = {};
         const bool fast_filter = !P.complexity_enabled;
@@ -616,7 +730,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             const uint32_t t0 = lo + (uint32_t)k * T;
             const int nt = (int)min((uint32_t)T, hi - t0);
             for(int i = tt; i < nt; i += WS_TRIM){ so[i] = B.offsets[t0 + i]; sl[i] = B.lengths[t0 + i]; }
-            if(tt == 0){ uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; }
+            if(tt == 0){ uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; c[2] = 0; }
             bar_trim();
             if(tt == 0){
                 const uint32_t a = so[0];
@@ -668,7 +782,9 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                     atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
                     if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
                     if(pass && rec.start == 0 && rec.len == dlen){
-                        clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17) | hasN << 30;
+                        const uint32_t e = doff | hasN | (dlen << 17);
+                        if(dlen > fullmin) clist[atomicAdd(&cnt[0], 1u)] = e;
+                        else clist[T - 1 - atomicAdd(&cnt[2], 1u)] = e;
                     }else{
                         const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
                         olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y | hasN << 28);
@@ -688,7 +804,9 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                         atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
                         if(own) atomicAdd(smPost + 4 * NSETS * C + plen, 1u);
                         if(own && start == 0 && plen == dlen){
-                            clist[atomicAdd(&cnt[0], 1u)] = (doff >> 4) | (dlen << 17) | hasN << 30;
+                            const uint32_t e = doff | hasN | (dlen << 17);
+                            if(dlen > fullmin) clist[atomicAdd(&cnt[0], 1u)] = e;
+                            else clist[T - 1 - atomicAdd(&cnt[2], 1u)] = e;
                         }else{
                             const Desc d = make_desc(doff, dlen, start, plen, own ? 2u : 1u);
                             olist[atomicAdd(&cnt[1], 1u)] = make_uint2(d.x, d.y | hasN << 28);
@@ -715,18 +833,14 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         counters_add_tally(bc, tl);
     }else{
         // ============================ statistics warps ============================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 152;\n");
-        // threads per read: enough words for the longest raw read of the batch when it is known
-        // (paired-end: max_cycles also has to hold merged reads, twice the raw length)
-        int Wr = W;
-        if(M.maxlen && MODE == 1) Wr = min(W, max(8, (int)((*M.maxlen + 3u) >> 2)));
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
         const int G = WS_STATS / Wr;
         const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
-        const uint32_t l2 = smem_u32(l2base) + 4 * threadIdx.x;
-        Acc1 common, preo, posto;
-        common.zero(); preo.zero(); posto.zero();
-        int usedC = 0, leftO = 255;
+        QuadAcc qa;
+        Acc1 preo, posto;
+        qa.zero(); preo.zero(); posto.zero();
+        int usedQ = 0, leftO = 255;
         for(int k = 0; k < ntiles; ++k){
             const int s = k % NS;
             const uint32_t S32 = sp32 + (uint32_t)s * stage_bytes;
@@ -736,26 +850,42 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 const uint32_t bshift = (a0 >> 2) & 15u;
                 const uint32_t sq0 = S32, sb0 = S32 + o_b + bshift;
                 const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;
-                const int nc = (int)lds32(S32 + o_cnt), no = (int)lds32(S32 + o_cnt + 4);
-                const int mine = nc > g ? (nc - g + G - 1) / G : 0;
-                if(usedC + mine > 255){ fold(common, l2); usedC = 0; }
-                usedC += mine;
-                // ---- common reads: contribute identically to pre1 and post1 ----
+                const int nc = (int)lds32(S32 + o_cnt), no = (int)lds32(S32 + o_cnt + 4), nr = (int)lds32(S32 + o_cnt + 8);
+                const uint32_t cl = S32 + o_cl;
+                // ---- common reads: contribute identically to pre1 and post1, four at a time ----
                 {
-                    const uint32_t cl = S32 + o_cl;
-                    uint32_t qraw = 0, b = 0;
-                    auto fetch = [&](int i, uint32_t& q, uint32_t& bb){
-                        const uint32_t e = lds32(cl + 4 * i);
-                        const uint32_t off = (e & 0x1FFFFu) << 4, len = (e >> 17) & 0x1FFFu;
-                        const bool in = (uint32_t)(4 * w) < len;
-                        q = lds32(in ? sqw + off : zero_addr);
-                        bb = in ? lds8(sbw + (off >> 2)) : 0u;
+                    const int nq = nc >> 2, rem = nc & 3, items = rem + nr;
+                    const int mine = (nq > g ? (nq - g + G - 1) / G : 0) + (items + 3) / 4;
+                    if(usedQ + mine > QUAD_LIMIT){ quad_drain(qa, smPre, smPost, C, w); usedQ = 0; }
+                    usedQ += mine;
+                    // full-width reads: every thread of the group has a word inside each read, no range checks
+                    uint32_t q[4] = {0, 0, 0, 0}, b[4] = {0, 0, 0, 0};
+                    auto fetch = [&](int qd){
+                        const uint4 e = lds128(cl + 16 * qd);
+                        const uint32_t o0 = e.x & 0x1FFF0u, o1 = e.y & 0x1FFF0u, o2 = e.z & 0x1FFF0u, o3 = e.w & 0x1FFF0u;
+                        q[0] = lds32(sqw + o0); q[1] = lds32(sqw + o1); q[2] = lds32(sqw + o2); q[3] = lds32(sqw + o3);
+                        b[0] = lds8(sbw + (o0 >> 2)); b[1] = lds8(sbw + (o1 >> 2)); b[2] = lds8(sbw + (o2 >> 2)); b[3] = lds8(sbw + (o3 >> 2));
                     };
-                    if(g < nc) fetch(g, qraw, b);
-                    for(int i = g; i < nc; i += G){
-                        const uint32_t qc = qraw, bcur = b;
-                        if(i + G < nc) fetch(i + G, qraw, b);
-                        acc_word(common, qc, bcur);
+                    if(g < nq) fetch(g);
+                    for(int qd = g; qd < nq; qd += G){
+                        const uint32_t c0 = q[0], c1 = q[1], c2 = q[2], c3 = q[3], d0 = b[0], d1 = b[1], d2 = b[2], d3 = b[3];
+                        if(qd + G < nq) fetch(qd + G);
+                        quad_accumulate(qa, c0, c1, c2, c3, d0, d1, d2, d3);
+                    }
+                    // the last full-width reads and the shorter ones: same reduction with range checks
+                    for(int qd = g; 4 * qd < items; qd += G){
+#pragma unroll
+                        for(int r = 0; r < 4; ++r){
+                            const int it = 4 * qd + r;
+                            uint32_t e = 0;
+                            if(it < rem) e = lds32(cl + 4 * (4 * nq + it));
+                            else if(it < items) e = lds32(cl + 4 * (T - 1 - (it - rem)));
+                            const uint32_t off = e & 0x1FFF0u, len = e >> 17;
+                            const bool in = (uint32_t)(4 * w) < len;
+                            q[r] = in ? lds32(sqw + off) : 0u;
+                            b[r] = in ? lds8(sbw + (off >> 2)) : 0u;
+                        }
+                        quad_accumulate(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
                     }
                 }
                 // ---- other reads: raw part -> pre1, shifted kept part of passing reads -> post1 ----
@@ -809,11 +939,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 if(KMER){
                     uint64_t* kpre = flat + D.L.stats_off[M.pre_obj] + D.L.s_kmer;
                     uint64_t* kpost = flat + D.L.stats_off[M.post_obj] + D.L.s_kmer;
-                    const uint32_t cl = S32 + o_cl;
                     const uint32_t kh32 = kbins ? smem_u32(khist) : 0u;
-                    for(int i = g; i < nc; i += G){
-                        const uint32_t e = lds32(cl + 4 * i);
-                        kmers_word(sq0, sb0, (e & 0x1FFFFu) << 4, 0, (e >> 17) & 0x1FFFu, (e >> 30) & 1u, w, P.kmer_len, kpre, kpost, kh32);
+                    for(int i = g; i < nc + nr; i += G){
+                        const uint32_t e = lds32(cl + 4 * (i < nc ? i : T - 1 - (i - nc)));
+                        kmers_word(sq0, sb0, e & 0x1FFF0u, 0, e >> 17, e & 1u, w, P.kmer_len, kpre, kpost, kh32);
                     }
                     for(int i = g; i < no; i += G){
                         const uint2 dc = lds64(ol + 8 * i);
@@ -828,8 +957,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             mbar_arrive(&freeb[s]);
         }
         if(active){
-            fold(common, l2);
-            drain_l2(l2, smPre, smPost, C, w);
+            quad_drain(qa, smPre, smPost, C, w);
             drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w);
         }
     }
@@ -850,8 +978,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 
 size_t ws_smem_bytes(int W, int T, int K = 0){
     const int C = 4 * W, Cp = (C + 15) & ~15;
-    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 8 + 16;
-    s += (size_t)L2_SLOTS * THREADS * 4;
+    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 16 + 16;
     if(K > 0 && K <= KMER_SMEM_MAX) s += (size_t)3 * 4 * ((size_t)1 << (2 * K));
     const size_t qcap = (size_t)T * Cp, bcap = ((qcap / 4 + 15) & ~(size_t)15) + 16;
     const size_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
@@ -903,8 +1030,10 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B){
 
 static int ws_tile(int W, int K){
     const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 2048 : 0;
-    for(int T = 256; T >= 32; T -= 16)
-        if(ws_smem_bytes(W, T, K) <= budget) return T;
+    for(int T = 512; T >= 32; T -= 16){
+        const size_t qcap = (size_t)T * ((4 * W + 15) & ~15);
+        if(qcap < (1u << 17) && ws_smem_bytes(W, T, K) <= budget) return T;      // list entries hold 17-bit tile offsets
+    }
     return 0;
 }
 
@@ -915,7 +1044,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
     if((variant == 0 || D.P.kmer_len) && ws_tile(W, D.P.kmer_len) > 0){
         const int T = ws_tile(W, D.P.kmer_len);
         int rpb = (int)((B.n + sms - 1) / sms);
-        rpb = std::min(rpb, 60000 * (WS_STATS / W));           // 16-bit level-2 count lanes: < 65536 reads per thread
+        rpb = std::min(rpb, 1 << 24);                          // 32-bit per-block sums of quality characters
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
@@ -946,7 +1075,7 @@ int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B
     const int K = D.P.kmer_len;
     const int T = ws_tile(W, K);
     int rpb = (int)((B1.n + sms - 1) / sms);
-    rpb = std::min(rpb, 60000 * (WS_STATS / W));
+    rpb = std::min(rpb, 1 << 24);
     rpb = (rpb + T - 1) / T * T;
     const int grid = (int)((B1.n + rpb - 1) / rpb);
     const int merge = D.P.merge_enabled;
