@@ -472,13 +472,12 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
 // Three staging buffers; mbarriers: full[s] (bulk copies landed), ready[s] (lists written), free[s]
 // (statistics done with the stage).  Register budget split with setmaxnreg (168 / 80).
 // ===========================================================================
-constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3;
+constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3, MS = 4;
 constexpr int KMER_SMEM_MAX = 6;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar){
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void bar_trim(){ asm volatile("bar.sync 1, %0;" :: "n"(WS_TRIM) : "memory"); }
 
 // phase 1 of one read staged in shared memory: the per-read sequence of processSingleEnd
 // (src/seprocessor.cpp:313-340); returns the record
@@ -674,18 +673,20 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     BlockCounters* bc = reinterpret_cast<BlockCounters*>(smPost + statw);
     uint64_t* mbar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bc + 1) + 7) & ~uintptr_t(7));
     uint64_t* full = mbar; uint64_t* ready = mbar + NS; uint64_t* freeb = mbar + 2 * NS;
-    uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS);
+    uint64_t* metab = mbar + 3 * NS;                                     // offsets/lengths of a tile landed
+    uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 3 * NS + MS);
     uint32_t* blkmax = zero_word + 2;                                    // longest raw read of this block's share
     // k-mer histograms privatised per block when 3 x 4^k counters fit (k <= 6): common / pre-only / post-only
     const uint32_t kbins = (KMER && P.kmer_len <= KMER_SMEM_MAX) ? (1u << (2 * P.kmer_len)) : 0u;
     uint32_t* khist = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(zero_word + 4) + 15) & ~uintptr_t(15));
     uint8_t* sp = reinterpret_cast<uint8_t*>(khist + 3 * kbins);
-    // stage layout: q[qcap] b[bcap] off[T] len[T] clist[T] olist[2T] cnt[4]
+    // stage layout: q[qcap] b[bcap] clist[T] olist[2T] cnt[4]; after the NS stages a ring of MS metadata slots off[T] len[T]
     // clist: full-width common reads from the front, shorter common reads from the back
     const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
     const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
-    const uint32_t o_b = qcap, o_off = o_b + bcap, o_len = o_off + mo, o_cl = o_len + ml, o_ol = o_cl + mo, o_cnt = o_ol + 2 * mo;
-    const uint32_t stage_bytes = o_cnt + 16;
+    const uint32_t o_b = qcap, o_cl = o_b + bcap, o_ol = o_cl + mo, o_cnt = o_ol + 2 * mo;
+    const uint32_t stage_bytes = o_cnt + 16, meta_bytes = mo + ml;
+    uint8_t* metap = sp + (size_t)NS * stage_bytes;
     const uint32_t sp32 = smem_u32(sp), zero_addr = smem_u32(zero_word);
 
     for(int i = threadIdx.x; i < 2 * statw; i += WS_THREADS) smPre[i] = 0;
@@ -693,6 +694,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], WS_TRIM); mbar_init(&freeb[s], WS_STATS); }
+        for(int s = 0; s < MS; ++s) mbar_init(&metab[s], 1);
         zero_word[0] = 0; zero_word[1] = 0; blkmax[0] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -722,42 +724,58 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         const int tt = threadIdx.x - WS_STATS;
         Tally tl = {};
         const bool fast_filter = !P.complexity_enabled;
-        // stage metadata, reset the list counters, then one thread issues the two bulk copies of tile k
-        auto prefetch = [&](int k){
-            const int s = k % NS;
-            uint8_t* S = sp + (size_t)s * stage_bytes;
-            uint32_t* so = reinterpret_cast<uint32_t*>(S + o_off); uint16_t* sl = reinterpret_cast<uint16_t*>(S + o_len);
+        // One producer thread.  Metadata (offsets, lengths) of tile k is bulk-copied into ring slot k % MS one
+        // tile ahead of the data, whose two bulk copies need the first and last offset of the tile.
+        auto issue_meta = [&](int k){
+            const int m = k % MS;
+            uint32_t* so = reinterpret_cast<uint32_t*>(metap + (size_t)m * meta_bytes);
+            uint16_t* sl = reinterpret_cast<uint16_t*>(metap + (size_t)m * meta_bytes + mo);
             const uint32_t t0 = lo + (uint32_t)k * T;
-            const int nt = (int)min((uint32_t)T, hi - t0);
-            for(int i = tt; i < nt; i += WS_TRIM){ so[i] = B.offsets[t0 + i]; sl[i] = B.lengths[t0 + i]; }
-            if(tt == 0){ uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; c[2] = 0; }
-            bar_trim();
-            if(tt == 0){
-                const uint32_t a = so[0];
-                uint64_t e = (uint64_t)so[nt - 1] + ((sl[nt - 1] + 15u) & ~15u);
-                const bool bad = (a & 15u) || e < a || e - a > qcap || e > B.total;
-                if(bad){ atomicOr(D.err, 2u); e = a; }
-                const uint32_t qbytes = (uint32_t)(e - a);
-                const uint32_t b0 = (a >> 2) & ~15u;
-                const uint32_t bbytes = qbytes ? (((uint32_t)(e >> 2) + 15u) & ~15u) - b0 : 0u;
-                mbar_expect_tx(&full[s], qbytes + bbytes);
-                if(qbytes){
-                    bulk_g2s(S, B.qual + a, qbytes, &full[s]);
-                    bulk_g2s(S + o_b, B.bases2 + b0, bbytes, &full[s]);
-                }
+            const uint32_t nt = min((uint32_t)T, hi - t0), nb = nt & ~7u;            // bulk copies move multiples of 16 bytes
+            for(uint32_t i = nb; i < nt; ++i){ so[i] = B.offsets[t0 + i]; sl[i] = B.lengths[t0 + i]; }   // last tile of the batch
+            mbar_expect_tx(&metab[m], nb * 6u);
+            if(nb){
+                bulk_g2s(so, B.offsets + t0, nb * 4u, &metab[m]);
+                bulk_g2s(sl, B.lengths + t0, nb * 2u, &metab[m]);
             }
         };
-        for(int k = 0; k < min(2, ntiles); ++k) prefetch(k);
+        auto issue_data = [&](int k){
+            const int s = k % NS, m = k % MS;
+            uint8_t* S = sp + (size_t)s * stage_bytes;
+            const uint32_t* so = reinterpret_cast<const uint32_t*>(metap + (size_t)m * meta_bytes);
+            const uint16_t* sl = reinterpret_cast<const uint16_t*>(metap + (size_t)m * meta_bytes + mo);
+            const uint32_t t0 = lo + (uint32_t)k * T;
+            const int nt = (int)min((uint32_t)T, hi - t0);
+            mbar_wait(&metab[m], (uint32_t)(k / MS) & 1u);
+            uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; c[2] = 0;
+            const uint32_t a = so[0];
+            uint64_t e = (uint64_t)so[nt - 1] + ((sl[nt - 1] + 15u) & ~15u);
+            const bool bad = (a & 15u) || e < a || e - a > qcap || e > B.total;
+            if(bad){ atomicOr(D.err, 2u); e = a; }
+            const uint32_t qbytes = (uint32_t)(e - a);
+            const uint32_t b0 = (a >> 2) & ~15u;
+            const uint32_t bbytes = qbytes ? (((uint32_t)(e >> 2) + 15u) & ~15u) - b0 : 0u;
+            mbar_expect_tx(&full[s], qbytes + bbytes);
+            if(qbytes){
+                bulk_g2s(S, B.qual + a, qbytes, &full[s]);
+                bulk_g2s(S + o_b, B.bases2 + b0, bbytes, &full[s]);
+            }
+        };
+        if(tt == 0){
+            for(int k = 0; k < min(3, ntiles); ++k) issue_meta(k);
+            for(int k = 0; k < min(2, ntiles); ++k) issue_data(k);
+        }
         for(int k = 0; k < ntiles; ++k){
             const int s = k % NS;
             uint8_t* S = sp + (size_t)s * stage_bytes;
-            const uint32_t* So = reinterpret_cast<const uint32_t*>(S + o_off);
-            const uint16_t* Sl = reinterpret_cast<const uint16_t*>(S + o_len);
+            const uint32_t* So = reinterpret_cast<const uint32_t*>(metap + (size_t)(k % MS) * meta_bytes);
+            const uint16_t* Sl = reinterpret_cast<const uint16_t*>(metap + (size_t)(k % MS) * meta_bytes + mo);
             uint32_t* clist = reinterpret_cast<uint32_t*>(S + o_cl);
             uint2* olist = reinterpret_cast<uint2*>(S + o_ol);
             uint32_t* cnt = reinterpret_cast<uint32_t*>(S + o_cnt);
             const uint32_t t0 = lo + (uint32_t)k * T;
             const int nt = (int)min((uint32_t)T, hi - t0);
+            mbar_wait(&metab[k % MS], (uint32_t)(k / MS) & 1u);
             mbar_wait(&full[s], (uint32_t)(k / NS) & 1u);
             const uint32_t a0 = So[0];
             const uint32_t bshift = (a0 >> 2) & 15u;
@@ -824,10 +842,13 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 }
             }
             mbar_arrive(&ready[s]);
-            if(k + 2 < ntiles){
+            if(tt == 0 && k + 2 < ntiles){
+                // stage of tile k+2 = stage of tile k-1: once the statistics warps released it, every thread of the block is
+                // done with tile k-1, whose metadata slot is the one tile k+3 lands in
                 const int k2 = k + 2, n2 = k2 / NS;
                 if(n2 >= 1) mbar_wait(&freeb[k2 % NS], (uint32_t)(n2 - 1) & 1u);
-                prefetch(k2);
+                if(k + 3 < ntiles) issue_meta(k + 3);
+                issue_data(k2);
             }
         }
         counters_add_tally(bc, tl);
@@ -846,7 +867,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             const uint32_t S32 = sp32 + (uint32_t)s * stage_bytes;
             mbar_wait(&ready[s], (uint32_t)(k / NS) & 1u);
             if(active){
-                const uint32_t a0 = lds32(S32 + o_off);
+                const uint32_t a0 = lds32(smem_u32(metap) + (uint32_t)(k % MS) * meta_bytes);
                 const uint32_t bshift = (a0 >> 2) & 15u;
                 const uint32_t sq0 = S32, sb0 = S32 + o_b + bshift;
                 const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;
@@ -978,11 +999,11 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 
 size_t ws_smem_bytes(int W, int T, int K = 0){
     const int C = 4 * W, Cp = (C + 15) & ~15;
-    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 3 * NS * 8 + 16 + 16;
+    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + (3 * NS + MS) * 8 + 16 + 16;
     if(K > 0 && K <= KMER_SMEM_MAX) s += (size_t)3 * 4 * ((size_t)1 << (2 * K));
     const size_t qcap = (size_t)T * Cp, bcap = ((qcap / 4 + 15) & ~(size_t)15) + 16;
     const size_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
-    s += NS * (qcap + bcap + mo + ml + mo + 2 * mo + 16);
+    s += NS * (qcap + bcap + mo + 2 * mo + 16) + MS * (mo + ml);
     return s + 128;
 }
 
@@ -1023,7 +1044,8 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B){
     const int W = (int)(D.L.max_cycles + 3) / 4;
     if(D.P.kmer_len && ws_tile(W, D.P.kmer_len) <= 0) return false;   // only the warp-specialised kernel counts k-mers
     if(W < 8 || W > THREADS) return false;
-    if((reinterpret_cast<uintptr_t>(B.qual) | reinterpret_cast<uintptr_t>(B.bases2)) & 15) return false;
+    if((reinterpret_cast<uintptr_t>(B.qual) | reinterpret_cast<uintptr_t>(B.bases2) | reinterpret_cast<uintptr_t>(B.offsets) |
+        reinterpret_cast<uintptr_t>(B.lengths)) & 15) return false;          // bulk copies: 16-byte aligned sources
     if(B.total % FQK_BATCH_PAD) return false;
     return fused_tile(W) >= THREADS / W;
 }
