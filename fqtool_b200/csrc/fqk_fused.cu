@@ -30,6 +30,7 @@
 // untouched by trimming ("common" reads); other reads use two small level-1 banks
 // (raw part for pre1, shifted kept part for post1) drained with shared atomics.
 #include <algorithm>
+#include <cstdlib>
 #include "fqk_fused.h"
 #include "fqk_pe.cuh"
 
@@ -472,7 +473,10 @@ k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __re
 // Three staging buffers; mbarriers: full[s] (bulk copies landed), ready[s] (lists written), free[s]
 // (statistics done with the stage).  Register budget split with setmaxnreg (168 / 80).
 // ===========================================================================
-constexpr int WS_STATS = 256, WS_TRIM = 256, WS_THREADS = WS_STATS + WS_TRIM, NS = 3, MS = 4;
+// Two splits: NSTAT = 128 statistics threads + 512 trim threads (single-end: phase 1 is the long pole, and it is
+// latency-bound, so it gets the warps) or 256 + 256 (statistics-only passes of paired-end batches).
+constexpr int NS = 3, MS = 4;
+constexpr int ws_trim_threads(int nstat){ return nstat == 128 ? 512 : 256; }
 constexpr int KMER_SMEM_MAX = 6;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar){
@@ -660,10 +664,11 @@ __device__ __forceinline__ void quad_drain(QuadAcc& A, uint32_t* smA, uint32_t* 
     A.zero();
 }
 
-template <int MODE, bool KMER>
-__global__ void __launch_bounds__(WS_THREADS, 1)
+template <int MODE, bool KMER, int NSTAT>
+__global__ void __launch_bounds__(NSTAT + ws_trim_threads(NSTAT), 1)
 k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
               uint64_t* __restrict__ flat, int W, int T, int reads_per_block, const StatsMode M){
+    constexpr int WS_STATS = NSTAT, WS_TRIM = (NSTAT == 128 ? 512 : 256), WS_THREADS = WS_STATS + WS_TRIM;
     extern __shared__ __align__(128) uint8_t smraw[];
     const fq_params& P = D.P;
     const int C = 4 * W, Cp = (C + 15) & ~15;
@@ -720,7 +725,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
 
     if(threadIdx.x >= WS_STATS){
         // ============================== trim warps ==============================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;\n");
+        // registers released here are what the statistics warps can claim: 512 x (96 - 72) = 128 x (192 - 96), or
+        // 256 x (128 - 80) >= 256 x (168 - 128); asking for more than was released blocks forever
+        if(NSTAT == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 72;\n");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 80;\n");
         const int tt = threadIdx.x - WS_STATS;
         Tally tl = {};
         const bool fast_filter = !P.complexity_enabled;
@@ -779,7 +787,10 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             mbar_wait(&full[s], (uint32_t)(k / NS) & 1u);
             const uint32_t a0 = So[0];
             const uint32_t bshift = (a0 >> 2) & 15u;
-            for(int i = tt; i < nt; i += WS_TRIM){
+            // read i of tile k goes to thread (i + k*T) mod WS_TRIM: when T is not a multiple of the trim threads the
+            // remainder lands on different warps tile after tile (the warps run up to two tiles apart)
+            const int rot = (int)(((uint32_t)k * (uint32_t)T) % (uint32_t)WS_TRIM);
+            for(int i = (tt - rot + WS_TRIM) % WS_TRIM; i < nt; i += WS_TRIM){
                 uint32_t doff = So[i] - a0, dlen = Sl[i];
                 const uint32_t padded = (dlen + 15u) & ~15u;
                 bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
@@ -854,7 +865,8 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         counters_add_tally(bc, tl);
     }else{
         // ============================ statistics warps ============================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
+        if(NSTAT == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 192;\n");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
         const int G = WS_STATS / Wr;
         const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
@@ -1032,11 +1044,13 @@ static int ws_tile(int W, int K = 0);
 void fused_configure(const cudaDeviceProp& prop){
     g_smem_optin = prop.sharedMemPerBlockOptin;
     cudaFuncSetAttribute(k_fused_se, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_fused_se_ws<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<0, true, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<1, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<1, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -1052,6 +1066,7 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B){
 
 static int ws_tile(int W, int K){
     const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 2048 : 0;
+    if(W > 256) return 0;                                      // a read has to fit the statistics threads of a block
     for(int T = 512; T >= 32; T -= 16){
         const size_t qcap = (size_t)T * ((4 * W + 15) & ~15);
         if(qcap < (1u << 17) && ws_smem_bytes(W, T, K) <= budget) return T;      // list entries hold 17-bit tile offsets
@@ -1070,8 +1085,15 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
-        if(D.P.kmer_len) k_fused_se_ws<0, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, D.P.kmer_len), st>>>(D, B, out, flat, W, T, rpb, M);
-        else k_fused_se_ws<0, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B, out, flat, W, T, rpb, M);
+        const size_t sm = ws_smem_bytes(W, T, D.P.kmer_len);
+        static const int split128 = getenv("FQK_WS_SPLIT128") ? 1 : 0;   // tuning aid: 4 + 16 warps measured slower than 8 + 8 on B200
+        if(W <= 128 && split128){                              // a read fits the 128 statistics threads
+            if(D.P.kmer_len) k_fused_se_ws<0, true, 128><<<grid, 640, sm, st>>>(D, B, out, flat, W, T, rpb, M);
+            else k_fused_se_ws<0, false, 128><<<grid, 640, sm, st>>>(D, B, out, flat, W, T, rpb, M);
+        }else{
+            if(D.P.kmer_len) k_fused_se_ws<0, true, 256><<<grid, 512, sm, st>>>(D, B, out, flat, W, T, rpb, M);
+            else k_fused_se_ws<0, false, 256><<<grid, 512, sm, st>>>(D, B, out, flat, W, T, rpb, M);
+        }
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     const int T = fused_tile(W);
@@ -1104,13 +1126,13 @@ int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B
     const StatsMode M1{1, 0, merge, 0, 2, r1, r2, rp, maxlen2}, M2{1, 1, merge, 1, 3, r2, r1, rp, maxlen2 ? maxlen2 + 1 : nullptr},
                     M3{2, 1, merge, 1, 2, r2, r1, rp, nullptr};
     if(K){
-        k_fused_se_ws<1, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
-        k_fused_se_ws<1, true><<<grid, WS_THREADS, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+        k_fused_se_ws<1, true, 256><<<grid, 512, ws_smem_bytes(W, T, K), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+        k_fused_se_ws<1, true, 256><<<grid, 512, ws_smem_bytes(W, T, K), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
     }else{
-        k_fused_se_ws<1, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
-        k_fused_se_ws<1, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
+        k_fused_se_ws<1, false, 256><<<grid, 512, ws_smem_bytes(W, T, 0), st>>>(D, B1, nullptr, flat, W, T, rpb, M1);
+        k_fused_se_ws<1, false, 256><<<grid, 512, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M2);
     }
     int n = 2;
-    if(merge){ k_fused_se_ws<2, false><<<grid, WS_THREADS, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
+    if(merge){ k_fused_se_ws<2, false, 256><<<grid, 512, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
     return cudaGetLastError() == cudaSuccess ? n : -1;
 }
