@@ -313,7 +313,7 @@ extern "C" const char* fqk_last_error(const fqk_ctx* c){
 }
 extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
 extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
-extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 2) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 3) return FQK_E_INVALID; c->impl = impl; return 0; }
 extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
 extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
     if(!c) return FQK_E_INVALID;

@@ -1037,6 +1037,27 @@ int fused_tile(int W){
     return 0;
 }
 
+#include "fqk_se3.cuh"
+
+// largest tile (multiple of 32 reads, whole quads per statistics group preferred) whose NS stages fit
+int v3_tile(int W){
+    const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 1024 : 0;
+    if(W > V3_STATS) return 0;
+    const int G = V3_STATS / W;
+    int fallback = 0;
+    for(int T = 256; T >= 32; T -= 32){
+        const V3L l = v3_layout(W, T);
+        if(l.qcap >= (1u << 17) || l.total + 128 > budget) continue;   // exception entries hold 17-bit tile offsets
+        if((T / 4) % G == 0) return T;
+        if(!fallback) fallback = T;
+    }
+    return fallback;
+}
+bool v3_fast_options(const fq_params& P){
+    return !P.polyg_enabled && !P.polyx_enabled && !(P.adapter_trim_enabled && P.adapter_r1_len > 0) && !P.complexity_enabled &&
+           !(P.average_quality_limit > 0) && P.trim_max_len1 <= 0 && P.low_quality_limit >= 1 && P.low_quality_limit <= 128;
+}
+
 } // namespace
 
 static int ws_tile(int W, int K = 0);
@@ -1051,6 +1072,8 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_fused_se_ws<1, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_fused_se_ws<1, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -1078,7 +1101,18 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
                     int variant){
     const int W = (int)(D.L.max_cycles + 3) / 4;
     const int G = THREADS / W;
-    if((variant == 0 || D.P.kmer_len) && ws_tile(W, D.P.kmer_len) > 0){
+    if(variant == 0 && !D.P.kmer_len && v3_tile(W) > 0){
+        const int T = v3_tile(W);
+        int rpb = (int)((B.n + sms - 1) / sms);
+        rpb = std::min(rpb, 1 << 24);                          // 32-bit per-block sums of quality characters
+        rpb = (rpb + T - 1) / T * T;
+        const int grid = (int)((B.n + rpb - 1) / rpb);
+        const size_t sm = v3_layout(W, T).total + 128;
+        if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb);
+        else k_se_v3<false><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb);
+        return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    }
+    if((variant == 0 || variant == 3 || D.P.kmer_len) && ws_tile(W, D.P.kmer_len) > 0){
         const int T = ws_tile(W, D.P.kmer_len);
         int rpb = (int)((B.n + sms - 1) / sms);
         rpb = std::min(rpb, 1 << 24);                          // 32-bit per-block sums of quality characters

@@ -4,7 +4,8 @@
 void fused_configure(const cudaDeviceProp& prop);
 bool fused_supported_se(const DevParams& D, const DevBatch& B);
 // returns the number of kernels launched, or < 0 on error
-// variant 0: warp-specialised kernel (default), 2: single-role kernel
+// variant 0: decoupled warp-specialised kernel k_se_v3 (default; k-mers fall to k_fused_se_ws), 2: single-role kernel,
+// 3: k_fused_se_ws
 int  fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, uint64_t* flat, int sms, cudaStream_t st,
                      int variant);
 
