@@ -10,9 +10,9 @@
 //     dp4a quad path, no lists, no per-read conditions), D = the parts of raw reads that do not reach the output
 //     at their raw cycle (failed reads, trimmed tails; whole read if the front was cut) and Z = kept parts of
 //     front-trimmed reads at their shifted cycle.  D and Z are short exception lists handled by the SWAR word path.
-//   * N bases never reach the statistics warps: the trim lane that owns a read adds its N bases to the N-class
-//     arrays with shared atomics (they are rare) and clears the N flag bits of the staged bytes, so the quad
-//     path has no N branch and needs no flag masking.
+//   * N bases are not the statistics warps' business: the trim lane that owns a read adds its N bases to the
+//     N-class arrays with shared atomics (they are rare), so the quad path has no N branch; it only masks the
+//     flag bit (an N base still counts in the "all" sums, as in the reference, with code 0).
 #pragma once
 
 constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = 4;
@@ -39,12 +39,23 @@ __host__ __device__ inline V3L v3_layout(int W, int T){
     return l;
 }
 
-__device__ __forceinline__ void sts8(uint32_t a, uint32_t v){ asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+// mbarrier wait that sleeps between polls: a spinning warp would take issue slots from the working warps
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns){
+    uint32_t ok = 0;
+    const uint32_t a = smem_u32(bar);
+    for(;;){
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if(ok) break;
+        __nanosleep(ns);
+    }
+}
 __device__ __forceinline__ void sts16(uint32_t a, uint32_t v){ asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void reds_add(uint32_t a, uint32_t v){ asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
 
-// SWAR word path without N handling (the staged bytes carry no N flags any more)
-__device__ __forceinline__ void acc_word_nf(Acc1& a, uint32_t q7, uint32_t b){
+// SWAR word path without the N class (filled by the trim lanes)
+__device__ __forceinline__ void acc_word_nf(Acc1& a, uint32_t qraw, uint32_t b){
+    const uint32_t q7 = qraw & 0x7F7F7F7Fu;
     const uint32_t t7 = (q7 + 0x4A4A4A4Au) >> 7;
     const uint32_t s6 = q7 >> 6;
     uint32_t x = (b | (b << 12)) & 0x000F000Fu;
@@ -116,7 +127,7 @@ __device__ __forceinline__ void quad_accumulate_nf(QuadAccNF& A, uint32_t q0, ui
 #pragma unroll
     for(int j = 0; j < 4; ++j){
         const uint32_t one = ones << (2 * j);
-        const uint32_t q7 = qT[j];
+        const uint32_t q7 = qT[j] & 0x7F7F7F7Fu;
         const uint32_t t7 = (q7 + 0x4A4A4A4Au) & 0x80808080u;
         const uint32_t s6 = q7 & 0x40404040u;
         uint32_t m[3];
@@ -227,42 +238,95 @@ __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, 
     return true;
 }
 
+// N bases of one read: Stats::statRead's contribution of the N class (src/stats.cpp:249-264).  nmask flags the
+// 32-byte granules of the read that hold an N.  sign = +1: add every N of the raw read to pre and, tentatively,
+// those inside the kept part [pstart, pstart+plen) to post at their shifted cycle; returns the number of N bases in
+// the kept part.  sign = -1: take the post contributions back (the read failed the filter after all).
+__device__ __noinline__ int n_bases_of_read(uint32_t qa, int len, uint32_t nmask, uint32_t pre32, uint32_t post32, int C,
+                                            int pstart, int plen, int sign){
+    int nkept = 0;
+    const uint32_t cellN = (uint32_t)((KN * NSETS + S_N) * C) * 4u, cell20 = (uint32_t)((KN20 * NSETS + S_N) * C) * 4u,
+                   cell30 = (uint32_t)((KN30 * NSETS + S_N) * C) * 4u, cellQ = (uint32_t)((KQS * NSETS + S_N) * C) * 4u;
+    const uint32_t one = (uint32_t)sign;
+    while(nmask){
+        const int gi = __ffs((int)nmask) - 1;
+        nmask &= nmask - 1;
+        const int nw = min(8, ((len + 3) >> 2) - 8 * gi);      // the granule may reach into the next read
+#pragma unroll 1
+        for(int h = 0; h < nw; ++h){
+            const uint32_t wv = lds32(qa + 32u * gi + 4u * h);
+            uint32_t f = wv & 0x80808080u;
+            while(f){
+                const int j = (__ffs((int)f) - 1) >> 3;
+                f &= f - 1;
+                const int p = 32 * gi + 4 * h + j;
+                const uint32_t q7 = (wv >> (8 * j)) & 0x7Fu;
+                if(sign > 0){
+                    reds_add(pre32 + cellN + 4u * p, 1u);
+                    if(q7 > 53u) reds_add(pre32 + cell20 + 4u * p, 1u);
+                    if(q7 > 63u) reds_add(pre32 + cell30 + 4u * p, 1u);
+                    reds_add(pre32 + cellQ + 4u * p, q7);
+                }
+                if(p >= pstart && p < pstart + plen){
+                    const uint32_t pc = (uint32_t)(p - pstart);
+                    ++nkept;
+                    reds_add(post32 + cellN + 4u * pc, one);
+                    if(q7 > 53u) reds_add(post32 + cell20 + 4u * pc, one);
+                    if(q7 > 63u) reds_add(post32 + cell30 + 4u * pc, one);
+                    reds_add(post32 + cellQ + 4u * pc, q7 * one);
+                }
+            }
+        }
+    }
+    return nkept;
+}
+
 // The per-read sequence of processSingleEnd (src/seprocessor.cpp:313-340) when only quality cuts, fixed trims and
 // the -q / -l filters are enabled (no polyG/polyX/adapter/complexity/average-quality/max-length).  passFilter's
-// low-quality count is taken over the whole padded read in one uniform sweep (16 quality bytes per load, byte + K
-// carries into bit 7 iff byte >= limit, one dp4a per word sums the carries); reads that were trimmed or hold an N
-// are recounted over their kept part by swar_counts.  anyN returns the OR of all raw bytes (bit 7 = N flags).
-__device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len, uint32_t& anyN){
+// low-quality count is taken over the whole padded read in one uniform sweep (16 quality bytes per load;
+// (byte | 0x80) - limit keeps bit 7 iff the quality is >= limit whatever the N flag; one dp4a per word sums the
+// flags); for trimmed reads the bases that were cut off are counted back out.  The same sweep notes which 32-byte
+// granules hold an N (nmask).  N bases go to the N class of the statistics right here (n_bases_of_read).
+__device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len, uint32_t pre32, uint32_t post32, int C){
     const uint32_t nch = ((uint32_t)len + 15u) >> 4;
-    uint32_t any = 0, ge = 0;
+    uint32_t nmask = 0, ge = 0;
     if(P.qual_filter_enabled){
-        const uint32_t K = 0x80808080u - (uint32_t)P.low_quality_limit * 0x01010101u;
+        const uint32_t L4 = (uint32_t)P.low_quality_limit * 0x01010101u;
 #pragma unroll 2
         for(uint32_t c = 0; c < nch; ++c){
             const uint4 v = lds128(qa + 16u * c);
-            any |= v.x | v.y; any |= v.z | v.w;
-            ge = dp4((v.x + K) & 0x80808080u, 0x01010101u, ge);
-            ge = dp4((v.y + K) & 0x80808080u, 0x01010101u, ge);
-            ge = dp4((v.z + K) & 0x80808080u, 0x01010101u, ge);
-            ge = dp4((v.w + K) & 0x80808080u, 0x01010101u, ge);
+            const uint32_t fl = ((v.x | v.y) | (v.z | v.w)) & 0x80808080u;
+            nmask |= (fl ? 1u : 0u) << (c >> 1);
+            ge = dp4(((v.x | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
+            ge = dp4(((v.y | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
+            ge = dp4(((v.z | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
+            ge = dp4(((v.w | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
         }
     }else{
         for(uint32_t c = 0; c < nch; ++c){
             const uint4 v = lds128(qa + 16u * c);
-            any |= v.x | v.y; any |= v.z | v.w;
+            const uint32_t fl = ((v.x | v.y) | (v.z | v.w)) & 0x80808080u;
+            nmask |= (fl ? 1u : 0u) << (c >> 1);
         }
     }
-    anyN = any & 0x80808080u;
     fq_read_result rec = {};
     int start, plen;
     const bool alive = s_trim_and_cut(P, qa, len, P.trim_front1, P.trim_tail1, start, plen);
+    int nn = 0;
+    if(nmask) nn = n_bases_of_read(qa, len, nmask, pre32, post32, C, start, alive ? plen : 0, 1);
     int result = FQK_PASS_FILTER;
     if(!alive || plen == 0) result = FQK_FAIL_LENGTH;
     else{
         if(P.qual_filter_enabled){
-            int lowq, nn = 0;
-            if(start == 0 && plen == len && !anyN) lowq = len - (int)(ge >> 7);
-            else{ int total; swar_counts(qa, start, plen, P.low_quality_limit, false, lowq, nn, total); }
+            int lowq = len - (int)(ge >> 7);               // zero padding never reaches the limit
+            const int cut = len - plen;
+            if(cut > 0){
+                if(cut <= 32){
+                    const int lim = P.low_quality_limit;
+                    for(int i = 0; i < start; ++i) lowq -= (sq7(qa, i) < lim);
+                    for(int i = start + plen; i < len; ++i) lowq -= (sq7(qa, i) < lim);
+                }else{ int n2, total; swar_counts(qa, start, plen, P.low_quality_limit, false, lowq, n2, total); }
+            }
             if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
             else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
         }
@@ -271,47 +335,11 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
             else if(P.max_read_length > 0 && plen > P.max_read_length) result = FQK_FAIL_TOO_LONG;
         }
     }
+    if(nn > 0 && result != FQK_PASS_FILTER) n_bases_of_read(qa, len, nmask, pre32, post32, C, start, plen, -1);
     rec.result = (uint8_t)result;
     if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
     else { rec.start = (uint16_t)start; rec.len = (uint16_t)plen; }
     return rec;
-}
-
-// N bases of one read: Stats::statRead's contribution of the N class (src/stats.cpp:249-264) to pre (every N of the
-// raw read) and post (those inside the kept part of a passing read, at their shifted cycle), then the flag bits
-// are cleared in the staged copy.
-__device__ __noinline__ void n_bases_of_read(uint32_t qa, int len, uint32_t pre32, uint32_t post32, int C,
-                                             int pstart, int plen /* 0: read is not in the output */){
-    const uint32_t nch = ((uint32_t)len + 15u) >> 4;
-    for(uint32_t c = 0; c < nch; ++c){
-        const uint4 v = lds128(qa + 16u * c);
-        if(!((v.x | v.y | v.z | v.w) & 0x80808080u)) continue;
-        const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for(int k = 0; k < 4; ++k){
-            uint32_t f = wv[k] & 0x80808080u;
-            while(f){
-                const int j = (__ffs((int)f) - 1) >> 3;
-                f &= f - 1;
-                const int p = (int)(16u * c) + 4 * k + j;
-                const uint32_t q7 = (wv[k] >> (8 * j)) & 0x7Fu;
-                const uint32_t cellN = (uint32_t)((KN * NSETS + S_N) * C) * 4u, cell20 = (uint32_t)((KN20 * NSETS + S_N) * C) * 4u,
-                               cell30 = (uint32_t)((KN30 * NSETS + S_N) * C) * 4u, cellQ = (uint32_t)((KQS * NSETS + S_N) * C) * 4u;
-                reds_add(pre32 + cellN + 4u * p, 1u);
-                if(q7 > 53u) reds_add(pre32 + cell20 + 4u * p, 1u);
-                if(q7 > 63u) reds_add(pre32 + cell30 + 4u * p, 1u);
-                reds_add(pre32 + cellQ + 4u * p, q7);
-                if(p >= pstart && p < pstart + plen){
-                    const uint32_t pc = (uint32_t)(p - pstart);
-                    reds_add(post32 + cellN + 4u * pc, 1u);
-                    if(q7 > 53u) reds_add(post32 + cell20 + 4u * pc, 1u);
-                    if(q7 > 63u) reds_add(post32 + cell30 + 4u * pc, 1u);
-                    reds_add(post32 + cellQ + 4u * pc, q7);
-                }
-                sts8(qa + (uint32_t)p, q7);
-            }
-        }
-    }
 }
 
 // exception entry (8 bytes): x = (tile offset)/16 | raw length << 17,  y = kept start | kept length << 13 | kind << 26
@@ -374,7 +402,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     const uint32_t t1 = t0 + T, nt1 = min((uint32_t)T, hi - t1);
                     a = B.offsets[t1]; last = B.offsets[t1 + nt1 - 1]; ll = B.lengths[t1 + nt1 - 1];
                 }
-                if(n >= 1) mbar_wait(&freeb[s], (uint32_t)(n - 1) & 1u);
+                if(n >= 1) mbar_wait_sleep(&freeb[s], (uint32_t)(n - 1) & 1u, 200);
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 uint32_t* So = reinterpret_cast<uint32_t*>(S + L.o_off);
                 uint16_t* Sl = reinterpret_cast<uint16_t*>(S + L.o_len);
@@ -415,7 +443,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 const int k = c / CH, j = c - k * CH, s = k % V3_NS;
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
-                mbar_wait(&full[s], (uint32_t)(k / V3_NS) & 1u);
+                mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 100);
                 const uint32_t* So = reinterpret_cast<const uint32_t*>(S + L.o_off);
                 const uint16_t* Sl = reinterpret_cast<const uint16_t*>(S + L.o_len);
                 const int nt = (int)lds32(S32 + L.o_cnt + 8);
@@ -427,7 +455,6 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     const uint32_t t0 = lo + (uint32_t)k * T;
                     uint32_t doff = 0, dlen = 0;
                     fq_read_result rec = {};
-                    uint32_t anyN = 0;
                     bool pass = false;
                     if(valid){
                         doff = So[i] - a0; dlen = Sl[i];
@@ -439,12 +466,16 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             sts16(S32 + L.o_len + 2u * i, 0u);                          // the statistics warps skip it
                         }
                         const uint32_t qa = S32 + doff;
-                        if(FAST) rec = fast_phase1(P, qa, (int)dlen, anyN);
+                        if(FAST) rec = fast_phase1(P, qa, (int)dlen, pre32, post32, C);
                         else{
-                            uint32_t any = 0;
-                            for(uint32_t cc = 0; cc < padded; cc += 16){ const uint4 v = lds128(qa + cc); any |= v.x | v.y | v.z | v.w; }
-                            anyN = any & 0x80808080u;
+                            uint32_t nmask = 0;
+                            for(uint32_t cc = 0; cc < padded; cc += 16){
+                                const uint4 v = lds128(qa + cc);
+                                nmask |= ((((v.x | v.y) | (v.z | v.w)) & 0x80808080u) ? 1u : 0u) << (cc >> 5);
+                            }
                             rec = phase1_read(D, S + doff, S + L.o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
+                            const bool ps = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
+                            if(nmask) n_bases_of_read(qa, (int)dlen, nmask, pre32, post32, C, rec.start, ps ? rec.len : 0, 1);
                         }
                         out[t0 + i] = rec;
                         pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
@@ -463,7 +494,6 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                         const uint32_t idx = atomicAdd(reinterpret_cast<uint32_t*>(S + L.o_cnt), 1u);
                         reinterpret_cast<uint2*>(S + L.o_ex)[idx] = make_uint2(d.x, d.y);
                     }
-                    if(valid && anyN) n_bases_of_read(S32 + doff, (int)dlen, pre32, post32, C, rec.start, pass ? rec.len : 0);
                 }
                 __syncwarp();
                 if(lane == 0) mbar_arrive(&ready[s]);
@@ -484,7 +514,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         for(int k = 0; k < ntiles; ++k){
             const int s = k % V3_NS;
             const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
-            mbar_wait(&ready[s], (uint32_t)(k / V3_NS) & 1u);
+            mbar_wait_sleep(&ready[s], (uint32_t)(k / V3_NS) & 1u, 100);
             if(active){
                 const uint32_t a0 = lds32(S32 + L.o_off);
                 const uint32_t bshift = (a0 >> 2) & 15u;
