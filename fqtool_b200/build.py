@@ -29,7 +29,7 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB] + srcs + ["-ldl"]
+    cmd = [nvcc] + NVCC_FLAGS + os.environ.get("FQK_NVCC_EXTRA", "").split() + ["-o", LIB] + srcs + ["-ldl"]
     if verbose:
         print(" ".join(cmd))
     subprocess.run(cmd, check=True)

@@ -34,6 +34,26 @@
 #include "fqk_fused.h"
 #include "fqk_pe.cuh"
 
+// Optional cycle accounting per warp role (nvcc -DFQK_V3_PROF; read back with fqk_debug_prof): development aid only.
+#ifdef FQK_V3_PROF
+__device__ unsigned long long g_v3prof[16];
+#define PROF_T(var) const long long var = clock64()
+#define PROF_ADD(slot, t0) do{ if((threadIdx.x & 31) == 0) atomicAdd(&g_v3prof[slot], (unsigned long long)(clock64() - (t0))); }while(0)
+#else
+#define PROF_T(var)
+#define PROF_ADD(slot, t0)
+#endif
+extern "C" int fqk_debug_prof(unsigned long long* out16, int reset){
+#ifdef FQK_V3_PROF
+    cudaDeviceSynchronize();
+    if(out16) cudaMemcpyFromSymbol(out16, g_v3prof, sizeof(unsigned long long) * 16);
+    if(reset){ unsigned long long z[16] = {}; cudaMemcpyToSymbol(g_v3prof, z, sizeof(z)); }
+    return 1;
+#else
+    (void)out16; (void)reset; return 0;
+#endif
+}
+
 namespace {
 
 constexpr int KN = 0, KN20 = 1, KN30 = 2, KQS = 3;                 // kinds
@@ -1108,8 +1128,9 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const size_t sm = v3_layout(W, T).total + 128;
-        if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb);
-        else k_se_v3<false><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb);
+        static const int dbg = getenv("FQK_V3_DEBUG") ? atoi(getenv("FQK_V3_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
+        if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
+        else k_se_v3<false><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     if((variant == 0 || variant == 3 || D.P.kmer_len) && ws_tile(W, D.P.kmer_len) > 0){

@@ -10,9 +10,8 @@
 //     dp4a quad path, no lists, no per-read conditions), D = the parts of raw reads that do not reach the output
 //     at their raw cycle (failed reads, trimmed tails; whole read if the front was cut) and Z = kept parts of
 //     front-trimmed reads at their shifted cycle.  D and Z are short exception lists handled by the SWAR word path.
-//   * N bases are not the statistics warps' business: the trim lane that owns a read adds its N bases to the
-//     N-class arrays with shared atomics (they are rare), so the quad path has no N branch; it only masks the
-//     flag bit (an N base still counts in the "all" sums, as in the reference, with code 0).
+//   * the trim lanes are specialised for the common option set (quality cuts + -q/-l filters): one uniform 16-byte
+//     sweep per read for passFilter's counts, four window positions per step in the cut scans.
 #pragma once
 
 constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = 4;
@@ -81,7 +80,7 @@ __device__ __forceinline__ void acc_word_nf(Acc1& a, uint32_t qraw, uint32_t b){
 // level 1 -> shared arrays of ONE Stats object, added or subtracted
 __device__ __noinline__ void drain1_signed(uint32_t* vals /*[NSETS*5]*/, uint32_t* sm, int C, int w, int neg){
     const int c0 = 4 * w;
-    for(int s = 0; s < 4; ++s){                               // the N set stays empty on this path
+    for(int s = 0; s < NSETS; ++s){
         const uint32_t n = vals[s * 5 + 0], n20 = vals[s * 5 + 1], n30 = vals[s * 5 + 2], qe = vals[s * 5 + 3], qo = vals[s * 5 + 4];
         for(int j = 0; j < 4; ++j){
             uint32_t v[4];
@@ -177,6 +176,12 @@ __device__ __forceinline__ void quad_drain_nf(QuadAccNF& A, uint32_t* smA, uint3
 // byte 0).  Same statements as dev_trim_and_cut (fqk_trim.cuh), explicit shared loads instead of generic ones.
 __device__ __forceinline__ int sq7(uint32_t qa, int i){ return (int)(lds8(qa + (uint32_t)i) & 0x7Fu); }
 __device__ __forceinline__ bool sisn(uint32_t qa, int i){ return (lds8(qa + (uint32_t)i) & 0x80u) != 0; }
+// quality values (flag masked) of positions p .. p+7 of a staged read as two words; p may be unaligned or negative
+__device__ __forceinline__ void ldq8(uint32_t qa, int p, uint32_t& lo, uint32_t& hi){
+    const uint32_t addr = qa + (uint32_t)p, a = addr & ~3u, sh = (addr & 3u) * 8u;
+    const uint32_t w0 = lds32(a), w1 = lds32(a + 4), w2 = lds32(a + 8);
+    lo = __funnelshift_r(w0, w1, sh) & 0x7F7F7F7Fu; hi = __funnelshift_r(w1, w2, sh) & 0x7F7F7F7Fu;
+}
 __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, int l, int F, int T, int& ostart, int& olen){
     const bool ef = P.cut_front_enabled, er = P.cut_right_enabled, et = P.cut_tail_enabled;
     ostart = 0; olen = l;
@@ -189,11 +194,26 @@ __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, 
         if(l - F - T - w <= 0) return false;
         const int thr = w * (33 + P.cut_front_qual);
         int s = F, sum = 0;
-        for(int i = 0; i < w - 1; ++i) sum += sq7(qa, s + i);
-        for(; s + w < l - T; ++s){
-            sum += sq7(qa, s + w - 1);
-            if(s > F) sum -= sq7(qa, s - 1);
-            if(sum >= thr) break;
+        if(w == 4){                              // four window positions per step from seven bytes
+            const int lim = l - T;
+            s = lim - 4;                         // where the scalar loop ends when no window passes
+            for(int base = F; base + 4 < lim; base += 4){
+                uint32_t lo, hi; ldq8(qa, base, lo, hi);
+                uint32_t m = 0;
+#pragma unroll
+                for(int j = 0; j < 4; ++j){
+                    const int sj = (int)dp4(j ? __funnelshift_r(lo, hi, 8 * j) : lo, 0x01010101u, 0u);
+                    m |= (sj >= thr && base + j + 4 < lim) ? (1u << j) : 0u;
+                }
+                if(m){ s = base + __ffs((int)m) - 1; break; }
+            }
+        }else{
+            for(int i = 0; i < w - 1; ++i) sum += sq7(qa, s + i);
+            for(; s + w < l - T; ++s){
+                sum += sq7(qa, s + w - 1);
+                if(s > F) sum -= sq7(qa, s - 1);
+                if(sum >= thr) break;
+            }
         }
         if(s > 0) s += w - 1;
         while(s < l && sisn(qa, s)) ++s;
@@ -223,11 +243,26 @@ __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, 
         if(l - F - T - w <= 0) return false;
         const int thr = w * (33 + P.cut_tail_qual);
         int t = l - T - 1, sum = 0;
-        for(int i = 0; i < w - 1; ++i) sum += sq7(qa, t - i);
-        for(; t - w >= F; --t){
-            sum += sq7(qa, t - w + 1);
-            if(t < l - T - 1) sum -= sq7(qa, t + 1);
-            if(sum >= thr) break;
+        if(w == 4){
+            int top = t;
+            t = F + 3;                           // where the scalar loop ends when no window passes
+            for(; top - 4 >= F; top -= 4){
+                uint32_t lo, hi; ldq8(qa, top - 6, lo, hi);
+                uint32_t m = 0;
+#pragma unroll
+                for(int j = 0; j < 4; ++j){      // candidate t = top - j: window [t-3, t] starts at byte 3-j of (lo, hi)
+                    const int sj = (int)dp4(j < 3 ? __funnelshift_r(lo, hi, 8 * (3 - j)) : lo, 0x01010101u, 0u);
+                    m |= (sj >= thr && top - j - 4 >= F) ? (1u << j) : 0u;
+                }
+                if(m){ t = top - (__ffs((int)m) - 1); break; }
+            }
+        }else{
+            for(int i = 0; i < w - 1; ++i) sum += sq7(qa, t - i);
+            for(; t - w >= F; --t){
+                sum += sq7(qa, t - w + 1);
+                if(t < l - T - 1) sum -= sq7(qa, t + 1);
+                if(sum >= thr) break;
+            }
         }
         if(t < l - 1) t -= w - 1;
         while(t >= 0 && sisn(qa, t)) --t;
@@ -238,47 +273,19 @@ __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, 
     return true;
 }
 
-// N bases of one read: Stats::statRead's contribution of the N class (src/stats.cpp:249-264).  nmask flags the
-// 32-byte granules of the read that hold an N.  sign = +1: add every N of the raw read to pre and, tentatively,
-// those inside the kept part [pstart, pstart+plen) to post at their shifted cycle; returns the number of N bases in
-// the kept part.  sign = -1: take the post contributions back (the read failed the filter after all).
-__device__ __noinline__ int n_bases_of_read(uint32_t qa, int len, uint32_t nmask, uint32_t pre32, uint32_t post32, int C,
-                                            int pstart, int plen, int sign){
-    int nkept = 0;
-    const uint32_t cellN = (uint32_t)((KN * NSETS + S_N) * C) * 4u, cell20 = (uint32_t)((KN20 * NSETS + S_N) * C) * 4u,
-                   cell30 = (uint32_t)((KN30 * NSETS + S_N) * C) * 4u, cellQ = (uint32_t)((KQS * NSETS + S_N) * C) * 4u;
-    const uint32_t one = (uint32_t)sign;
+// number of N bases of a read; nmask flags the 32-byte granules that hold one
+__device__ __forceinline__ int n_count(uint32_t qa, int len, uint32_t nmask){
+    int nn = 0;
     while(nmask){
         const int gi = __ffs((int)nmask) - 1;
         nmask &= nmask - 1;
-        const int nw = min(8, ((len + 3) >> 2) - 8 * gi);      // the granule may reach into the next read
-#pragma unroll 1
-        for(int h = 0; h < nw; ++h){
-            const uint32_t wv = lds32(qa + 32u * gi + 4u * h);
-            uint32_t f = wv & 0x80808080u;
-            while(f){
-                const int j = (__ffs((int)f) - 1) >> 3;
-                f &= f - 1;
-                const int p = 32 * gi + 4 * h + j;
-                const uint32_t q7 = (wv >> (8 * j)) & 0x7Fu;
-                if(sign > 0){
-                    reds_add(pre32 + cellN + 4u * p, 1u);
-                    if(q7 > 53u) reds_add(pre32 + cell20 + 4u * p, 1u);
-                    if(q7 > 63u) reds_add(pre32 + cell30 + 4u * p, 1u);
-                    reds_add(pre32 + cellQ + 4u * p, q7);
-                }
-                if(p >= pstart && p < pstart + plen){
-                    const uint32_t pc = (uint32_t)(p - pstart);
-                    ++nkept;
-                    reds_add(post32 + cellN + 4u * pc, one);
-                    if(q7 > 53u) reds_add(post32 + cell20 + 4u * pc, one);
-                    if(q7 > 63u) reds_add(post32 + cell30 + 4u * pc, one);
-                    reds_add(post32 + cellQ + 4u * pc, q7 * one);
-                }
-            }
-        }
+        const int nw = ((len + 3) >> 2) - 8 * gi;              // the granule may reach into the next read
+        const uint4 v0 = lds128(qa + 32u * gi), v1 = lds128(qa + 32u * gi + 16u);
+        const uint32_t wv8[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for(int h = 0; h < 8; ++h) nn += (h < nw) ? __popc(wv8[h] & 0x80808080u) : 0;
     }
-    return nkept;
+    return nn;
 }
 
 // The per-read sequence of processSingleEnd (src/seprocessor.cpp:313-340) when only quality cuts, fixed trims and
@@ -286,10 +293,11 @@ __device__ __noinline__ int n_bases_of_read(uint32_t qa, int len, uint32_t nmask
 // low-quality count is taken over the whole padded read in one uniform sweep (16 quality bytes per load;
 // (byte | 0x80) - limit keeps bit 7 iff the quality is >= limit whatever the N flag; one dp4a per word sums the
 // flags); for trimmed reads the bases that were cut off are counted back out.  The same sweep notes which 32-byte
-// granules hold an N (nmask).  N bases go to the N class of the statistics right here (n_bases_of_read).
-__device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len, uint32_t pre32, uint32_t post32, int C){
+// granules hold an N (nmask), from which passFilter's N count is taken.
+__device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len){
     const uint32_t nch = ((uint32_t)len + 15u) >> 4;
     uint32_t nmask = 0, ge = 0;
+    PROF_T(t_sweep);
     if(P.qual_filter_enabled){
         const uint32_t L4 = (uint32_t)P.low_quality_limit * 0x01010101u;
 #pragma unroll 2
@@ -309,11 +317,17 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
             nmask |= (fl ? 1u : 0u) << (c >> 1);
         }
     }
+    PROF_ADD(9, t_sweep);
     fq_read_result rec = {};
     int start, plen;
+    PROF_T(t_cut);
     const bool alive = s_trim_and_cut(P, qa, len, P.trim_front1, P.trim_tail1, start, plen);
+    PROF_ADD(10, t_cut);
     int nn = 0;
-    if(nmask) nn = n_bases_of_read(qa, len, nmask, pre32, post32, C, start, alive ? plen : 0, 1);
+    PROF_T(t_nb);
+    if(nmask && alive && P.qual_filter_enabled) nn = n_count(qa, len, nmask);
+    PROF_ADD(2, t_nb);
+    PROF_T(t_res);
     int result = FQK_PASS_FILTER;
     if(!alive || plen == 0) result = FQK_FAIL_LENGTH;
     else{
@@ -323,9 +337,9 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
             if(cut > 0){
                 if(cut <= 32){
                     const int lim = P.low_quality_limit;
-                    for(int i = 0; i < start; ++i) lowq -= (sq7(qa, i) < lim);
-                    for(int i = start + plen; i < len; ++i) lowq -= (sq7(qa, i) < lim);
-                }else{ int n2, total; swar_counts(qa, start, plen, P.low_quality_limit, false, lowq, n2, total); }
+                    for(int i = 0; i < start; ++i){ const int by = (int)lds8(qa + (uint32_t)i); lowq -= ((by & 0x7F) < lim); nn -= by >> 7; }
+                    for(int i = start + plen; i < len; ++i){ const int by = (int)lds8(qa + (uint32_t)i); lowq -= ((by & 0x7F) < lim); nn -= by >> 7; }
+                }else{ int total; swar_counts(qa, start, plen, P.low_quality_limit, false, lowq, nn, total); }
             }
             if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
             else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
@@ -335,7 +349,7 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
             else if(P.max_read_length > 0 && plen > P.max_read_length) result = FQK_FAIL_TOO_LONG;
         }
     }
-    if(nn > 0 && result != FQK_PASS_FILTER) n_bases_of_read(qa, len, nmask, pre32, post32, C, start, plen, -1);
+    PROF_ADD(12, t_res);
     rec.result = (uint8_t)result;
     if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
     else { rec.start = (uint16_t)start; rec.len = (uint16_t)plen; }
@@ -348,7 +362,7 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
 template <bool FAST>
 __global__ void __launch_bounds__(V3_THREADS, 1)
 k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
-        uint64_t* __restrict__ flat, int W, int T, int reads_per_block){
+        uint64_t* __restrict__ flat, int W, int T, int reads_per_block, int dbg){
     extern __shared__ __align__(128) uint8_t smraw[];
     const fq_params& P = D.P;
     const V3L L = v3_layout(W, T);
@@ -385,6 +399,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     }
     const int Wr = min(W, max(8, (int)((blkmax[0] + 3u) >> 2)));
     const int lane = threadIdx.x & 31;
+    PROF_T(t_block);
 
     if(threadIdx.x >= V3_STATS){
         asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
@@ -402,7 +417,10 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     const uint32_t t1 = t0 + T, nt1 = min((uint32_t)T, hi - t1);
                     a = B.offsets[t1]; last = B.offsets[t1 + nt1 - 1]; ll = B.lengths[t1 + nt1 - 1];
                 }
+                PROF_T(t_pw);
                 if(n >= 1) mbar_wait_sleep(&freeb[s], (uint32_t)(n - 1) & 1u, 200);
+                PROF_ADD(6, t_pw);
+                PROF_T(t_pi);
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 uint32_t* So = reinterpret_cast<uint32_t*>(S + L.o_off);
                 uint16_t* Sl = reinterpret_cast<uint16_t*>(S + L.o_len);
@@ -431,6 +449,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                         bulk_g2s(Sl, B.lengths + t0, nb * 2u, &full[s]);
                     }
                 }
+                PROF_ADD(7, t_pi);
             }
         }else{
             // ============================== trim warps ==============================
@@ -443,13 +462,16 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 const int k = c / CH, j = c - k * CH, s = k % V3_NS;
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
+                PROF_T(t_tw);
                 mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 100);
+                PROF_ADD(0, t_tw);
+                PROF_T(t_tc);
                 const uint32_t* So = reinterpret_cast<const uint32_t*>(S + L.o_off);
                 const uint16_t* Sl = reinterpret_cast<const uint16_t*>(S + L.o_len);
                 const int nt = (int)lds32(S32 + L.o_cnt + 8);
                 const int i = 32 * j + lane;
                 const bool valid = i < nt;
-                if(32 * j < nt){
+                if(32 * j < nt && !(dbg & 1)){
                     const uint32_t a0 = So[0];
                     const uint32_t bshift = (a0 >> 2) & 15u;
                     const uint32_t t0 = lo + (uint32_t)k * T;
@@ -466,20 +488,12 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             sts16(S32 + L.o_len + 2u * i, 0u);                          // the statistics warps skip it
                         }
                         const uint32_t qa = S32 + doff;
-                        if(FAST) rec = fast_phase1(P, qa, (int)dlen, pre32, post32, C);
-                        else{
-                            uint32_t nmask = 0;
-                            for(uint32_t cc = 0; cc < padded; cc += 16){
-                                const uint4 v = lds128(qa + cc);
-                                nmask |= ((((v.x | v.y) | (v.z | v.w)) & 0x80808080u) ? 1u : 0u) << (cc >> 5);
-                            }
-                            rec = phase1_read(D, S + doff, S + L.o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
-                            const bool ps = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
-                            if(nmask) n_bases_of_read(qa, (int)dlen, nmask, pre32, post32, C, rec.start, ps ? rec.len : 0, 1);
-                        }
+                        if(FAST) rec = fast_phase1(P, qa, (int)dlen);
+                        else rec = phase1_read(D, S + doff, S + L.o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
                         out[t0 + i] = rec;
                         pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
                     }
+                    PROF_T(t_tt);
                     // run counters, aggregated over the warp where every lane agrees (the usual case)
                     const unsigned mv = __ballot_sync(0xffffffffu, valid), mp = __ballot_sync(0xffffffffu, pass);
                     if(lane == 0 && mp) atomicAdd(&bc->filter[FQK_PASS_FILTER], (uint32_t)__popc(mp));
@@ -494,8 +508,10 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                         const uint32_t idx = atomicAdd(reinterpret_cast<uint32_t*>(S + L.o_cnt), 1u);
                         reinterpret_cast<uint2*>(S + L.o_ex)[idx] = make_uint2(d.x, d.y);
                     }
+                    PROF_ADD(11, t_tt);
                 }
                 __syncwarp();
+                PROF_ADD(1, t_tc);
                 if(lane == 0) mbar_arrive(&ready[s]);
             }
             counters_add_tally(bc, tl);
@@ -506,7 +522,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         const int G = V3_STATS / Wr;
         const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
-        QuadAccNF qa;
+        QuadAcc qa;
         Acc1 dsub, zadd;
         qa.zero(); dsub.zero(); zadd.zero();
         int usedQ = 0, leftO = 255;
@@ -514,15 +530,18 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         for(int k = 0; k < ntiles; ++k){
             const int s = k % V3_NS;
             const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
+            PROF_T(t_sw);
             mbar_wait_sleep(&ready[s], (uint32_t)(k / V3_NS) & 1u, 100);
-            if(active){
+            PROF_ADD(3, t_sw);
+            PROF_T(t_sp);
+            if(active && !(dbg & 2)){
                 const uint32_t a0 = lds32(S32 + L.o_off);
                 const uint32_t bshift = (a0 >> 2) & 15u;
                 const uint32_t sq0 = S32, sb0 = S32 + L.o_b + bshift;
                 const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;
                 const int nex = (int)lds32(S32 + L.o_cnt), uniform = (int)lds32(S32 + L.o_cnt + 4), nt = (int)lds32(S32 + L.o_cnt + 8);
                 const int mine = (quads_per_tile + G - 1) / G;
-                if(usedQ + mine > QUAD_LIMIT){ quad_drain_nf(qa, smPre, smPost, C, w); usedQ = 0; }
+                if(usedQ + mine > QUAD_LIMIT){ quad_drain(qa, smPre, smPost, C, w); usedQ = 0; }
                 usedQ += mine;
                 uint32_t q[4], b[4];
                 if(uniform){
@@ -539,7 +558,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     for(int qd = g; qd < quads_per_tile; qd += G){
                         const uint32_t c0 = q[0], c1_ = q[1], c2 = q[2], c3 = q[3], d0 = b[0], d1 = b[1], d2 = b[2], d3 = b[3];
                         if(qd + G < quads_per_tile) fetch();
-                        quad_accumulate_nf(qa, c0, c1_, c2, c3, d0, d1, d2, d3);
+                        quad_accumulate(qa, c0, c1_, c2, c3, d0, d1, d2, d3);
                     }
                 }else{
                     const int nq = (nt + 3) >> 2;
@@ -554,9 +573,10 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             q[r] = in ? lds32(sqw + of[r]) : 0u;
                             b[r] = in ? lds8(sbw + (of[r] >> 2)) : 0u;
                         }
-                        quad_accumulate_nf(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
+                        quad_accumulate(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
                     }
                 }
+                PROF_ADD(4, t_sp);
                 // ---- exceptions: D is subtracted from post1, Z is added to it ----
                 const uint32_t ex = S32 + L.o_ex;
                 for(int i = g; i < nex; i += G){
@@ -568,7 +588,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     if(c0 < len && c0 + 4 > d0){
                         uint32_t q2 = lds32(sqw + off), b2 = lds8(sbw + (off >> 2));
                         if(c0 < d0){ const uint32_t nb = d0 - c0; q2 &= 0xFFFFFFFFu << (8 * nb); b2 &= 0xFFu << (2 * nb); }
-                        acc_word_nf(dsub, q2, b2);
+                        acc_word(dsub, q2, b2);
                     }
                     if(kind == 2 && start > 0){
                         const int nv = (int)plen - 4 * w;
@@ -581,21 +601,25 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             const uint32_t e0 = lds8(sb0 + (p >> 2)), e1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
                             uint32_t b2 = ((e0 | (e1 << 8)) >> (2 * sh)) & 0xFF;
                             if(nv < 4){ q2 &= (1u << (8 * nv)) - 1u; b2 &= (1u << (2 * nv)) - 1u; }
-                            acc_word_nf(zadd, q2, b2);
+                            acc_word(zadd, q2, b2);
                         }
                     }
                     if(--leftO == 0){ drain_l1_signed(dsub, smPost, C, w, 1); drain_l1_signed(zadd, smPost, C, w, 0); leftO = 255; }
                 }
             }
             __syncwarp();
+            PROF_ADD(5, t_sp);
             if(lane == 0) mbar_arrive(&freeb[s]);
         }
         if(active){
-            quad_drain_nf(qa, smPre, smPost, C, w);
+            quad_drain(qa, smPre, smPost, C, w);
             drain_l1_signed(dsub, smPost, C, w, 1); drain_l1_signed(zadd, smPost, C, w, 0);
         }
     }
     __syncthreads();
+#ifdef FQK_V3_PROF
+    if(threadIdx.x == 0) atomicAdd(&g_v3prof[8], (unsigned long long)(clock64() - t_block));
+#endif
     retire(smPre, C, D.L, flat + D.L.stats_off[0]);
     retire(smPost, C, D.L, flat + D.L.stats_off[2]);
     counters_flush(bc, D.L, flat);

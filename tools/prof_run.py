@@ -33,5 +33,16 @@ for _ in range(reps):
 eng.sync()
 ms, cnt = eng.kernel_times()
 print("kernel ms per launch [all, trim, stats, dup, fused]:", [round(m / max(c, 1), 4) for m, c in zip(ms, cnt)])
+import ctypes
+if hasattr(eng.lib, "fqk_debug_prof"):
+    buf = (ctypes.c_ulonglong * 16)()
+    if eng.lib.fqk_debug_prof(buf, 0):
+        names = ["trim wait full", "trim chunk", "trim n_bases", "stats wait ready", "stats P", "stats exceptions", "producer wait free",
+                 "producer issue", "block total", "trim sweep", "trim cut", "trim tail", "trim result", "-", "-", "-"]
+        tot = buf[8] or 1
+        print("cycle accounting (sum over warps / block total):")
+        for nm, v in zip(names, buf):
+            if v:
+                print(f"  {nm:20s} {v / tot:8.3f}")
 flat = eng.finalize()
 print("reads counted:", int(flat[eng.layout.stats_off[0] + eng.layout.s_reads]))
