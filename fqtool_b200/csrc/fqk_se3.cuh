@@ -273,6 +273,10 @@ __device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, 
     return true;
 }
 
+// passFilter's counts over a sub-range of a staged read (the parts a trim removed)
+__device__ __noinline__ void range_counts(uint32_t qa, int from, int n, int lim, int& lowq, int& nn){
+    int total; swar_counts(qa, from, n, lim, false, lowq, nn, total);
+}
 // number of N bases of a read; nmask flags the 32-byte granules that hold one
 __device__ __forceinline__ int n_count(uint32_t qa, int len, uint32_t nmask){
     int nn = 0;
@@ -296,7 +300,7 @@ __device__ __forceinline__ int n_count(uint32_t qa, int len, uint32_t nmask){
 // granules hold an N (nmask), from which passFilter's N count is taken.
 __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len){
     const uint32_t nch = ((uint32_t)len + 15u) >> 4;
-    uint32_t nmask = 0, ge = 0;
+    uint32_t nmask = 0, ge = 0, ge2 = 0;
     PROF_T(t_sweep);
     if(P.qual_filter_enabled){
         const uint32_t L4 = (uint32_t)P.low_quality_limit * 0x01010101u;
@@ -306,10 +310,11 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
             const uint32_t fl = ((v.x | v.y) | (v.z | v.w)) & 0x80808080u;
             nmask |= (fl ? 1u : 0u) << (c >> 1);
             ge = dp4(((v.x | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
-            ge = dp4(((v.y | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
+            ge2 = dp4(((v.y | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge2);
             ge = dp4(((v.z | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
-            ge = dp4(((v.w | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge);
+            ge2 = dp4(((v.w | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge2);
         }
+        ge += ge2;
     }else{
         for(uint32_t c = 0; c < nch; ++c){
             const uint4 v = lds128(qa + 16u * c);
@@ -333,13 +338,9 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
     else{
         if(P.qual_filter_enabled){
             int lowq = len - (int)(ge >> 7);               // zero padding never reaches the limit
-            const int cut = len - plen;
-            if(cut > 0){
-                if(cut <= 32){
-                    const int lim = P.low_quality_limit;
-                    for(int i = 0; i < start; ++i){ const int by = (int)lds8(qa + (uint32_t)i); lowq -= ((by & 0x7F) < lim); nn -= by >> 7; }
-                    for(int i = start + plen; i < len; ++i){ const int by = (int)lds8(qa + (uint32_t)i); lowq -= ((by & 0x7F) < lim); nn -= by >> 7; }
-                }else{ int total; swar_counts(qa, start, plen, P.low_quality_limit, false, lowq, nn, total); }
+            if(plen < len){                                // take the bases that were cut off back out
+                if(start > 0){ int l1, n1; range_counts(qa, 0, start, P.low_quality_limit, l1, n1); lowq -= l1; nn -= n1; }
+                if(start + plen < len){ int l2, n2; range_counts(qa, start + plen, len - start - plen, P.low_quality_limit, l2, n2); lowq -= l2; nn -= n2; }
             }
             if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
             else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
@@ -354,6 +355,25 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
     if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
     else { rec.start = (uint16_t)start; rec.len = (uint16_t)plen; }
     return rec;
+}
+
+// one 4-cycle word of a front-trimmed read's kept part, added to post1 at cycles 4w.. by shared atomics (rare: the
+// reference's cut_front / fixed front trim moved the read): the set representation of acc_word, one base at a time
+__device__ __noinline__ void z_word_atomic(uint32_t qraw, uint32_t b, int nv, uint32_t* sm, int C, int w){
+    for(int j = 0; j < 4 && j < nv; ++j){
+        const uint32_t by = (qraw >> (8 * j)) & 0xFFu, q7 = by & 0x7Fu, code = (b >> (2 * j)) & 3u;
+        const int c = 4 * w + j;
+        uint32_t sets = 1u << S_ALL;
+        if(by & 0x80u) sets |= 1u << S_N;
+        else{ if(code & 1u) sets |= 1u << S_B0; if(code & 2u) sets |= 1u << S_B1; if(code == 3u) sets |= 1u << S_B01; }
+        for(int s = 0; s < NSETS; ++s){
+            if(!((sets >> s) & 1u)) continue;
+            if(s) atomicAdd(sm_cell(sm, C, KN, s) + c, 1u);
+            if(q7 > 53u) atomicAdd(sm_cell(sm, C, KN20, s) + c, 1u);
+            if(q7 > 63u) atomicAdd(sm_cell(sm, C, KN30, s) + c, 1u);
+            atomicAdd(sm_cell(sm, C, KQS, s) + c, q7);
+        }
+    }
 }
 
 // exception entry (8 bytes): x = (tile offset)/16 | raw length << 17,  y = kept start | kept length << 13 | kind << 26
@@ -523,8 +543,8 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
         const bool active = g < G;
         QuadAcc qa;
-        Acc1 dsub, zadd;
-        qa.zero(); dsub.zero(); zadd.zero();
+        Acc1 dsub;
+        qa.zero(); dsub.zero();
         int usedQ = 0, leftO = 255;
         const int quads_per_tile = T / 4;
         for(int k = 0; k < ntiles; ++k){
@@ -549,16 +569,27 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     const uint32_t qstep = 4u * (uint32_t)G * (uint32_t)Cp, bstep = (uint32_t)G * (uint32_t)Cp;
                     uint32_t aq = sqw + 4u * (uint32_t)g * (uint32_t)Cp, ab = sbw + (uint32_t)g * (uint32_t)Cp;
                     const uint32_t c1 = (uint32_t)Cp, c1b = (uint32_t)Cp >> 2;
-                    auto fetch = [&](){
+                    // two register sets, loads of a quad issued one accumulate ahead (no register copies)
+                    uint32_t q2[4], b2[4];
+                    auto fetchA = [&](){
                         q[0] = lds32(aq); q[1] = lds32(aq + c1); q[2] = lds32(aq + 2 * c1); q[3] = lds32(aq + 3 * c1);
                         b[0] = lds8(ab); b[1] = lds8(ab + c1b); b[2] = lds8(ab + 2 * c1b); b[3] = lds8(ab + 3 * c1b);
                         aq += qstep; ab += bstep;
                     };
-                    if(g < quads_per_tile) fetch();
-                    for(int qd = g; qd < quads_per_tile; qd += G){
-                        const uint32_t c0 = q[0], c1_ = q[1], c2 = q[2], c3 = q[3], d0 = b[0], d1 = b[1], d2 = b[2], d3 = b[3];
-                        if(qd + G < quads_per_tile) fetch();
-                        quad_accumulate(qa, c0, c1_, c2, c3, d0, d1, d2, d3);
+                    auto fetchB = [&](){
+                        q2[0] = lds32(aq); q2[1] = lds32(aq + c1); q2[2] = lds32(aq + 2 * c1); q2[3] = lds32(aq + 3 * c1);
+                        b2[0] = lds8(ab); b2[1] = lds8(ab + c1b); b2[2] = lds8(ab + 2 * c1b); b2[3] = lds8(ab + 3 * c1b);
+                        aq += qstep; ab += bstep;
+                    };
+                    if(g < quads_per_tile) fetchA();
+                    if(g + G < quads_per_tile) fetchB();
+                    for(int qd = g; qd < quads_per_tile; qd += 2 * G){
+                        quad_accumulate(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
+                        if(qd + 2 * G < quads_per_tile) fetchA();
+                        if(qd + G < quads_per_tile){
+                            quad_accumulate(qa, q2[0], q2[1], q2[2], q2[3], b2[0], b2[1], b2[2], b2[3]);
+                            if(qd + 3 * G < quads_per_tile) fetchB();
+                        }
                     }
                 }else{
                     const int nq = (nt + 3) >> 2;
@@ -600,11 +631,10 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             uint32_t q2 = __funnelshift_r(w0, w1, sh * 8);
                             const uint32_t e0 = lds8(sb0 + (p >> 2)), e1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
                             uint32_t b2 = ((e0 | (e1 << 8)) >> (2 * sh)) & 0xFF;
-                            if(nv < 4){ q2 &= (1u << (8 * nv)) - 1u; b2 &= (1u << (2 * nv)) - 1u; }
-                            acc_word(zadd, q2, b2);
+                            z_word_atomic(q2, b2, nv, smPost, C, w);
                         }
                     }
-                    if(--leftO == 0){ drain_l1_signed(dsub, smPost, C, w, 1); drain_l1_signed(zadd, smPost, C, w, 0); leftO = 255; }
+                    if(--leftO == 0){ drain_l1_signed(dsub, smPost, C, w, 1); leftO = 255; }
                 }
             }
             __syncwarp();
@@ -613,7 +643,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         }
         if(active){
             quad_drain(qa, smPre, smPost, C, w);
-            drain_l1_signed(dsub, smPost, C, w, 1); drain_l1_signed(zadd, smPost, C, w, 0);
+            drain_l1_signed(dsub, smPost, C, w, 1);
         }
     }
     __syncthreads();
