@@ -37,8 +37,11 @@
 // Optional cycle accounting per warp role (nvcc -DFQK_V3_PROF; read back with fqk_debug_prof): development aid only.
 #ifdef FQK_V3_PROF
 __device__ unsigned long long g_v3prof[16];
+// per block accumulators in dynamic shared memory, flushed once at the end (global atomics per probe distort the timing)
+__device__ __forceinline__ unsigned long long* v3prof_base(){ extern __shared__ __align__(128) uint8_t smraw[]; return reinterpret_cast<unsigned long long*>(smraw); }
+#define s_v3prof v3prof_base()
 #define PROF_T(var) const long long var = clock64()
-#define PROF_ADD(slot, t0) do{ if((threadIdx.x & 31) == 0) atomicAdd(&g_v3prof[slot], (unsigned long long)(clock64() - (t0))); }while(0)
+#define PROF_ADD(slot, t0) do{ if((threadIdx.x & 31) == 0) atomicAdd(&s_v3prof[slot], (unsigned long long)(clock64() - (t0))); }while(0)
 #else
 #define PROF_T(var)
 #define PROF_ADD(slot, t0)

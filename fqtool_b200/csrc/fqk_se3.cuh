@@ -15,14 +15,14 @@
 #pragma once
 
 constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = 4;
-constexpr int V3_WORKERS = 7;                      // trim warps 0..6 work on chunks, warp 7 is the copy producer
+constexpr int V3_WORKERS = V3_TRIM / 32 - 1;                      // trim warps 0..6 work on chunks, warp 7 is the copy producer
 
 struct V3L { uint32_t statw, o_bc, o_bar, o_zero, o_stage, qcap, o_b, o_off, o_len, o_ex, o_cnt, stage_bytes, total; };
 __host__ __device__ inline V3L v3_layout(int W, int T){
     V3L l;
     const uint32_t C = 4u * (uint32_t)W, Cp = (C + 15u) & ~15u;
     l.statw = 4 * NSETS * C + C + 1;
-    uint32_t o = 2 * l.statw * 4; o = (o + 7u) & ~7u;
+    uint32_t o = 128 + 2 * l.statw * 4; o = (o + 7u) & ~7u;     // first 128 bytes: cycle accounting of FQK_V3_PROF builds
     l.o_bc = o; o += (uint32_t)sizeof(BlockCounters); o = (o + 7u) & ~7u;
     l.o_bar = o; o += 3 * V3_NS * 8;
     l.o_zero = o; o += 16;
@@ -387,17 +387,21 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     const fq_params& P = D.P;
     const V3L L = v3_layout(W, T);
     const int C = 4 * W, Cp = (C + 15) & ~15;
-    uint32_t* smPre = reinterpret_cast<uint32_t*>(smraw);
+    uint32_t* smPre = reinterpret_cast<uint32_t*>(smraw + 128);
     uint32_t* smPost = smPre + L.statw;
     BlockCounters* bc = reinterpret_cast<BlockCounters*>(smraw + L.o_bc);
     uint64_t* full = reinterpret_cast<uint64_t*>(smraw + L.o_bar);
     uint64_t* ready = full + V3_NS; uint64_t* freeb = ready + V3_NS;
     uint32_t* blkmax = reinterpret_cast<uint32_t*>(smraw + L.o_zero);
+
     uint8_t* sp = smraw + L.o_stage;
     const uint32_t sp32 = smem_u32(sp);
     const int CH = T / 32;                                       // chunks per tile (T is a multiple of 32)
 
     for(int i = threadIdx.x; i < (int)(2 * L.statw); i += V3_THREADS) smPre[i] = 0;
+#ifdef FQK_V3_PROF
+    if(threadIdx.x < 16) s_v3prof[threadIdx.x] = 0;
+#endif
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < V3_NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], (uint32_t)CH); mbar_init(&freeb[s], V3_STATS / 32); }
@@ -610,17 +614,25 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 PROF_ADD(4, t_sp);
                 // ---- exceptions: D is subtracted from post1, Z is added to it ----
                 const uint32_t ex = S32 + L.o_ex;
+                const uint32_t c0 = 4u * (uint32_t)w;
+                // descriptor and word of the next entry are loaded before the current one is reduced
+                auto exfetch = [&](int i, uint2& d, uint32_t& qq, uint32_t& bb){
+                    d = lds64(ex + 8 * i);
+                    const uint32_t off = (d.x & 0x1FFFFu) << 4, len = d.x >> 17;
+                    const uint32_t d0 = (((d.y >> 26) & 3u) == 2u && (d.y & 0x1FFFu) == 0u) ? ((d.y >> 13) & 0x1FFFu) : 0u;   // D = raw positions [d0, len)
+                    const bool in = c0 < len && c0 + 4 > d0;
+                    qq = in ? lds32(sqw + off) : 0u;
+                    bb = in ? lds8(sbw + (off >> 2)) : 0u;
+                    if(c0 < d0){ const uint32_t nb = min(d0 - c0, 4u); qq = nb >= 4 ? 0u : (qq & (0xFFFFFFFFu << (8 * nb))); bb &= 0xFFu << (2 * nb); }
+                };
+                uint2 dn = make_uint2(0u, 0u); uint32_t qn = 0, bn = 0;
+                if(g < nex) exfetch(g, dn, qn, bn);
                 for(int i = g; i < nex; i += G){
-                    const uint2 dc = lds64(ex + 8 * i);
-                    const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = (dc.y >> 26) & 3u;
+                    const uint2 dc = dn; const uint32_t qc = qn, bcur = bn;
+                    if(i + G < nex) exfetch(i + G, dn, qn, bn);
+                    const uint32_t off = (dc.x & 0x1FFFFu) << 4, kind = (dc.y >> 26) & 3u;
                     const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
-                    const uint32_t c0 = 4u * (uint32_t)w;
-                    const uint32_t d0 = (kind == 2 && start == 0) ? plen : 0u;          // D = raw positions [d0, len)
-                    if(c0 < len && c0 + 4 > d0){
-                        uint32_t q2 = lds32(sqw + off), b2 = lds8(sbw + (off >> 2));
-                        if(c0 < d0){ const uint32_t nb = d0 - c0; q2 &= 0xFFFFFFFFu << (8 * nb); b2 &= 0xFFu << (2 * nb); }
-                        acc_word(dsub, q2, b2);
-                    }
+                    if(qc) acc_word(dsub, qc, bcur);                 // a word inside a read never has four zero quality bytes
                     if(kind == 2 && start > 0){
                         const int nv = (int)plen - 4 * w;
                         if(nv > 0){
@@ -648,7 +660,9 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     }
     __syncthreads();
 #ifdef FQK_V3_PROF
-    if(threadIdx.x == 0) atomicAdd(&g_v3prof[8], (unsigned long long)(clock64() - t_block));
+    if(threadIdx.x == 0) atomicAdd(&s_v3prof[8], (unsigned long long)(clock64() - t_block));
+    __syncthreads();
+    if(threadIdx.x < 16) atomicAdd(&g_v3prof[threadIdx.x], s_v3prof[threadIdx.x]);
 #endif
     retire(smPre, C, D.L, flat + D.L.stats_off[0]);
     retire(smPost, C, D.L, flat + D.L.stats_off[2]);
