@@ -15,6 +15,9 @@
 #pragma once
 
 constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = 4;
+#ifndef V3_STATS_HIGH
+#define V3_STATS_HIGH 0
+#endif
 constexpr int V3_WORKERS = V3_TRIM / 32 - 1;                      // trim warps 0..6 work on chunks, warp 7 is the copy producer
 
 struct V3L { uint32_t statw, o_bc, o_bar, o_zero, o_stage, qcap, o_b, o_off, o_len, o_ex, o_cnt, stage_bytes, total; };
@@ -38,15 +41,16 @@ __host__ __device__ inline V3L v3_layout(int W, int T){
     return l;
 }
 
-// mbarrier wait that sleeps between polls: a spinning warp would take issue slots from the working warps
+// mbarrier wait for the long waits between roles: try_wait with a suspend-time hint parks the thread in hardware
+// until the phase completes (or the hint expires), so a waiting warp issues almost nothing; a spinning warp would
+// take issue slots from the working warps (12 % of all instructions in the first version)
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns){
     uint32_t ok = 0;
     const uint32_t a = smem_u32(bar);
     for(;;){
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity), "r"(ns) : "memory");
         if(ok) break;
-        __nanosleep(ns);
     }
 }
 __device__ __forceinline__ void sts16(uint32_t a, uint32_t v){ asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
@@ -425,9 +429,12 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     const int lane = threadIdx.x & 31;
     PROF_T(t_block);
 
-    if(threadIdx.x >= V3_STATS){
+    // role of a thread: the statistics warps take the high warp ids (V3_STATS_HIGH) or the low ones
+    const bool is_trim = V3_STATS_HIGH ? (threadIdx.x < V3_TRIM) : (threadIdx.x >= V3_STATS);
+    const int rtid = V3_STATS_HIGH ? (is_trim ? threadIdx.x : threadIdx.x - V3_TRIM) : (is_trim ? threadIdx.x - V3_STATS : threadIdx.x);
+    if(is_trim){
         asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
-        const int tw = (threadIdx.x - V3_STATS) >> 5;
+        const int tw = rtid >> 5;
         if(tw == V3_WORKERS){
             // ============================== copy producer ==============================
             uint32_t a = 0, last = 0, ll = 0;
@@ -442,7 +449,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     a = B.offsets[t1]; last = B.offsets[t1 + nt1 - 1]; ll = B.lengths[t1 + nt1 - 1];
                 }
                 PROF_T(t_pw);
-                if(n >= 1) mbar_wait_sleep(&freeb[s], (uint32_t)(n - 1) & 1u, 200);
+                if(n >= 1) mbar_wait_sleep(&freeb[s], (uint32_t)(n - 1) & 1u, 20000);
                 PROF_ADD(6, t_pw);
                 PROF_T(t_pi);
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
@@ -487,7 +494,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
                 PROF_T(t_tw);
-                mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 100);
+                mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 20000);
                 PROF_ADD(0, t_tw);
                 PROF_T(t_tc);
                 const uint32_t* So = reinterpret_cast<const uint32_t*>(S + L.o_off);
@@ -544,7 +551,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
         // ============================ statistics warps ============================
         asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
         const int G = V3_STATS / Wr;
-        const int g = threadIdx.x / Wr, w = threadIdx.x - g * Wr;
+        const int g = rtid / Wr, w = rtid - g * Wr;
         const bool active = g < G;
         QuadAcc qa;
         Acc1 dsub;
@@ -555,7 +562,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             const int s = k % V3_NS;
             const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
             PROF_T(t_sw);
-            mbar_wait_sleep(&ready[s], (uint32_t)(k / V3_NS) & 1u, 100);
+            mbar_wait_sleep(&ready[s], (uint32_t)(k / V3_NS) & 1u, 20000);
             PROF_ADD(3, t_sw);
             PROF_T(t_sp);
             if(active && !(dbg & 2)){
