@@ -260,7 +260,8 @@ def main():
         peaks = json.load(open(pk))
     peak = peaks.get("hbm_gbs", 6650.0)
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    names = {abi.T_TRIM: "k_trim", abi.T_STATS: "k_stats", abi.T_DUP: "k_dup", abi.T_FUSED: "k_fused_se_ws"}
+    fused_name = "k_se_v3" if (not c["paired"] and not opt.to_params().kmer_len and a.impl == "b200") else "k_fused_se_ws"
+    names = {abi.T_TRIM: "k_trim", abi.T_STATS: "k_stats", abi.T_DUP: "k_dup", abi.T_FUSED: fused_name}
     dom = max(names, key=lambda s: kms[s])
     per_launch_ms = kms[dom] / max(kn[dom], 1)
     alg = workload.algorithmic_bytes(cfg, min(BATCH_READS, reads))
