@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libfqk.so")
+LIB_PATH = os.environ.get("FQK_LIB") or os.path.join(HERE, "csrc", "libfqk.so")   # FQK_LIB: A/B builds of the same library (development aid)
 
 FQK_ABI_VERSION = 1
 FQK_MAX_ADAPTER = 128
