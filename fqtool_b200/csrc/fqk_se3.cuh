@@ -302,7 +302,9 @@ __device__ __forceinline__ int n_count(uint32_t qa, int len, uint32_t nmask){
 // (byte | 0x80) - limit keeps bit 7 iff the quality is >= limit whatever the N flag; one dp4a per word sums the
 // flags); for trimmed reads the bases that were cut off are counted back out.  The same sweep notes which 32-byte
 // granules hold an N (nmask), from which passFilter's N count is taken.
-__device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32_t qa, int len){
+struct Fast1 { uint32_t ge; int nn, start, plen; bool alive; };
+// first half: the sweep, trimAndCut and the N count of the whole read
+__device__ __forceinline__ Fast1 fast_phase1a(const fq_params& P, uint32_t qa, int len){
     const uint32_t nch = ((uint32_t)len + 15u) >> 4;
     uint32_t nmask = 0, ge = 0, ge2 = 0;
     PROF_T(t_sweep);
@@ -327,24 +329,32 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
         }
     }
     PROF_ADD(9, t_sweep);
-    fq_read_result rec = {};
-    int start, plen;
+    Fast1 f;
+    f.ge = ge; f.nn = 0;
     PROF_T(t_cut);
-    const bool alive = s_trim_and_cut(P, qa, len, P.trim_front1, P.trim_tail1, start, plen);
+    f.alive = s_trim_and_cut(P, qa, len, P.trim_front1, P.trim_tail1, f.start, f.plen);
     PROF_ADD(10, t_cut);
-    int nn = 0;
     PROF_T(t_nb);
-    if(nmask && alive && P.qual_filter_enabled) nn = n_count(qa, len, nmask);
+    if(nmask && f.alive && P.qual_filter_enabled) f.nn = n_count(qa, len, nmask);
     PROF_ADD(2, t_nb);
+    return f;
+}
+// second half: passFilter's decision.  tail_done: the counts of the cut-off tail (tl, tn) were taken by the warp
+__device__ __forceinline__ fq_read_result fast_phase1b(const fq_params& P, uint32_t qa, int len, const Fast1& f,
+                                                       bool tail_done, int tl, int tn){
+    fq_read_result rec = {};
+    const int start = f.start, plen = f.plen;
+    int nn = f.nn;
     PROF_T(t_res);
     int result = FQK_PASS_FILTER;
-    if(!alive || plen == 0) result = FQK_FAIL_LENGTH;
+    if(!f.alive || plen == 0) result = FQK_FAIL_LENGTH;
     else{
         if(P.qual_filter_enabled){
-            int lowq = len - (int)(ge >> 7);               // zero padding never reaches the limit
+            int lowq = len - (int)(f.ge >> 7);             // zero padding never reaches the limit
             if(plen < len){                                // take the bases that were cut off back out
                 if(start > 0){ int l1, n1; range_counts(qa, 0, start, P.low_quality_limit, l1, n1); lowq -= l1; nn -= n1; }
-                if(start + plen < len){ int l2, n2; range_counts(qa, start + plen, len - start - plen, P.low_quality_limit, l2, n2); lowq -= l2; nn -= n2; }
+                if(tail_done){ lowq -= tl; nn -= tn; }
+                else if(start + plen < len){ int l2, n2; range_counts(qa, start + plen, len - start - plen, P.low_quality_limit, l2, n2); lowq -= l2; nn -= n2; }
             }
             if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
             else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
@@ -356,7 +366,7 @@ __device__ __forceinline__ fq_read_result fast_phase1(const fq_params& P, uint32
     }
     PROF_ADD(12, t_res);
     rec.result = (uint8_t)result;
-    if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
+    if(!f.alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
     else { rec.start = (uint16_t)start; rec.len = (uint16_t)plen; }
     return rec;
 }
@@ -508,6 +518,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     const uint32_t t0 = lo + (uint32_t)k * T;
                     uint32_t doff = 0, dlen = 0;
                     fq_read_result rec = {};
+                    Fast1 f1 = {0u, 0, 0, 0, false};
                     bool pass = false;
                     if(valid){
                         doff = So[i] - a0; dlen = Sl[i];
@@ -519,10 +530,62 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                             sts16(S32 + L.o_len + 2u * i, 0u);                          // the statistics warps skip it
                         }
                         const uint32_t qa = S32 + doff;
-                        if(FAST) rec = fast_phase1(P, qa, (int)dlen);
+                        if(FAST) f1 = fast_phase1a(P, qa, (int)dlen);
                         else rec = phase1_read(D, S + doff, S + L.o_b + bshift + (doff >> 2), (int)dlen, fast_filter, tl);
+                    }
+                    bool coop = false;
+                    if(FAST){
+                        // Short cut-off tails of front-intact reads (the usual trimmed read) are handled by the whole warp,
+                        // one lane per cut-off base: first passFilter's counts of the tail (two ballots instead of a
+                        // per-lane range scan), then, for reads that pass, D = raw positions [plen, len) is taken out of
+                        // post1 by shared reductions right here, so that the statistics warps never see these reads as
+                        // exceptions.
+                        coop = valid && f1.alive && f1.start == 0 && f1.plen > 0 && (uint32_t)f1.plen < dlen && dlen - (uint32_t)f1.plen <= 32u;
+                        const unsigned mc0 = __ballot_sync(0xffffffffu, coop);
+                        int tlow = 0, tn = 0;
+                        const uint32_t lim = (uint32_t)P.low_quality_limit;
+                        for(unsigned mc = mc0; mc; mc &= mc - 1){
+                            const int src = __ffs((int)mc) - 1;
+                            const uint32_t o = __shfl_sync(0xffffffffu, doff, src), pl = (uint32_t)__shfl_sync(0xffffffffu, f1.plen, src),
+                                           ln = __shfl_sync(0xffffffffu, dlen, src);
+                            const uint32_t pos = pl + (uint32_t)lane;
+                            const uint32_t by = pos < ln ? lds8(S32 + o + pos) : 0u;
+                            const unsigned bl = __ballot_sync(0xffffffffu, pos < ln && (by & 0x7Fu) < lim), bn = __ballot_sync(0xffffffffu, (by & 0x80u) != 0);
+                            if(lane == src){ tlow = __popc(bl); tn = __popc(bn); }
+                        }
+                        if(valid) rec = fast_phase1b(P, S32 + doff, (int)dlen, f1, coop, tlow, tn);
+                    }
+                    if(valid){
                         out[t0 + i] = rec;
                         pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
+                    }
+                    if(FAST){
+                        coop = coop && pass;
+                        const uint32_t sbase = S32 + L.o_b + bshift;
+                        const uint32_t row = 4u * (uint32_t)C, krow = (uint32_t)NSETS * row;
+                        for(unsigned mc = __ballot_sync(0xffffffffu, coop); mc; mc &= mc - 1){
+                            const int src = __ffs((int)mc) - 1;
+                            const uint32_t o = __shfl_sync(0xffffffffu, doff, src), pl = (uint32_t)__shfl_sync(0xffffffffu, (int)rec.len, src),
+                                           ln = __shfl_sync(0xffffffffu, dlen, src);
+                            const uint32_t pos = pl + (uint32_t)lane;
+                            if(pos < ln){
+                                const uint32_t by = lds8(S32 + o + pos), q7 = by & 0x7Fu;
+                                const uint32_t code = (lds8(sbase + ((o + pos) >> 2)) >> (2u * (pos & 3u))) & 3u;
+                                const bool isn = (by & 0x80u) != 0;
+                                const uint32_t cell = post32 + 4u * pos;
+                                const uint32_t m20 = q7 > 53u ? 0xFFFFFFFFu : 0u, m30 = q7 > 63u ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+                                for(int st = 0; st < NSETS; ++st){
+                                    const bool in = st == S_ALL ? true : st == S_N ? isn : (!isn && (st == S_B0 ? (code & 1u) != 0 : st == S_B1 ? (code & 2u) != 0 : code == 3u));
+                                    if(!in) continue;
+                                    const uint32_t a = cell + (uint32_t)st * row;
+                                    if(st) reds_add(a + KN * krow, 0xFFFFFFFFu);
+                                    if(m20) reds_add(a + KN20 * krow, 0xFFFFFFFFu);
+                                    if(m30) reds_add(a + KN30 * krow, 0xFFFFFFFFu);
+                                    reds_add(a + KQS * krow, 0u - q7);
+                                }
+                            }
+                        }
                     }
                     PROF_T(t_tt);
                     // run counters, aggregated over the warp where every lane agrees (the usual case)
@@ -534,7 +597,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     else if(valid) reds_add(pre32 + lh + 4u * dlen, 1u);
                     if(__all_sync(0xffffffffu, !pass || rec.len == dl0)){ if(lane == 0 && mp) reds_add(post32 + lh + 4u * dl0, (uint32_t)__popc(mp)); }
                     else if(pass) reds_add(post32 + lh + 4u * rec.len, 1u);
-                    if(valid && !(pass && rec.start == 0 && rec.len == dlen)){
+                    if(valid && !coop && !(pass && rec.start == 0 && rec.len == dlen)){
                         const Desc d = make_desc(doff, dlen, rec.start, rec.len, pass ? 2u : 1u);
                         const uint32_t idx = atomicAdd(reinterpret_cast<uint32_t*>(S + L.o_cnt), 1u);
                         reinterpret_cast<uint2*>(S + L.o_ex)[idx] = make_uint2(d.x, d.y);
