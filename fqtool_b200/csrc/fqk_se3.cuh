@@ -14,7 +14,11 @@
 //     sweep per read for passFilter's counts, four window positions per step in the cut scans.
 #pragma once
 
-constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = 4;
+#ifndef V3_NSTAGES
+#define V3_NSTAGES 4
+#endif
+constexpr int V3_STATS = 256, V3_TRIM = 256, V3_THREADS = V3_STATS + V3_TRIM, V3_NS = V3_NSTAGES;
+static_assert(2 * V3_NS + 1 <= 16, "named barriers: id 0 is __syncthreads, ids 1 .. 2*NS the stage handshakes");
 #ifndef V3_STATS_HIGH
 #define V3_STATS_HIGH 0
 #endif
@@ -51,6 +55,25 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, 
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(a), "r"(parity), "r"(ns) : "memory");
         if(ok) break;
+    }
+}
+// Named barriers (bar.sync / bar.arrive) for the two handshakes that have no transaction count: a warp blocked in
+// bar.sync is parked by the hardware and issues nothing, whereas mbarrier.try_wait returns after a few tens of
+// nanoseconds whatever the hint, and the retry loops of the waiting warps took 16 % of all issued instructions
+// (profiles/r01d_k_se_v3_lines.txt).  ids 1..NS: tile ready (CH trim-warp arrivals + the statistics warps),
+// ids NS+1..2NS: stage free (the statistics warps arrive, the producer warp waits).
+__device__ __forceinline__ void nb_sync(int id, int nthreads){ asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory"); }
+__device__ __forceinline__ void nb_arrive(int id, int nthreads){ asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory"); }
+// mbarrier wait with a short back-off between polls (the `full` barriers: completed by the bulk copies)
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity){
+    uint32_t ok = 0, ns = 32;
+    const uint32_t a = smem_u32(bar);
+    for(;;){
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if(ok) break;
+        __nanosleep(ns);
+        ns = min(ns * 2u, 256u);
     }
 }
 __device__ __forceinline__ void sts16(uint32_t a, uint32_t v){ asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
@@ -459,7 +482,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     a = B.offsets[t1]; last = B.offsets[t1 + nt1 - 1]; ll = B.lengths[t1 + nt1 - 1];
                 }
                 PROF_T(t_pw);
-                if(n >= 1) mbar_wait_sleep(&freeb[s], (uint32_t)(n - 1) & 1u, 20000);
+                if(n >= 1) nb_sync(1 + V3_NS + s, V3_STATS + 32);
                 PROF_ADD(6, t_pw);
                 PROF_T(t_pi);
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
@@ -504,7 +527,11 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
                 PROF_T(t_tw);
+#ifdef V3_FULL_BACKOFF
+                mbar_wait_backoff(&full[s], (uint32_t)(k / V3_NS) & 1u);
+#else
                 mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 20000);
+#endif
                 PROF_ADD(0, t_tw);
                 PROF_T(t_tc);
                 const uint32_t* So = reinterpret_cast<const uint32_t*>(S + L.o_off);
@@ -606,7 +633,8 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 }
                 __syncwarp();
                 PROF_ADD(1, t_tc);
-                if(lane == 0) mbar_arrive(&ready[s]);
+                __threadfence_block();
+                nb_arrive(1 + s, CH * 32 + V3_STATS);
             }
             counters_add_tally(bc, tl);
         }
@@ -625,7 +653,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             const int s = k % V3_NS;
             const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
             PROF_T(t_sw);
-            mbar_wait_sleep(&ready[s], (uint32_t)(k / V3_NS) & 1u, 20000);
+            nb_sync(1 + s, CH * 32 + V3_STATS);
             PROF_ADD(3, t_sw);
             PROF_T(t_sp);
             if(active && !(dbg & 2)){
@@ -721,7 +749,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             }
             __syncwarp();
             PROF_ADD(5, t_sp);
-            if(lane == 0) mbar_arrive(&freeb[s]);
+            if(k + V3_NS < ntiles) nb_arrive(1 + V3_NS + s, V3_STATS + 32);      // the producer waits only for stages it refills
         }
         if(active){
             quad_drain(qa, smPre, smPost, C, w);
