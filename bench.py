@@ -20,6 +20,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries the ONE JSON line: NCCL's banner ("NCCL version ...", printed to stdout at NCCL_DEBUG >= VERSION) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 BATCH_READS = 4_000_000
 
