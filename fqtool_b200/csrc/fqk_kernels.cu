@@ -93,7 +93,7 @@ __device__ inline OvRes analyze_pair(const ReadView& a, const ReadView& b, int l
     return dev_analyze_packed(pa, pr, limit, require);
 }
 
-__global__ void __launch_bounds__(128) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
+__global__ void __launch_bounds__(128, 8) k_trim_pe(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2,
                                                   fq_read_result* __restrict__ out1, fq_read_result* __restrict__ out2,
                                                   fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
                                                   uint32_t* __restrict__ maxlen2, fq_correction* __restrict__ corr,

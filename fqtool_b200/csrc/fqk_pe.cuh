@@ -65,7 +65,7 @@ __device__ inline void pack_view(const ReadView& v, PackedSeq& s){
         c &= (vm | (vm << 1)) & ~(n | (n << 1));                       // bases outside the view and N bases carry code 0
         s.c[j] = c; s.n[j] = n;
     }
-    for(int j = nw; j < PE_MAXW + 2; ++j){ s.c[j] = 0; s.n[j] = 0; }
+    for(int j = nw; j < nw + 2; ++j){ s.c[j] = 0; s.n[j] = 0; }        // words nw, nw+1 are read by the funnel shifts; nothing reads further
 }
 
 // reverse complement (Seq::reverseComplement, src/seq.h:24-48) of a packed view
@@ -85,7 +85,7 @@ __device__ inline void revcomp_packed(const PackedSeq& b, PackedSeq& r){
         rc &= ~(rn | (rn << 1));                                       // N stays N (code 0)
         r.c[j] = rc; r.n[j] = rn;
     }
-    for(int j = nw; j < PE_MAXW + 2; ++j){ r.c[j] = 0; r.n[j] = 0; }
+    for(int j = nw; j < nw + 2; ++j){ r.c[j] = 0; r.n[j] = 0; }
 }
 
 // mismatches between x[xo + i] and y[yo + i] for i in [from, to) ; from is a multiple of 16
@@ -133,11 +133,61 @@ __device__ __forceinline__ bool try_offset(const PackedSeq& a, int ao, const Pac
     return d < limit || ol > 50;
 }
 
+// out-of-line copy for the rare survivors of the sliding-window quick reject (keeps the scan loops small)
+static __device__ __noinline__ bool try_offset_call(const PackedSeq& a, int ao, const PackedSeq& r, int ro, int ol, int limit, int brk, int& diff){
+    return try_offset(a, ao, r, ro, ol, limit, brk, diff);
+}
+
 // OverlapAnalysis::analyze on packed views; r = revcomp of read2's view
 __device__ inline OvRes dev_analyze_packed(const PackedSeq& a, const PackedSeq& r, int limit, int require){
     const int len1 = a.len, len2 = r.len;
     const int brk = max(limit, 1);
     OvRes o; int diff = 0;
+    if(!a.hasN && !r.hasN && require >= 16 && len1 >= 16 && len2 >= 16){
+        // Without N every overlap is at least 16 long, so the quick reject of try_offset (mismatches among the first
+        // 16 positions >= brk) is one funnel shift of a sliding two-word window, XOR, fold and popc per offset; the
+        // full test runs only for the few offsets that survive it.  Same scan order, same answers.
+        const uint32_t y0 = r.c[0], x0 = a.c[0];
+        const int nA = len1 - require, nB = len2 - require;
+        uint32_t lo = 0, hi = 0;
+        // four offsets per step, one branch for all four (a survivor is rare)
+#define FQK_QR(sh, other) __popc(((__funnelshift_r(lo, hi, (sh)) ^ (other)) | ((__funnelshift_r(lo, hi, (sh)) ^ (other)) >> 1)) & 0x55555555u)
+#pragma unroll 1
+        for(int base = 0; base < nA; base += 4){                       // src/overlapanalysis.cpp:20-41
+            if((base & 15) == 0){ lo = a.c[base >> 4]; hi = a.c[(base >> 4) + 1]; }
+            const int sh = 2 * (base & 15);
+            const int p0 = FQK_QR(sh, y0), p1 = FQK_QR(sh + 2, y0), p2 = FQK_QR(sh + 4, y0), p3 = FQK_QR(sh + 6, y0);
+            if(min(min(p0, p1), min(p2, p3)) < brk){
+                const int pk[4] = {p0, p1, p2, p3};
+#pragma unroll 1
+                for(int k = 0; k < 4; ++k){
+                    const int offset = base + k;
+                    if(pk[k] >= brk || offset >= nA) continue;
+                    const int ol = min(len1 - offset, len2);
+                    if(try_offset_call(a, offset, r, 0, ol, limit, brk, diff)){ o.overlapped = 1; o.offset = offset; o.len = ol; o.diff = diff; return o; }
+                }
+            }
+        }
+#pragma unroll 1
+        for(int base = 0; base < nB; base += 4){                       // src/overlapanalysis.cpp:44-67 (offset = -d)
+            if((base & 15) == 0){ lo = r.c[base >> 4]; hi = r.c[(base >> 4) + 1]; }
+            const int sh = 2 * (base & 15);
+            const int p0 = FQK_QR(sh, x0), p1 = FQK_QR(sh + 2, x0), p2 = FQK_QR(sh + 4, x0), p3 = FQK_QR(sh + 6, x0);
+            if(min(min(p0, p1), min(p2, p3)) < brk){
+                const int pk[4] = {p0, p1, p2, p3};
+#pragma unroll 1
+                for(int k = 0; k < 4; ++k){
+                    const int d = base + k;
+                    if(pk[k] >= brk || d >= nB) continue;
+                    const int ol = min(len1, len2 - d);
+                    if(try_offset_call(a, 0, r, d, ol, limit, brk, diff)){ o.overlapped = 1; o.offset = -d; o.len = ol; o.diff = diff; return o; }
+                }
+            }
+        }
+#undef FQK_QR
+        o.overlapped = 0; o.offset = 0; o.len = 0; o.diff = 0;
+        return o;
+    }
     for(int offset = 0; offset < len1 - require; ++offset){           // src/overlapanalysis.cpp:20-41
         const int ol = min(len1 - offset, len2);
         if(try_offset(a, offset, r, 0, ol, limit, brk, diff)){ o.overlapped = 1; o.offset = offset; o.len = ol; o.diff = diff; return o; }
