@@ -136,11 +136,22 @@ __device__ inline void dev_trim_polyg(ReadView& v, int compareReq, int maxMismat
                                       fq_read_result& rec, Tally& tl){
     const int rlen = v.len;
     int mismatch = 0, i = 0, firstG = rlen - 1;
-    for(i = 0; i < rlen; ++i){
-        const int p = rlen - i - 1;
-        if(v.cls(p) != 3) ++mismatch; else firstG = p;
-        const int allowed = min(maxMismatch, max(1, (i + 1) / oneEach));
-        if(mismatch > allowed) break;
+    if(oneEach > 0){
+        // (i + 1) / oneEach kept as a running quotient: the division was 4 % of k_trim_pe's instructions
+        int quo = 0, rem = 0;
+        for(i = 0; i < rlen; ++i){
+            const int p = rlen - i - 1;
+            if(v.cls(p) != 3) ++mismatch; else firstG = p;
+            if(++rem == oneEach){ rem = 0; ++quo; }
+            if(mismatch > min(maxMismatch, max(1, quo))) break;
+        }
+    }else{
+        for(i = 0; i < rlen; ++i){
+            const int p = rlen - i - 1;
+            if(v.cls(p) != 3) ++mismatch; else firstG = p;
+            const int allowed = min(maxMismatch, max(1, (i + 1) / oneEach));
+            if(mismatch > allowed) break;
+        }
     }
     if(i + 1 >= compareReq){
         view_resize(v, firstG);
