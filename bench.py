@@ -20,8 +20,18 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries the ONE JSON line: NCCL's banner ("NCCL version ...", printed to stdout at NCCL_DEBUG >= VERSION) goes to stderr
+# stdout carries the ONE JSON line and nothing else: the original stdout is kept aside for it and file descriptor 1 is
+# pointed at stderr, so that whatever a library prints (NCCL's "NCCL version ..." banner still reached stdout with
+# NCCL_DEBUG_FILE=/dev/stderr under torchrun) lands on stderr
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+sys.stdout.flush()
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
 
 BATCH_READS = 4_000_000
 
@@ -149,7 +159,7 @@ def run_reference_arm(a):
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ----------------------------------------------------------------- B200 arm
@@ -364,7 +374,7 @@ def main():
                            "impl": a.impl},
                 "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu_baseline}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

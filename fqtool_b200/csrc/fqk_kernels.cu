@@ -486,34 +486,52 @@ __global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, co
 
 // ---------------------------------------------------------------- ASCII ingest
 // FASTQ characters -> the packed batch layout, on the device (the host-side twin is fqk_pack_ascii).
-// One warp per read, a lane per 16-base chunk: 16 sequence and 16 quality characters become one 32-bit
-// word of 2-bit codes and one 16-byte quality vector (N flag in bit 7); padding is written as zeros.
+// One warp per read, a lane per 4-base group of the padded read: four sequence and four quality characters are
+// fetched as (at most two) aligned 32-bit words each and funnel-shifted to the read's byte position, classified
+// four at a time (exact zero-byte tests against A, C, G, T, N), turned into 2-bit codes ((c >> 1) & 3 with its two
+// bits swapped is the reference's A0 T1 C2 G3), gathered into one byte by a multiply, and written as one
+// quality word (N flag in bit 7) + one base byte; the groups past the read's end write the zero padding.
+// The staging buffers are 256-byte aligned with 16 spare bytes, so the second word of a straddling group exists.
+__device__ __forceinline__ uint32_t eq_bytes(uint32_t v, uint32_t pat){                  // 0x80 in every byte of v equal to pat's
+    const uint32_t z = v ^ pat;
+    return ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
+}
 __global__ void __launch_bounds__(256) k_pack_ascii(uint32_t n, const char* __restrict__ seq, const char* __restrict__ qual,
                                                      const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
                                                      const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
                                                      uint8_t* __restrict__ qout, uint32_t* __restrict__ err){
     const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(seq);
+    const uint32_t* q32 = reinterpret_cast<const uint32_t*>(qual);
+    uint32_t bad = 0;
     for(uint32_t r = blockIdx.x * warps + (threadIdx.x >> 5); r < n; r += gridDim.x * warps){
         const uint32_t so = src_off[r], dof = dst_off[r], len = lengths[r];
-        const uint32_t chunks = (len + 15) >> 4;
-        for(uint32_t c = lane; c < chunks; c += 32){
-            uint32_t code = 0, q[4] = {0, 0, 0, 0};
-#pragma unroll
-            for(int j = 0; j < 16; ++j){
-                const uint32_t i = 16 * c + j;
-                if(i < len){
-                    const char ch = seq[so + i];
-                    const uint32_t qq = (uint8_t)qual[so + i];
-                    uint32_t cl;
-                    switch(ch){ case 'A': cl = 0; break; case 'T': cl = 1; break; case 'C': cl = 2; break; case 'G': cl = 3; break;
-                                case 'N': cl = 4; break; default: cl = 0; atomicOr(err, 4u); }
-                    if(qq & 0x80u) atomicOr(err, 4u);
-                    if(cl == 4) q[j >> 2] |= (qq | 0x80u) << (8 * (j & 3));
-                    else { q[j >> 2] |= qq << (8 * (j & 3)); code |= cl << (2 * j); }
-                }
+        const uint32_t groups = ((len + 15) >> 4) << 2;
+        const uint32_t sh = 8u * (so & 3u);
+        for(uint32_t g = lane; g < groups; g += 32){
+            const uint32_t i0 = 4u * g;
+            uint32_t q = 0, code = 0;
+            if(i0 < len){
+                const uint32_t w = (so + i0) >> 2;
+                const uint32_t a0 = s32[w], b0 = q32[w];
+                uint32_t a1 = 0, b1 = 0;
+                if(sh){ a1 = s32[w + 1]; b1 = q32[w + 1]; }
+                const uint32_t sv = __funnelshift_r(a0, a1, sh), qv = __funnelshift_r(b0, b1, sh);
+                const uint32_t nv = len - i0;
+                const uint32_t vm = nv >= 4u ? 0xFFFFFFFFu : ((1u << (8u * nv)) - 1u);
+                const uint32_t hv = vm & 0x80808080u;
+                const uint32_t fn = eq_bytes(sv, 0x4E4E4E4Eu) & hv;
+                const uint32_t fa = (eq_bytes(sv, 0x41414141u) | eq_bytes(sv, 0x43434343u) | eq_bytes(sv, 0x47474747u) | eq_bytes(sv, 0x54545454u)) & hv;
+                bad |= ((fa | fn) ^ hv) | (qv & hv);                                      // foreign character, or a quality byte with bit 7 set
+                uint32_t x = (sv >> 1) & 0x03030303u;
+                x = ((x & 0x01010101u) << 1) | ((x >> 1) & 0x01010101u);
+                x &= (fa >> 7) * 3u;
+                code = (x * 0x01041040u) >> 24;
+                q = (qv & vm) | fn;
             }
-            *reinterpret_cast<uint4*>(qout + dof + 16 * c) = make_uint4(q[0], q[1], q[2], q[3]);
-            *reinterpret_cast<uint32_t*>(bases2 + ((dof + 16 * c) >> 2)) = code;
+            *reinterpret_cast<uint32_t*>(qout + dof + i0) = q;
+            bases2[(dof >> 2) + g] = (uint8_t)code;
         }
     }
+    if(bad) atomicOr(err, 4u);
 }
