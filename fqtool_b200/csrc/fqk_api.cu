@@ -476,21 +476,26 @@ static int stage_ascii(fqk_ctx* c, int m, const fq_ascii_batch* b){
     StagedBatch& s = c->st[m];
     const uint64_t chars = b->off[n] - b->off[0];
     if(chars > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "ASCII batch larger than 2^32 characters");
+    // the characters go first: the two large copies (pinned source) run while the host builds the index arrays below
+    if(c->aseq[m].ensure(chars + 16) || c->aqual[m].ensure(chars + 16))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    CU(cudaMemcpyAsync(c->aseq[m].p, b->seq + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->aqual[m].p, b->qual + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
     c->hsrc[m].resize(n); c->hdst[m].resize(n); c->hlen[m].resize(n);
     uint64_t pos = 0;
     for(uint32_t r = 0; r < n; ++r){
         const uint64_t l = b->off[r + 1] - b->off[r];
-        if(l > FQK_MAX_READ_LEN) return fail(c, FQK_E_LIMIT, "read longer than FQK_MAX_READ_LEN");
+        if(l > FQK_MAX_READ_LEN){ cudaStreamSynchronize(c->stream); return fail(c, FQK_E_LIMIT, "read longer than FQK_MAX_READ_LEN"); }   // the copies read the caller's buffers
         c->hsrc[m][r] = (uint32_t)(b->off[r] - b->off[0]); c->hdst[m][r] = (uint32_t)pos; c->hlen[m][r] = (uint16_t)l;
         pos += (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD;
-        if(pos > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "batch larger than 2^32 padded bases");
+        if(pos > 0xFFFFFFF0ull){ cudaStreamSynchronize(c->stream); return fail(c, FQK_E_LIMIT, "batch larger than 2^32 padded bases"); }
     }
     const uint64_t total = (pos + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
     if(s.off.ensure((size_t)n * 4 + 16) || s.len.ensure((size_t)n * 2 + 16) || s.b2.ensure(total / 4 + 16) || s.q.ensure(total + 16) ||
-       c->aseq[m].ensure(chars + 16) || c->aqual[m].ensure(chars + 16) || c->asrc[m].ensure((size_t)n * 4 + 16))
+       c->asrc[m].ensure((size_t)n * 4 + 16)){
+        cudaStreamSynchronize(c->stream);
         return fail(c, FQK_E_NOMEM, "device staging allocation failed");
-    CU(cudaMemcpyAsync(c->aseq[m].p, b->seq + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(c->aqual[m].p, b->qual + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
+    }
     CU(cudaMemcpyAsync(c->asrc[m].p, c->hsrc[m].data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s.off.p, c->hdst[m].data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(s.len.p, c->hlen[m].data(), (size_t)n * 2, cudaMemcpyHostToDevice, c->stream));
@@ -499,7 +504,7 @@ static int stage_ascii(fqk_ctx* c, int m, const fq_ascii_batch* b){
         CU(cudaMemsetAsync((uint8_t*)s.b2.p + pos / 4, 0, (total - pos) / 4, c->stream));
     }
     if(n){
-        k_pack_ascii<<<grid_for(c, n, 8, 8), 256, 0, c->stream>>>(n, (const char*)c->aseq[m].p, (const char*)c->aqual[m].p,
+        k_pack_ascii<<<grid_for(c, n, 16, 8), 256, 0, c->stream>>>(n, (const char*)c->aseq[m].p, (const char*)c->aqual[m].p,
             (const uint32_t*)c->asrc[m].p, (const uint32_t*)s.off.p, (const uint16_t*)s.len.p, (uint8_t*)s.b2.p, (uint8_t*)s.q.p, c->err);
         c->launches++;
     }
