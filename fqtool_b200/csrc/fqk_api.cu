@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 #include "fqk_kernels.h"
 #include "fqk_fused.h"
+#include "fqk_hostutil.h"
 
 // ------------------------------------------------------------------- NCCL
 // NCCL is bound at run time (dlopen) so that the library also loads on hosts
@@ -131,33 +132,9 @@ extern "C" void fqk_default_params(fq_params* p){
     p->dup_keylen = 12; p->max_cycles = 512;
 }
 
-extern "C" int fqk_stats_layout(const fq_params* p, fq_stats_layout* L){
-    if(!p || !L) return FQK_E_INVALID;
-    memset(L, 0, sizeof(*L));
-    const uint64_t C = p->max_cycles > 0 ? (uint64_t)p->max_cycles : 512;
-    L->max_cycles = C;
-    L->kmer_bins = p->kmer_len > 0 ? (1ull << (2 * p->kmer_len)) : 0;
-    L->s_q20 = 0; L->s_q30 = 8 * C; L->s_content = 16 * C; L->s_qualsum = 24 * C;
-    L->s_total_base = 32 * C; L->s_total_qual = 33 * C;
-    L->s_reads = 34 * C; L->s_length_sum = 34 * C + 1; L->s_kmer = 34 * C + 2;
-    L->stats_stride = 34 * C + 2 + L->kmer_bins;
-    for(int s = 0; s < 4; ++s) L->stats_off[s] = (uint64_t)s * L->stats_stride;
-    uint64_t o = 4 * L->stats_stride;
-    L->filter_off = o; o += FQK_FILTER_RESULT_TYPES;
-    L->adapter_reads_off = o++; L->adapter_bases_off = o++;
-    L->polyx_reads_off = o; o += 5; L->polyx_bases_off = o; o += 5;
-    L->merged_pairs_off = o++;
-    L->insert_hist_off = o; L->insert_hist_len = (uint64_t)p->insert_size_max + 1; o += L->insert_hist_len;
-    L->correction_off = o; o += 64;
-    L->corrected_reads_off = o; o += 1;
-    L->total_u64 = o;
-    L->dup_bins = p->dup_enabled ? (1ull << (2 * p->dup_keylen)) : 0;
-    return 0;
-}
+extern "C" int fqk_stats_layout(const fq_params* p, fq_stats_layout* L){ return fqk_layout_fill(p, L); }
 
-static int cls_of_char(char ch){
-    switch(ch){ case 'A': return 0; case 'T': return 1; case 'C': return 2; case 'G': return 3; case 'N': return 4; default: return -1; }
-}
+static int cls_of_char(char ch){ return fqk_cls_of_char(ch); }
 
 static int validate_params(const fq_params* p, std::string& why){
     if(p->abi_version != FQK_ABI_VERSION){ why = "abi_version mismatch"; return FQK_E_INVALID; }
@@ -233,20 +210,7 @@ extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal,
     if(device_ordinal < 0 || device_ordinal >= ndev) return fail(nullptr, FQK_E_INVALID, "bad device ordinal");
     fqk_ctx* c = new fqk_ctx();
     c->device = device_ordinal; c->rank = rank; c->nranks = nranks;
-    memset(&c->D, 0, sizeof(c->D));
-    c->D.P = *p;
-    if(c->D.P.max_cycles == 0) c->D.P.max_cycles = 512;
-    for(int i = 0; i < p->adapter_r1_len; ++i) c->D.ad1[i] = (uint8_t)cls_of_char(p->adapter_r1[i]);
-    for(int i = 0; i < p->adapter_r2_len; ++i) c->D.ad2[i] = (uint8_t)cls_of_char(p->adapter_r2[i]);
-    for(int i = 0; i < p->adapter_r1_len; ++i){
-        const int cl = c->D.ad1[i];
-        if(cl == 4) c->D.adn1[i >> 4] |= 1u << (2 * (i & 15)); else c->D.adc1[i >> 4] |= (uint32_t)cl << (2 * (i & 15));
-    }
-    for(int i = 0; i < p->adapter_r2_len; ++i){
-        const int cl = c->D.ad2[i];
-        if(cl == 4) c->D.adn2[i >> 4] |= 1u << (2 * (i & 15)); else c->D.adc2[i >> 4] |= (uint32_t)cl << (2 * (i & 15));
-    }
-    fqk_stats_layout(&c->D.P, &c->D.L);
+    fqk_dev_params_fill(c->D, p);
     auto bail = [&](int code, const std::string& m){ std::string mm = m; fqk_destroy(c); return fail(nullptr, code, mm); };
     if(cudaSetDevice(device_ordinal) != cudaSuccess) return bail(FQK_E_CUDA, "cudaSetDevice failed");
     cudaDeviceProp prop;
@@ -313,7 +277,7 @@ extern "C" const char* fqk_last_error(const fqk_ctx* c){
 }
 extern "C" void* fqk_stream(fqk_ctx* c){ return c ? (void*)c->stream : nullptr; }
 extern "C" uint64_t fqk_launch_count(const fqk_ctx* c){ return c ? c->launches : 0; }
-extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 3) return FQK_E_INVALID; c->impl = impl; return 0; }
+extern "C" int fqk_set_impl(fqk_ctx* c, int impl){ if(!c || impl < 0 || impl > 3 || impl == 2) return FQK_E_INVALID; c->impl = impl; return 0; }
 extern "C" int fqk_set_kernel_timing(fqk_ctx* c, int enabled){ if(!c) return FQK_E_INVALID; c->timing = enabled != 0; return 0; }
 extern "C" int fqk_kernel_times(fqk_ctx* c, double* ms, uint64_t* launches){
     if(!c) return FQK_E_INVALID;

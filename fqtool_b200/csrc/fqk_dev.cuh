@@ -7,7 +7,9 @@
 // quality boundary and a 4-byte base boundary.
 #pragma once
 #include <cstdint>
+#ifndef FQK_EMU
 #include <cuda_runtime.h>
+#endif
 #include "../../include/fqk.h"
 
 struct DevBatch {

@@ -1,38 +1,27 @@
-// fqk_fused.cu -- fused single-end kernel: trim + filter + pre/post per-cycle
-// statistics in ONE pass over HBM (sm_100a).
+// fqk_fused.cu -- the fused kernels: trim + filter + pre/post per-cycle statistics in ONE pass over HBM (sm_100a).
+//   k_se_v3       single-end batches without k-mers (fqk_se3.cuh): three warp roles, P - D + Z statistics
+//   k_pe_v4       paired-end batches (fqk_pe4.cuh): both mates staged per tile, warp-cooperative overlap analysis
+//   k_fused_se_ws single-end with k-mers, and the statistics-only passes of the older paired-end path
 //
-// Data movement.  Persistent blocks (one per SM) walk their share of the batch in
-// tiles of T consecutive reads.  The quality and base bytes of a tile are one
-// contiguous range of the dense batch, so one elected thread stages them into shared
-// memory with two bulk async copies (cp.async.bulk global->shared::cluster, completion
-// counted on an mbarrier) while the block is still computing on the previous tile
-// (two stages).  HBM is read exactly once per base; records are written once.
+// Data movement.  Persistent blocks (one per SM) walk their share of the batch in tiles of T consecutive reads.
+// The quality and base bytes of a tile are one contiguous range of the dense batch, so they are staged into
+// shared memory with bulk async copies (cp.async.bulk global->shared::cluster, completion counted on an
+// mbarrier) while the block is still computing on earlier tiles.  HBM is read once per base; records are
+// written once.
 //
-// Phase 1 (one thread per read): the reference's per-read sequence
-// (processSingleEnd, /root/reference/src/seprocessor.cpp:313-340) on the staged bytes;
-// passFilter's counts are SWAR over 4 quality bytes per step.
-//
-// Phase 2 (Stats::statRead, /root/reference/src/stats.cpp:237-295) is a register-
-// resident SIMD-within-a-register reduction.  A thread owns one 4-cycle word of the
-// read (4 quality bytes + one byte of 2-bit bases); consecutive threads own consecutive
-// words, so a group of W = max_cycles/4 threads covers a read and G = THREADS/W groups
-// cover different reads.  For five "sets" of bases (all, code bit0, code bit1, both
-// bits, N) each thread keeps per-cycle counters n, n(q>20), n(q>30) as 4x8-bit lanes
-// and quality sums as 2x16-bit lanes (level 1).  Every 255 reads level 1 is folded into
-// level-2 registers (16-bit count lanes, 32-bit sums) -- no shared-memory atomics on
-// the steady-state path (ATOMS costs ~2 cycles/lane on this part).  When the block
-// retires, level 2 goes to per-block shared arrays and sets are converted to the
-// reference's bins: A = all - bit0 - bit1 + both - N, T = bit0 - both, C = bit1 - both,
-// G = both.  Per-cycle base totals come from a per-block read-length histogram, which
-// relies on the zero padding of the batch layout.
-//
-// pre1 covers every raw read.  post1 reuses the same registers when a passing read is
-// untouched by trimming ("common" reads); other reads use two small level-1 banks
-// (raw part for pre1, shifted kept part for post1) drained with shared atomics.
+// Statistics (Stats::statRead, /root/reference/src/stats.cpp:237-295) are register-resident reductions.  A
+// thread owns one 4-cycle word of the read (4 quality bytes + one byte of 2-bit bases); consecutive threads own
+// consecutive words, so a group of W threads covers a read and several groups cover different reads.  For five
+// "sets" of bases (all, code bit0, code bit1, both bits, N) the per-cycle counters n, n(q>20), n(q>30) and the
+// quality sums are accumulated either four reads at a time with dp4a (QuadAcc) or one read at a time as byte
+// lanes (Acc1).  When the block retires, sets are converted to the reference's bins: A = all - bit0 - bit1 +
+// both - N, T = bit0 - both, C = bit1 - both, G = both.  Per-cycle base totals come from a per-block read-length
+// histogram, which relies on the zero padding of the batch layout.
 #include <algorithm>
 #include <cstdlib>
 #include "fqk_fused.h"
 #include "fqk_pe.cuh"
+#include "fqk_smem.cuh"
 
 // Optional cycle accounting per warp role (nvcc -DFQK_V3_PROF; read back with fqk_debug_prof): development aid only.
 #ifdef FQK_V3_PROF
@@ -59,14 +48,7 @@ extern "C" int fqk_debug_prof(unsigned long long* out16, int reset){
 
 namespace {
 
-constexpr int KN = 0, KN20 = 1, KN30 = 2, KQS = 3;                 // kinds
-constexpr int S_ALL = 0, S_B0 = 1, S_B1 = 2, S_B01 = 3, S_N = 4;   // sets
-constexpr int NSETS = 5;
-constexpr int THREADS = 384;
 
-__device__ __forceinline__ uint32_t lds32(uint32_t a){ uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint32_t lds8(uint32_t a){ uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint2 lds64(uint32_t a){ uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
 
 // level 1: 8-bit count lanes, 16-bit sum lanes (n[S_ALL] is unused: totals come from lengths)
 struct Acc1 {
@@ -76,28 +58,6 @@ struct Acc1 {
         for(int s = 0; s < NSETS; ++s){ n[s] = n20[s] = n30[s] = qe[s] = qo[s] = 0; }
     }
 };
-// level 2 lives in per-thread private shared-memory slots (plain load/add/store, no atomics, conflict-free
-// layout [slot][thread]): per level-1 count register two words of 2x16-bit lanes (bytes 0,2 / bytes 1,3),
-// per level-1 sum register two 32-bit sums.  Slot index = (set*5 + kind5)*2 + half.
-constexpr int L2_SLOTS = NSETS * 5 * 2;
-__device__ __forceinline__ void sts32(uint32_t a, uint32_t v){ asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
-__device__ __forceinline__ void l2_add(uint32_t l2, int slot, uint32_t v){
-    const uint32_t a = l2 + (uint32_t)slot * (THREADS * 4);
-    sts32(a, lds32(a) + v);
-}
-// l2 = shared address of this thread's slot 0
-__device__ __forceinline__ void fold(Acc1& a, uint32_t l2){
-#pragma unroll
-    for(int s = 0; s < NSETS; ++s){
-        if(s){ l2_add(l2, (s * 5 + 0) * 2, a.n[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 0) * 2 + 1, (a.n[s] >> 8) & 0x00FF00FFu); }
-        l2_add(l2, (s * 5 + 1) * 2, a.n20[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 1) * 2 + 1, (a.n20[s] >> 8) & 0x00FF00FFu);
-        l2_add(l2, (s * 5 + 2) * 2, a.n30[s] & 0x00FF00FFu); l2_add(l2, (s * 5 + 2) * 2 + 1, (a.n30[s] >> 8) & 0x00FF00FFu);
-        l2_add(l2, (s * 5 + 3) * 2, a.qe[s] & 0xFFFFu); l2_add(l2, (s * 5 + 3) * 2 + 1, a.qe[s] >> 16);
-        l2_add(l2, (s * 5 + 4) * 2, a.qo[s] & 0xFFFFu); l2_add(l2, (s * 5 + 4) * 2 + 1, a.qo[s] >> 16);
-    }
-    a.zero();
-}
-
 // shared-memory layout of one Stats object: u32 [kind 4][set 5][C] then lenhist[C+1]
 __device__ __forceinline__ uint32_t* sm_cell(uint32_t* sm, int C, int kind, int set){ return sm + (kind * NSETS + set) * C; }
 __device__ __forceinline__ void sm_add(uint32_t* smA, uint32_t* smB, int C, int kind, int set, int cyc, uint32_t v){
@@ -164,27 +124,6 @@ __device__ __forceinline__ void drain_l1(Acc1& a, uint32_t* smA, uint32_t* smB, 
     drain1(vals, smA, smB, C, w);
     a.zero();
 }
-// level 2 -> shared arrays (once per block)
-__device__ __noinline__ void drain2(uint32_t* vals /*[NSETS*10]*/, uint32_t* smA, uint32_t* smB, int C, int w){
-    const int c0 = 4 * w;
-    for(int s = 0; s < NSETS; ++s){
-        const uint32_t* v = vals + s * 10;
-        for(int j = 0; j < 4; ++j){
-            const int h = j & 1, sh = (j >> 1) * 16;          // byte j lives in register h, 16-bit lane j>>1
-            if(s) sm_add(smA, smB, C, KN, s, c0 + j, (v[0 + h] >> sh) & 0xFFFF);
-            sm_add(smA, smB, C, KN20, s, c0 + j, (v[2 + h] >> sh) & 0xFFFF);
-            sm_add(smA, smB, C, KN30, s, c0 + j, (v[4 + h] >> sh) & 0xFFFF);
-            sm_add(smA, smB, C, KQS, s, c0 + j, h ? v[8 + (j >> 1)] : v[6 + (j >> 1)]);   // qe: bytes 0,2; qo: bytes 1,3
-        }
-    }
-}
-__device__ __forceinline__ void drain_l2(uint32_t l2, uint32_t* smA, uint32_t* smB, int C, int w){
-    uint32_t vals[NSETS * 10];
-#pragma unroll
-    for(int i = 0; i < NSETS * 10; ++i) vals[i] = lds32(l2 + (uint32_t)i * (THREADS * 4));
-    drain2(vals, smA, smB, C, w);
-}
-
 // block retirement: sets -> bins, raw quality chars -> Phred (minus 33 per base), add to the global u64 arrays.
 // Everything is linear and evaluated in wrapping signed arithmetic, so a block may hold a partial view
 // (e.g. only the tail of merged reads: length histogram entries +1 at the end, -1 at the start of the range).
@@ -228,264 +167,6 @@ __device__ void retire(const uint32_t* sm, int C, const fq_stats_layout& L, uint
     if((threadIdx.x & 31) == 0){ if(nr) add_u64(S + L.s_reads, (uint64_t)nr); if(ls) add_u64(S + L.s_length_sum, (uint64_t)ls); }
 }
 
-// ------------------------------------------------------------- async staging
-__device__ __forceinline__ uint32_t smem_u32(const void* p){ return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count){
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes){
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar){
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity){
-    uint32_t ok = 0;
-    const uint32_t a = smem_u32(bar);
-    while(!ok){
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
-    }
-}
-
-// Filter::passFilter (src/filter.cpp:15-25) counts over the kept part [start, start+len) of a read staged
-// in shared memory at address qa (16-byte aligned), 16 quality bytes per load.  Low-quality bases: byte + k
-// carries into bit 7 iff byte >= limit; the four carry words of a chunk are merged into one word before the
-// popcount.  N bases: bit 7 of the stored byte (chunks without N skip the masking).
-__device__ __forceinline__ uint4 lds128(uint32_t a){
-    uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v;
-}
-__device__ __forceinline__ uint32_t byte_range_mask(int p, int start, int end){      // bytes of word at position p inside [start, end)
-    const int nlo = min(4, max(0, start - p)), nhi = min(4, max(0, p + 4 - end));
-    return (nlo + nhi >= 4) ? 0u : ((0xFFFFFFFFu << (8 * nlo)) & (0xFFFFFFFFu >> (8 * nhi)));
-}
-__device__ __forceinline__ void swar_counts(uint32_t qa, int start, int len, int lim, bool want_total,
-                                            int& lowq, int& nn, int& total){
-    lowq = nn = total = 0;
-    if(len <= 0) return;
-    const int end = start + len;
-    const uint32_t k = (uint32_t)(0x80 - lim) * 0x01010101u;
-    int ge_bytes = 0;                                                  // bytes with q >= limit
-    for(int c = start >> 4; c <= (end - 1) >> 4; ++c){
-        uint4 v = lds128(qa + 16 * c);
-        const int p = 16 * c;
-        if(p < start || p + 16 > end){                                 // edge chunk: zero the bytes outside the read part
-            v.x &= byte_range_mask(p, start, end); v.y &= byte_range_mask(p + 4, start, end);
-            v.z &= byte_range_mask(p + 8, start, end); v.w &= byte_range_mask(p + 12, start, end);
-        }
-        const uint32_t nf = (v.x | v.y | v.z | v.w) & 0x80808080u;
-        if(nf){
-            nn += __popc(v.x & 0x80808080u) + __popc(v.y & 0x80808080u) + __popc(v.z & 0x80808080u) + __popc(v.w & 0x80808080u);
-            v.x &= 0x7F7F7F7Fu; v.y &= 0x7F7F7F7Fu; v.z &= 0x7F7F7F7Fu; v.w &= 0x7F7F7F7Fu;
-        }
-        const uint32_t g = ((v.x + k) & 0x80808080u) | (((v.y + k) & 0x80808080u) >> 1) |
-                           (((v.z + k) & 0x80808080u) >> 2) | (((v.w + k) & 0x80808080u) >> 3);
-        ge_bytes += __popc(g);
-        if(want_total){
-            total = (int)__dp4a(v.x, 0x01010101u, (uint32_t)total); total = (int)__dp4a(v.y, 0x01010101u, (uint32_t)total);
-            total = (int)__dp4a(v.z, 0x01010101u, (uint32_t)total); total = (int)__dp4a(v.w, 0x01010101u, (uint32_t)total);
-        }
-    }
-    lowq = len - ge_bytes;                                             // zeroed bytes never reach the limit (limit >= 33)
-    total -= 33 * len;
-}
-
-// per-read descriptor of a tile, 8 bytes: x = (offset in tile)/16 | len << 17, y = start | plen << 13 | kind << 26
-// kind: 0 common (passing, untrimmed), 1 raw only, 2 raw + shifted kept part for post1
-struct Desc { uint32_t x, y; };
-__device__ __forceinline__ Desc make_desc(uint32_t off, uint32_t len, uint32_t start, uint32_t plen, uint32_t kind){
-    Desc d; d.x = (off >> 4) | (len << 17); d.y = start | (plen << 13) | (kind << 26); return d;
-}
-
-__global__ void __launch_bounds__(THREADS, 1)
-k_fused_se(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
-           uint64_t* __restrict__ flat, int W, int T, int reads_per_block){
-    extern __shared__ __align__(128) uint8_t smraw[];
-    const fq_params& P = D.P;
-    const int C = 4 * W, Cp = (C + 15) & ~15;
-    const int statw = 4 * NSETS * C + C + 1;
-    uint32_t* smPre = reinterpret_cast<uint32_t*>(smraw);
-    uint32_t* smPost = smPre + statw;
-    BlockCounters* bc = reinterpret_cast<BlockCounters*>(smPost + statw);
-    uint64_t* mbar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bc + 1) + 7) & ~uintptr_t(7));
-    uint32_t* zero_word = reinterpret_cast<uint32_t*>(mbar + 2);         // 8 bytes of zeros
-    Desc* desc = reinterpret_cast<Desc*>(mbar + 3);
-    uint32_t* l2base = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(desc + T) + 15) & ~uintptr_t(15));
-    uint8_t* sp = reinterpret_cast<uint8_t*>(l2base + L2_SLOTS * THREADS);
-    const uint32_t qcap = (uint32_t)T * Cp, bcap = ((qcap / 4 + 15u) & ~15u) + 16;
-    const uint32_t mo = (T * 4 + 15) & ~15, ml = (T * 2 + 15) & ~15;
-    const uint32_t stage_bytes = qcap + bcap + mo + ml;
-    // stage s: quality bytes at sp + s*stage_bytes, then base bytes, offsets, lengths
-    auto stq = [&](int s){ return sp + (size_t)s * stage_bytes; };
-    auto stb = [&](int s){ return sp + (size_t)s * stage_bytes + qcap; };
-    auto sto = [&](int s){ return reinterpret_cast<uint32_t*>(sp + (size_t)s * stage_bytes + qcap + bcap); };
-    auto stl = [&](int s){ return reinterpret_cast<uint16_t*>(sp + (size_t)s * stage_bytes + qcap + bcap + mo); };
-    const uint32_t sp32 = smem_u32(sp), sd32 = smem_u32(desc), zero_addr = smem_u32(zero_word);
-    if(threadIdx.x == 0){ zero_word[0] = 0; zero_word[1] = 0; }
-    const uint32_t l2 = smem_u32(l2base) + 4 * threadIdx.x;          // this thread's private level-2 slots
-    for(int i = threadIdx.x; i < L2_SLOTS * THREADS; i += THREADS) l2base[i] = 0;
-
-    for(int i = threadIdx.x; i < 2 * statw; i += THREADS) smPre[i] = 0;
-    counters_zero(bc);
-    if(threadIdx.x == 0){ mbar_init(&mbar[0], 1); mbar_init(&mbar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-
-    const int G = THREADS / W;
-    const int g = threadIdx.x / W, w = threadIdx.x - g * W;
-    const bool active = g < G;
-    const uint32_t lo = (uint32_t)min((uint64_t)B.n, (uint64_t)blockIdx.x * reads_per_block);
-    const uint32_t hi = (uint32_t)min((uint64_t)B.n, (uint64_t)lo + reads_per_block);
-    const int ntiles = (int)((hi - lo + T - 1) / T);
-
-    // the two bulk copies of a tile whose offsets/lengths are already staged
-    auto issue = [&](int s, int nt){
-        const uint32_t* so = sto(s); const uint16_t* sl = stl(s);
-        const uint32_t a = so[0];
-        uint64_t e = (uint64_t)so[nt - 1] + ((sl[nt - 1] + 15u) & ~15u);
-        const bool bad = (a & 15u) || e < a || e - a > qcap || e > B.total;
-        if(bad){ atomicOr(D.err, 2u); e = a; }
-        const uint32_t qbytes = (uint32_t)(e - a);
-        const uint32_t b0 = (a >> 2) & ~15u;                               // base bytes start, aligned down to 16
-        const uint32_t bbytes = qbytes ? (((uint32_t)(e >> 2) + 15u) & ~15u) - b0 : 0u;
-        mbar_expect_tx(&mbar[s], qbytes + bbytes);
-        if(qbytes){
-            bulk_g2s(stq(s), B.qual + a, qbytes, &mbar[s]);
-            bulk_g2s(stb(s), B.bases2 + b0, bbytes, &mbar[s]);
-        }
-    };
-
-    if(ntiles > 0){
-        const int nt = (int)min((uint32_t)T, hi - lo);
-        for(int i = threadIdx.x; i < nt; i += THREADS){ sto(0)[i] = B.offsets[lo + i]; stl(0)[i] = B.lengths[lo + i]; }
-    }
-    __syncthreads();
-    if(threadIdx.x == 0 && ntiles > 0) issue(0, (int)min((uint32_t)T, hi - lo));
-
-    Acc1 common, preo, posto;
-    common.zero(); preo.zero(); posto.zero();
-    int leftC = 255, leftO = 255;
-    Tally tl = {};
-    const bool fast_filter = !P.complexity_enabled;
-
-    for(int k = 0; k < ntiles; ++k){
-        const int s = k & 1;
-        const uint8_t* Sq = stq(s); const uint8_t* Sb = stb(s);
-        const uint32_t* So = sto(s); const uint16_t* Sl = stl(s);
-        const uint32_t t0 = lo + (uint32_t)k * T;
-        const int nt = (int)min((uint32_t)T, hi - t0);
-        const uint32_t t1 = t0 + T;
-        const int nt1 = (k + 1 < ntiles) ? (int)min((uint32_t)T, hi - t1) : 0;
-        uint32_t moff = 0, mlen = 0;                                   // next tile's metadata: loads in flight during phase 1
-        if((int)threadIdx.x < nt1){ moff = B.offsets[t1 + threadIdx.x]; mlen = B.lengths[t1 + threadIdx.x]; }
-        mbar_wait(&mbar[s], (uint32_t)(k >> 1) & 1u);
-        const uint32_t a0 = So[0];
-        const uint32_t bshift = (a0 >> 2) & 15u;
-        // ---------------- phase 1: one thread per read ----------------
-        for(int i = threadIdx.x; i < nt; i += THREADS){
-            uint32_t doff = So[i] - a0, dlen = Sl[i];
-            const uint32_t padded = (dlen + 15u) & ~15u;
-            bool ok = !(So[i] & 15u) && So[i] >= a0 && doff + padded <= qcap && dlen <= (uint32_t)C;
-            if(ok && i + 1 < nt) ok = (So[i + 1] == So[i] + padded);            // dense, ordered batch
-            if(!ok){ atomicOr(D.err, dlen > (uint32_t)C ? 1u : 2u); doff = 0; dlen = 0; }
-            ReadView v; v.q = Sq + doff; v.b2 = Sb + bshift + (doff >> 2); v.start = 0; v.len = (int)dlen;
-            fq_read_result rec = {};
-            if(fast_filter){
-                const bool alive = dev_trim_and_cut(P, v, P.trim_front1, P.trim_tail1);
-                if(alive){
-                    if(P.polyg_enabled) dev_trim_polyg(v, P.polyg_min_len, P.polyg_max_mismatch, P.polyg_one_mismatch_each, rec, tl);
-                    if(P.adapter_trim_enabled && P.adapter_r1_len > 0) trim_by_sequence_any(D, v, 0, rec, tl);
-                    if(P.polyx_enabled) dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec, tl);
-                    if(P.trim_max_len1 > 0 && P.trim_max_len1 < v.len) view_resize(v, P.trim_max_len1);
-                }
-                int result = FQK_PASS_FILTER;
-                if(!alive || v.len == 0) result = FQK_FAIL_LENGTH;
-                else{
-                    if(P.qual_filter_enabled){
-                        int lowq, nn, total;
-                        swar_counts(smem_u32(Sq + doff), v.start, v.len, P.low_quality_limit,
-                                    P.average_quality_limit > 0, lowq, nn, total);
-                        if(lowq > P.low_quality_base_limit) result = FQK_FAIL_QUALITY;
-                        else if(P.average_quality_limit > 0 && P.average_quality_limit > (double)total / v.len) result = FQK_FAIL_QUALITY;
-                        else if(nn > P.n_base_limit) result = FQK_FAIL_N_BASE;
-                    }
-                    if(result == FQK_PASS_FILTER && P.length_filter_enabled){
-                        if(v.len < P.min_read_length) result = FQK_FAIL_LENGTH;
-                        else if(P.max_read_length > 0 && v.len > P.max_read_length) result = FQK_FAIL_TOO_LONG;
-                    }
-                }
-                rec.result = (uint8_t)result;
-                if(!alive){ rec.flags |= FQK_F_DROPPED; rec.start = 0; rec.len = 0; }
-                else { rec.start = (uint16_t)v.start; rec.len = (uint16_t)v.len; }
-            }else se_read(D, v, rec, tl);
-            out[t0 + i] = rec;
-            atomicAdd(&bc->filter[rec.result], 1u);
-            const bool pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
-            const uint32_t kind = pass ? ((rec.start == 0 && rec.len == dlen) ? 0u : 2u) : 1u;
-            desc[i] = make_desc(doff, dlen, rec.start, rec.len, kind);
-            atomicAdd(smPre + 4 * NSETS * C + dlen, 1u);
-            if(pass) atomicAdd(smPost + 4 * NSETS * C + rec.len, 1u);
-        }
-        if((int)threadIdx.x < nt1){ sto(s ^ 1)[threadIdx.x] = moff; stl(s ^ 1)[threadIdx.x] = (uint16_t)mlen; }
-        __syncthreads();
-        if(threadIdx.x == 0 && nt1 > 0) issue(s ^ 1, nt1);
-        // ---------------- phase 2: SWAR statistics ----------------
-        if(active){
-            const uint32_t sq0 = sp32 + (uint32_t)s * stage_bytes, sb0 = sq0 + qcap + bshift;
-            const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;           // this thread's word of a read at tile offset 0
-            const uint32_t sd = sd32;
-            // software pipeline: descriptor and data of the next read are loaded before the current one is reduced
-            uint2 dv = make_uint2(0u, 0u); uint32_t qraw = 0, b = 0;
-            auto fetch = [&](int i, uint2& d, uint32_t& q, uint32_t& bb){
-                d = lds64(sd + 8 * i);
-                const uint32_t off = (d.x & 0x1FFFFu) << 4, len = d.x >> 17;
-                const bool in = (uint32_t)(4 * w) < len;
-                q = lds32(in ? sqw + off : zero_addr);                 // words outside the read read a zero word
-                bb = in ? lds8(sbw + (off >> 2)) : 0u;
-            };
-            if(g < nt) fetch(g, dv, qraw, b);
-            for(int i = g; i < nt; i += G){
-                const uint2 dc = dv; const uint32_t qc = qraw, bcur = b;
-                if(i + G < nt) fetch(i + G, dv, qraw, b);
-                const uint32_t kind = dc.y >> 26;
-                if(kind == 0){
-                    acc_word(common, qc, bcur);
-                    if(--leftC == 0){ fold(common, l2); leftC = 255; }
-                }else{
-                    acc_word(preo, qc, bcur);
-                    if(kind == 2){
-                        const uint32_t off = (dc.x & 0x1FFFFu) << 4;
-                        const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
-                        const int nv = (int)plen - 4 * w;
-                        if(nv > 0){
-                            const uint32_t p = off + start + 4 * w;
-                            const uint32_t a1 = p & ~3u, sh = p & 3u;
-                            const uint32_t w0 = lds32(sq0 + a1);
-                            const uint32_t w1 = sh ? lds32(sq0 + a1 + 4) : 0u;
-                            uint32_t q2 = __funnelshift_r(w0, w1, sh * 8);
-                            const uint32_t c0 = lds8(sb0 + (p >> 2)), c1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
-                            uint32_t b2 = ((c0 | (c1 << 8)) >> (2 * sh)) & 0xFF;
-                            if(nv < 4){ q2 &= (1u << (8 * nv)) - 1u; b2 &= (1u << (2 * nv)) - 1u; }
-                            acc_word(posto, q2, b2);
-                        }
-                    }
-                    if(--leftO == 0){ drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w); leftO = 255; }
-                }
-            }
-        }
-        __syncthreads();
-    }
-    if(active){
-        fold(common, l2);
-        drain_l2(l2, smPre, smPost, C, w);
-        drain_l1(preo, smPre, nullptr, C, w); drain_l1(posto, smPost, nullptr, C, w);
-    }
-    counters_add_tally(bc, tl);
-    __syncthreads();
-    retire(smPre, C, D.L, flat + D.L.stats_off[0]);
-    retire(smPost, C, D.L, flat + D.L.stats_off[2]);
-    counters_flush(bc, D.L, flat);
-}
-
 
 // ===========================================================================
 // Warp-specialised variant (the default): 8 statistics warps + 8 trim warps per block.
@@ -502,9 +183,6 @@ constexpr int NS = 3, MS = 4;
 constexpr int ws_trim_threads(int nstat){ return nstat == 128 ? 512 : 256; }
 constexpr int KMER_SMEM_MAX = 6;
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar){
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
 
 // phase 1 of one read staged in shared memory: the per-read sequence of processSingleEnd
 // (src/seprocessor.cpp:313-340); returns the record
@@ -608,7 +286,6 @@ struct QuadAcc {
         }
     }
 };
-__device__ __forceinline__ uint32_t dp4(uint32_t a, uint32_t b, uint32_t c){ return __dp4a(a, b, c); }
 
 // q0..q3: the thread's quality word of four reads (0 outside a read), b0..b3: their code bytes
 __device__ __forceinline__ void quad_accumulate(QuadAcc& A, uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3,
@@ -1044,22 +721,6 @@ size_t ws_smem_bytes(int W, int T, int K = 0){
 
 size_t g_smem_optin = 0;
 
-size_t fused_smem_bytes(int W, int T){
-    const int C = 4 * W, Cp = (C + 15) & ~15;
-    size_t s = (size_t)2 * (4 * NSETS * C + C + 1) * 4 + sizeof(BlockCounters) + 8 + 24 + (size_t)T * sizeof(Desc) + 16;
-    s += (size_t)L2_SLOTS * THREADS * 4;
-    s += 2 * ((size_t)T * Cp + (((size_t)T * Cp / 4 + 15) & ~(size_t)15) + 16 + ((T * 4 + 15) & ~15) + ((T * 2 + 15) & ~15));
-    return s + 128;
-}
-// largest tile (multiple of the group count, at most THREADS reads) that fits one block per SM
-int fused_tile(int W){
-    const int G = THREADS / W;
-    const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 2048 : 0;
-    for(int T = THREADS / G * G; T >= G; T -= G)
-        if(fused_smem_bytes(W, T) <= budget) return T;
-    return 0;
-}
-
 #include "fqk_se3.cuh"
 
 // largest tile (multiple of 32 reads, whole quads per statistics group preferred) whose NS stages fit
@@ -1087,7 +748,6 @@ static int ws_tile(int W, int K = 0);
 
 void fused_configure(const cudaDeviceProp& prop){
     g_smem_optin = prop.sharedMemPerBlockOptin;
-    cudaFuncSetAttribute(k_fused_se, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_fused_se_ws<0, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_fused_se_ws<0, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_fused_se_ws<0, false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
@@ -1103,11 +763,11 @@ bool fused_supported_se(const DevParams& D, const DevBatch& B){
     if(D.P.kmer_len > 13) return false;                    // k-mers longer than the 16-base window: generic kernels
     const int W = (int)(D.L.max_cycles + 3) / 4;
     if(D.P.kmer_len && ws_tile(W, D.P.kmer_len) <= 0) return false;   // only the warp-specialised kernel counts k-mers
-    if(W < 8 || W > THREADS) return false;
+    if(W < 8 || W > 256) return false;
     if((reinterpret_cast<uintptr_t>(B.qual) | reinterpret_cast<uintptr_t>(B.bases2) | reinterpret_cast<uintptr_t>(B.offsets) |
         reinterpret_cast<uintptr_t>(B.lengths)) & 15) return false;          // bulk copies: 16-byte aligned sources
     if(B.total % FQK_BATCH_PAD) return false;
-    return fused_tile(W) >= THREADS / W;
+    return ws_tile(W, D.P.kmer_len) > 0 || v3_tile(W) > 0;
 }
 
 static int ws_tile(int W, int K){
@@ -1123,7 +783,6 @@ static int ws_tile(int W, int K){
 int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, uint64_t* flat, int sms, cudaStream_t st,
                     int variant){
     const int W = (int)(D.L.max_cycles + 3) / 4;
-    const int G = THREADS / W;
     if(variant == 0 && !D.P.kmer_len && v3_tile(W) > 0){
         const int T = v3_tile(W);
         int rpb = (int)((B.n + sms - 1) / sms);
@@ -1154,13 +813,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         }
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
-    const int T = fused_tile(W);
-    int rpb = (int)((B.n + sms - 1) / sms);
-    rpb = std::min(rpb, 60000 * G);                        // 16-bit level-2 count lanes: < 65536 reads per thread
-    rpb = (rpb + T - 1) / T * T;
-    const int grid = (int)((B.n + rpb - 1) / rpb);
-    k_fused_se<<<grid, THREADS, fused_smem_bytes(W, T), st>>>(D, B, out, flat, W, T, rpb);
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    return -1;
 }
 
 // paired-end statistics from the records of k_trim_pe: read1 pass, read2 pass and (with -m) the merged tails

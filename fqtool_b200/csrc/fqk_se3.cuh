@@ -45,40 +45,6 @@ __host__ __device__ inline V3L v3_layout(int W, int T){
     return l;
 }
 
-// mbarrier wait for the long waits between roles: try_wait with a suspend-time hint parks the thread in hardware
-// until the phase completes (or the hint expires), so a waiting warp issues almost nothing; a spinning warp would
-// take issue slots from the working warps (12 % of all instructions in the first version)
-__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns){
-    uint32_t ok = 0;
-    const uint32_t a = smem_u32(bar);
-    for(;;){
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity), "r"(ns) : "memory");
-        if(ok) break;
-    }
-}
-// Named barriers (bar.sync / bar.arrive) for the two handshakes that have no transaction count: a warp blocked in
-// bar.sync is parked by the hardware and issues nothing, whereas mbarrier.try_wait returns after a few tens of
-// nanoseconds whatever the hint, and the retry loops of the waiting warps took 16 % of all issued instructions
-// (profiles/r01d_k_se_v3_lines.txt).  ids 1..NS: tile ready (CH trim-warp arrivals + the statistics warps),
-// ids NS+1..2NS: stage free (the statistics warps arrive, the producer warp waits).
-__device__ __forceinline__ void nb_sync(int id, int nthreads){ asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory"); }
-__device__ __forceinline__ void nb_arrive(int id, int nthreads){ asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory"); }
-// mbarrier wait with a short back-off between polls (the `full` barriers: completed by the bulk copies)
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity){
-    uint32_t ok = 0, ns = 32;
-    const uint32_t a = smem_u32(bar);
-    for(;;){
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
-        if(ok) break;
-        __nanosleep(ns);
-        ns = min(ns * 2u, 256u);
-    }
-}
-__device__ __forceinline__ void sts16(uint32_t a, uint32_t v){ asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
-__device__ __forceinline__ void reds_add(uint32_t a, uint32_t v){ asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
-
 // SWAR word path without the N class (filled by the trim lanes)
 __device__ __forceinline__ void acc_word_nf(Acc1& a, uint32_t qraw, uint32_t b){
     const uint32_t q7 = qraw & 0x7F7F7F7Fu;
@@ -197,126 +163,6 @@ __device__ __forceinline__ void quad_drain_nf(QuadAccNF& A, uint32_t* smA, uint3
     }
     quad_drain1_nf(v, smA, smB, C, w);
     A.zero();
-}
-
-// Filter::trimAndCut (src/filter.cpp:69-189) on a read staged in shared memory (qa = shared address of quality
-// byte 0).  Same statements as dev_trim_and_cut (fqk_trim.cuh), explicit shared loads instead of generic ones.
-__device__ __forceinline__ int sq7(uint32_t qa, int i){ return (int)(lds8(qa + (uint32_t)i) & 0x7Fu); }
-__device__ __forceinline__ bool sisn(uint32_t qa, int i){ return (lds8(qa + (uint32_t)i) & 0x80u) != 0; }
-// quality values (flag masked) of positions p .. p+7 of a staged read as two words; p may be unaligned or negative
-__device__ __forceinline__ void ldq8(uint32_t qa, int p, uint32_t& lo, uint32_t& hi){
-    const uint32_t addr = qa + (uint32_t)p, a = addr & ~3u, sh = (addr & 3u) * 8u;
-    const uint32_t w0 = lds32(a), w1 = lds32(a + 4), w2 = lds32(a + 8);
-    lo = __funnelshift_r(w0, w1, sh) & 0x7F7F7F7Fu; hi = __funnelshift_r(w1, w2, sh) & 0x7F7F7F7Fu;
-}
-__device__ __forceinline__ bool s_trim_and_cut(const fq_params& P, uint32_t qa, int l, int F, int T, int& ostart, int& olen){
-    const bool ef = P.cut_front_enabled, er = P.cut_right_enabled, et = P.cut_tail_enabled;
-    ostart = 0; olen = l;
-    if(F == 0 && T == 0 && !ef && !er && !et) return true;
-    int rlen = l - F - T;
-    if(rlen < 0) return false;
-    if(!ef && !er && !et){ ostart = F; olen = rlen; return true; }
-    if(ef){
-        const int w = P.cut_front_window;
-        if(l - F - T - w <= 0) return false;
-        const int thr = w * (33 + P.cut_front_qual);
-        int s = F, sum = 0;
-        if(w == 4){                              // four window positions per step from seven bytes
-            const int lim = l - T;
-            s = lim - 4;                         // where the scalar loop ends when no window passes
-            for(int base = F; base + 4 < lim; base += 4){
-                uint32_t lo, hi; ldq8(qa, base, lo, hi);
-                uint32_t m = 0;
-#pragma unroll
-                for(int j = 0; j < 4; ++j){
-                    const int sj = (int)dp4(j ? __funnelshift_r(lo, hi, 8 * j) : lo, 0x01010101u, 0u);
-                    m |= (sj >= thr && base + j + 4 < lim) ? (1u << j) : 0u;
-                }
-                if(m){ s = base + __ffs((int)m) - 1; break; }
-            }
-        }else{
-            for(int i = 0; i < w - 1; ++i) sum += sq7(qa, s + i);
-            for(; s + w < l - T; ++s){
-                sum += sq7(qa, s + w - 1);
-                if(s > F) sum -= sq7(qa, s - 1);
-                if(sum >= thr) break;
-            }
-        }
-        if(s > 0) s += w - 1;
-        while(s < l && sisn(qa, s)) ++s;
-        F = s;
-        rlen = l - F - T;
-    }
-    if(er){
-        const int w = P.cut_right_window;
-        if(l - F - T - w <= 0) return false;
-        const int thr = w * (33 + P.cut_right_qual);
-        int s = F, sum = 0;
-        bool found = false;
-        for(int i = 0; i < w - 1; ++i) sum += sq7(qa, s + i);
-        for(; s + w < l - T; ++s){
-            sum += sq7(qa, s + w - 1);
-            if(s > F) sum -= sq7(qa, s - 1);
-            if(sum < thr){ found = true; break; }
-        }
-        if(found){
-            const int qr = 33 + P.cut_right_qual;
-            while(s < l - 1 && sq7(qa, s) >= qr) ++s;
-            rlen = s - F;
-        }
-    }
-    if(!er && et){
-        const int w = P.cut_tail_window;
-        if(l - F - T - w <= 0) return false;
-        const int thr = w * (33 + P.cut_tail_qual);
-        int t = l - T - 1, sum = 0;
-        if(w == 4){
-            int top = t;
-            t = F + 3;                           // where the scalar loop ends when no window passes
-            for(; top - 4 >= F; top -= 4){
-                uint32_t lo, hi; ldq8(qa, top - 6, lo, hi);
-                uint32_t m = 0;
-#pragma unroll
-                for(int j = 0; j < 4; ++j){      // candidate t = top - j: window [t-3, t] starts at byte 3-j of (lo, hi)
-                    const int sj = (int)dp4(j < 3 ? __funnelshift_r(lo, hi, 8 * (3 - j)) : lo, 0x01010101u, 0u);
-                    m |= (sj >= thr && top - j - 4 >= F) ? (1u << j) : 0u;
-                }
-                if(m){ t = top - (__ffs((int)m) - 1); break; }
-            }
-        }else{
-            for(int i = 0; i < w - 1; ++i) sum += sq7(qa, t - i);
-            for(; t - w >= F; --t){
-                sum += sq7(qa, t - w + 1);
-                if(t < l - T - 1) sum -= sq7(qa, t + 1);
-                if(sum >= thr) break;
-            }
-        }
-        if(t < l - 1) t -= w - 1;
-        while(t >= 0 && sisn(qa, t)) --t;
-        rlen = t - F + 1;
-    }
-    if(rlen <= 0 || F >= l - 1) return false;
-    ostart = F; olen = rlen;
-    return true;
-}
-
-// passFilter's counts over a sub-range of a staged read (the parts a trim removed)
-__device__ __noinline__ void range_counts(uint32_t qa, int from, int n, int lim, int& lowq, int& nn){
-    int total; swar_counts(qa, from, n, lim, false, lowq, nn, total);
-}
-// number of N bases of a read; nmask flags the 32-byte granules that hold one
-__device__ __forceinline__ int n_count(uint32_t qa, int len, uint32_t nmask){
-    int nn = 0;
-    while(nmask){
-        const int gi = __ffs((int)nmask) - 1;
-        nmask &= nmask - 1;
-        const int nw = ((len + 3) >> 2) - 8 * gi;              // the granule may reach into the next read
-        const uint4 v0 = lds128(qa + 32u * gi), v1 = lds128(qa + 32u * gi + 16u);
-        const uint32_t wv8[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-#pragma unroll
-        for(int h = 0; h < 8; ++h) nn += (h < nw) ? __popc(wv8[h] & 0x80808080u) : 0;
-    }
-    return nn;
 }
 
 // The per-read sequence of processSingleEnd (src/seprocessor.cpp:313-340) when only quality cuts, fixed trims and

@@ -296,9 +296,10 @@ uint64_t fqk_launch_count(const fqk_ctx* ctx);    /* kernels launched so far    
 #define FQK_T_SLOTS 5
 int  fqk_set_kernel_timing(fqk_ctx* ctx, int enabled);
 int  fqk_kernel_times(fqk_ctx* ctx, double ms[FQK_T_SLOTS], uint64_t launches[FQK_T_SLOTS]);
-/* implementation selector for A/B tests: 0 = automatic (fused kernel when the
- * configuration allows), 1 = generic kernels only, 2 = single-role fused kernel,
- * 3 = the first warp-specialised fused kernel (k_fused_se_ws) also for single-end batches */
+/* implementation selector for A/B tests: 0 = automatic (fused kernels when the
+ * configuration allows), 1 = generic kernels only, 3 = the first warp-specialised
+ * fused kernel (k_fused_se_ws) for single-end batches and the two-phase path
+ * (k_trim_pe + statistics passes) for paired-end batches; 2 is retired */
 int  fqk_set_impl(fqk_ctx* ctx, int impl);
 
 /* corrections made by the last fqk_process_pe / fqk_process_pe_device call (synchronises);

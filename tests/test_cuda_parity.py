@@ -9,7 +9,7 @@ from tests import configs, util
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2, 3], ids=["auto", "generic", "fused_single_role", "fused_ws"])
+@pytest.mark.parametrize("impl", [0, 1, 3], ids=["auto", "generic", "fused_ws"])
 @pytest.mark.parametrize("name", list(configs.SE))
 def test_se(name, impl):
     opt = configs.options(name)
