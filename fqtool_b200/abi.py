@@ -61,7 +61,7 @@ class FqParams(C.Structure):
 
 class FqBatch(C.Structure):
     _fields_ = [
-        ("n_reads", C.c_uint32), ("reserved", C.c_uint32),
+        ("n_reads", C.c_uint32), ("max_len", C.c_uint32),
         ("first_index", C.c_uint64), ("total_bases", C.c_uint64),
         ("offsets", C.c_void_p), ("lengths", C.c_void_p),
         ("bases2", C.c_void_p), ("qual", C.c_void_p),

@@ -301,7 +301,7 @@ static int grid_for(fqk_ctx* c, uint32_t n, int per_block, int blocks_per_sm){
 
 static DevBatch to_dev(const fq_batch* b){
     DevBatch d; d.n = b->n_reads; d.first_index = b->first_index; d.total = b->total_bases; d.offsets = b->offsets; d.lengths = b->lengths;
-    d.bases2 = b->bases2; d.qual = b->qual;
+    d.bases2 = b->bases2; d.qual = b->qual; d.max_len = b->max_len;
     return d;
 }
 
@@ -338,6 +338,19 @@ static int launch_pe(fqk_ctx* c, const DevBatch& B1, const DevBatch& B2, fq_read
     Timer all(c, FQK_T_ALL);
     const bool correct = c->D.P.correction_enabled != 0;
     const int Cs = c->stats_cs_pe;
+    if(c->impl == 0 && pe4_supported(c->D, B1, B2)){
+        // one fused launch: trim + filter + the four Stats objects (the duplication table keeps its own kernel)
+        if(c->D.P.dup_enabled){
+            Timer t(c, FQK_T_DUP);
+            k_dup<<<grid_for(c, B1.n, 256, 8), 256, 0, c->stream>>>(c->D, B1, B2, 1, c->tab128, c->first64); c->launches++;
+            c->dup_final = false;
+        }
+        Timer t(c, FQK_T_FUSED);
+        int nl = pe4_launch(c->D, B1, B2, o1, o2, op, c->flat, c->sms, c->stream);
+        if(nl < 0) return fail(c, FQK_E_CUDA, "fused PE launch failed");
+        c->launches += nl;
+        return 0;
+    }
     // everything that reads the RAW pair runs before k_trim_pe when -c corrects the batch in place
     if(c->D.P.dup_enabled){
         Timer t(c, FQK_T_DUP);
@@ -418,6 +431,9 @@ static int stage(fqk_ctx* c, StagedBatch& s, const fq_batch* b, cudaStream_t st 
     s.dev.n = b->n_reads; s.dev.first_index = b->first_index; s.dev.total = b->total_bases;
     s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
     s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
+    uint32_t mx = b->max_len;
+    if(!mx && c->D.P.is_paired) for(size_t r = 0; r < n; ++r) mx = std::max<uint32_t>(mx, b->lengths[r]);   // the fused PE kernel sizes its tiles by it
+    s.dev.max_len = mx;
     return 0;
 }
 
@@ -446,11 +462,12 @@ static int stage_ascii(fqk_ctx* c, int m, const fq_ascii_batch* b){
     CU(cudaMemcpyAsync(c->aseq[m].p, b->seq + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->aqual[m].p, b->qual + b->off[0], chars, cudaMemcpyHostToDevice, c->stream));
     c->hsrc[m].resize(n); c->hdst[m].resize(n); c->hlen[m].resize(n);
-    uint64_t pos = 0;
+    uint64_t pos = 0, maxl = 0;
     for(uint32_t r = 0; r < n; ++r){
         const uint64_t l = b->off[r + 1] - b->off[r];
         if(l > FQK_MAX_READ_LEN){ cudaStreamSynchronize(c->stream); return fail(c, FQK_E_LIMIT, "read longer than FQK_MAX_READ_LEN"); }   // the copies read the caller's buffers
         c->hsrc[m][r] = (uint32_t)(b->off[r] - b->off[0]); c->hdst[m][r] = (uint32_t)pos; c->hlen[m][r] = (uint16_t)l;
+        if(l > maxl) maxl = l;
         pos += (l + FQK_PAD - 1) / FQK_PAD * FQK_PAD;
         if(pos > 0xFFFFFFF0ull){ cudaStreamSynchronize(c->stream); return fail(c, FQK_E_LIMIT, "batch larger than 2^32 padded bases"); }
     }
@@ -474,7 +491,7 @@ static int stage_ascii(fqk_ctx* c, int m, const fq_ascii_batch* b){
     }
     s.dev.n = n; s.dev.first_index = b->first_index; s.dev.total = total;
     s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
-    s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p;
+    s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p; s.dev.max_len = (uint32_t)maxl;
     return 0;
 }
 

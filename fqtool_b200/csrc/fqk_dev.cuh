@@ -20,6 +20,7 @@ struct DevBatch {
     const uint16_t* lengths;
     const uint8_t* bases2;
     const uint8_t* qual;
+    uint32_t max_len;      // longest read of the batch, 0 = unknown (fq_batch::max_len)
 };
 
 // base classes used on the device: 0 A, 1 T, 2 C, 3 G, 4 N

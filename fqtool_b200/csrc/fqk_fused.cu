@@ -722,6 +722,7 @@ size_t ws_smem_bytes(int W, int T, int K = 0){
 size_t g_smem_optin = 0;
 
 #include "fqk_se3.cuh"
+#include "fqk_pe4.cuh"
 
 // largest tile (multiple of 32 reads, whole quads per statistics group preferred) whose NS stages fit
 int v3_tile(int W){
@@ -757,6 +758,7 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -846,4 +848,28 @@ int ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B
     int n = 2;
     if(merge){ k_fused_se_ws<2, false, 256><<<grid, 512, ws_smem_bytes(W, T, 0), st>>>(D, B2, nullptr, flat, W, T, rpb, M3); ++n; }
     return cudaGetLastError() == cudaSuccess ? n : -1;
+}
+
+// fused paired-end kernel: one launch per pair of batches
+static int pe4_maxlen(const DevBatch& B1, const DevBatch& B2){
+    return (B1.max_len && B2.max_len) ? (int)std::max(B1.max_len, B2.max_len) : 0;
+}
+bool pe4_supported(const DevParams& D, const DevBatch& B1, const DevBatch& B2){
+    if((reinterpret_cast<uintptr_t>(B1.qual) | reinterpret_cast<uintptr_t>(B1.bases2) | reinterpret_cast<uintptr_t>(B1.offsets) |
+        reinterpret_cast<uintptr_t>(B1.lengths) | reinterpret_cast<uintptr_t>(B2.qual) | reinterpret_cast<uintptr_t>(B2.bases2) |
+        reinterpret_cast<uintptr_t>(B2.offsets) | reinterpret_cast<uintptr_t>(B2.lengths)) & 15) return false;   // bulk copies: 16-byte aligned sources
+    if(B1.total % FQK_BATCH_PAD || B2.total % FQK_BATCH_PAD) return false;
+    return v4_plan(D, pe4_maxlen(B1, B2), g_smem_optin).ok;
+}
+int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_read_result* o1, fq_read_result* o2,
+               fq_pair_result* op, uint64_t* flat, int sms, cudaStream_t st){
+    const V4Plan p = v4_plan(D, pe4_maxlen(B1, B2), g_smem_optin);
+    if(!p.ok) return -1;
+    int ppb = (int)((B1.n + sms - 1) / sms);
+    ppb = std::min(ppb, 1 << 23);                          // 32-bit per-block sums of quality characters
+    ppb = (ppb + p.T - 1) / p.T * p.T;
+    const int grid = (int)((B1.n + ppb - 1) / ppb);
+    static const int dbg = getenv("FQK_V4_DEBUG") ? atoi(getenv("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
+    k_pe_v4<<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }

@@ -14,3 +14,8 @@ bool ws_stats_supported_pe(const DevParams& D, const DevBatch& B1, const DevBatc
 int  ws_stats_launch_pe(const DevParams& D, const DevBatch& B1, const DevBatch& B2, const fq_read_result* r1,
                         const fq_read_result* r2, const fq_pair_result* rp, uint64_t* flat, int sms, cudaStream_t st,
                         const uint32_t* maxlen2 /* device: longest raw read of each mate, or nullptr */);
+
+// fused paired-end kernel k_pe_v4 (fqk_pe4.cuh): trim + filter + all four Stats objects in one pass
+bool pe4_supported(const DevParams& D, const DevBatch& B1, const DevBatch& B2);
+int  pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_read_result* o1, fq_read_result* o2,
+                fq_pair_result* op, uint64_t* flat, int sms, cudaStream_t st);

@@ -22,6 +22,12 @@
 #include "fqk_smem.cuh"
 
 #define V4_FULL 0xffffffffu
+// Out-of-line helpers keep the kernel small (instruction-fetch stalls were 21 % of the samples of the fully inlined
+// version, profiles/r02c_*).  ptxas 12.9 fails register allocation ("register count of 168") when v4_sweep,
+// v4_polyg_ni, v4_trim_and_cut or v4_polyx are out of line inside this setmaxnreg kernel, so those four stay inline
+// and are instantiated once, in a loop over the two mates.
+#define V4_NI __noinline__
+#define V4_IN __forceinline__
 #ifndef EMU_MARK2
 #define EMU_MARK2(k)
 #endif
@@ -44,7 +50,7 @@ __host__ __device__ inline V4L v4_layout(int Wr, int Wm, int T, int NS, int ins_
     l.T = T; l.NS = NS;
     l.Cr = 4u * (uint32_t)Wr; l.Cm = 4u * (uint32_t)Wm; l.Cp = (l.Cr + 15u) & ~15u;
     l.statw_r = 4 * NSETS * l.Cr + l.Cr + 1; l.statw_m = 4 * NSETS * l.Cm + l.Cm + 1;
-    uint32_t o = 128;
+    uint32_t o = 256;                         // the head of the block's shared memory holds this struct
     l.o_pre[0] = o; o += 4 * l.statw_r;
     l.o_pre[1] = o; o += 4 * l.statw_r;
     l.o_post[0] = o; o += 4 * l.statw_m;
@@ -66,7 +72,7 @@ __host__ __device__ inline V4L v4_layout(int Wr, int Wm, int T, int NS, int ins_
     }
     for(int m = 0; m < 2; ++m){ s = (s + 15u) & ~15u; l.o_ex[m] = s; s += (uint32_t)T * 8; }
     l.o_exm = s; s += (uint32_t)T * 8;
-    l.o_cnt = s; s += 32;                     // [0] nex1 [1] nex2 [2] nM [3] uniform flags [4] pairs in the tile
+    l.o_cnt = s; s += 32;                     // [0] nex1 [1] nex2 [2] nM [3] uniform flags [4] pairs in the tile [5] tile tag
     l.stage_bytes = (s + 127u) & ~127u;
     l.total = l.o_stage + (uint32_t)NS * l.stage_bytes;
     return l;
@@ -83,13 +89,13 @@ struct PeRead {
 // one uniform 16-byte sweep of the padded raw read (see fast_phase1a in fqk_se3.cuh).  Lanes start at chunk
 // (lane >> 2) & 1: with a read pitch of 160 bytes the eight lanes of a quarter warp would otherwise land on four
 // 16-byte bank groups (two-way conflicts); the sums do not depend on the order.
-__device__ __forceinline__ void v4_sweep(PeRead& R, bool count, uint32_t L4, int lane){
-    const uint32_t nch = ((uint32_t)R.rawlen + 15u) >> 4;
+__device__ V4_IN uint2 v4_sweep(uint32_t qa, int rawlen, bool count, uint32_t L4, int lane){
+    const uint32_t nch = ((uint32_t)rawlen + 15u) >> 4;
     uint32_t nmask = 0, ge = 0, ge2 = 0;
     const uint32_t rot = ((uint32_t)lane >> 2) & 1u;
     for(uint32_t cc = 0; cc < nch; ++cc){
         uint32_t c = cc + rot; if(c >= nch) c = 0;
-        const uint4 v = lds128(R.qa + 16u * c);
+        const uint4 v = lds128(qa + 16u * c);
         const uint32_t fl = ((v.x | v.y) | (v.z | v.w)) & 0x80808080u;
         nmask |= (fl ? 1u : 0u) << (c >> 1);
         if(count){
@@ -99,7 +105,13 @@ __device__ __forceinline__ void v4_sweep(PeRead& R, bool count, uint32_t L4, int
             ge2 = dp4(((v.w | 0x80808080u) - L4) & 0x80808080u, 0x01010101u, ge2);
         }
     }
-    R.ge = ge + ge2; R.nmask = nmask;
+    return make_uint2(ge + ge2, nmask);
+}
+// Filter::trimAndCut out of line: len | start << 12 | alive << 31
+__device__ V4_IN uint32_t v4_trim_and_cut(const fq_params* P, uint32_t qa, int l, int F, int T){
+    int st, ln;
+    const bool alive = s_trim_and_cut(*P, qa, l, F, T, st, ln);
+    return (uint32_t)ln | ((uint32_t)st << 12) | (alive ? 0x80000000u : 0u);
 }
 
 // Filter::passFilter's counts (src/filter.cpp:15-25) of the current view: the sweep of the raw read minus what the
@@ -117,15 +129,60 @@ __device__ __forceinline__ ReadView v4_view(const PeRead& R){
     ReadView v; v.q = smem_ptr(R.qa); v.b2 = smem_ptr(R.ba); v.start = R.start; v.len = R.len; return v;
 }
 // Filter::passFilter of the current view (same decisions as pass_filter_fast, fqk_pe.cuh)
-__device__ __forceinline__ int v4_pass_filter(const fq_params& P, const PeRead& R, bool isnull){
+__device__ V4_NI int v4_pass_filter_ni(const fq_params* Pp, uint32_t qa, uint32_t ba, int rawlen, int start, int len, uint32_t ge, uint32_t nmask, bool isnull){
+    const fq_params& P = *Pp;
+    PeRead R; R.qa = qa; R.ba = ba; R.doff = 0; R.rawlen = rawlen; R.start = start; R.len = len; R.ge = ge; R.nmask = nmask;
     if(isnull || R.len == 0) return FQK_FAIL_LENGTH;
     if(P.complexity_enabled) return dev_pass_filter_view(P, v4_view(R), false);
     if(!P.qual_filter_enabled && !P.length_filter_enabled) return FQK_PASS_FILTER;
     int lowq = 0, nn = 0, total = 0;
-    EMU_MARK2(10);
     if(P.qual_filter_enabled) v4_view_counts(P, R, lowq, nn, total);
-    EMU_MARK2(11);
     return filter_from_counts(P, R.len, lowq, nn, total);
+}
+__device__ __forceinline__ int v4_pass_filter(const fq_params& P, const PeRead& R, bool isnull){
+    return v4_pass_filter_ni(&P, R.qa, R.ba, R.rawlen, R.start, R.len, R.ge, R.nmask, isnull);
+}
+// passFilter of the merged read (OverlapAnalysis::merge, src/overlapanalysis.cpp:74-93): read1's first len1 bases + the
+// last len2 bases of revcomp(read2's view)
+__device__ V4_NI int v4_merged_filter(const fq_params* Pp, uint32_t aqa, uint32_t aba, int astart, int alen,
+                                             uint32_t bqa, uint32_t bba, int bstart, int blen, int ol, int len1, int len2){
+    const fq_params& P = *Pp;
+    if(P.complexity_enabled){
+        ReadView va; va.q = smem_ptr(aqa); va.b2 = smem_ptr(aba); va.start = astart; va.len = alen;
+        ReadView vb; vb.q = smem_ptr(bqa); vb.b2 = smem_ptr(bba); vb.start = bstart; vb.len = blen;
+        return dev_pass_filter(P, len1 + len2, false, [&](int t, int& c, int& q){
+            if(t < len1){ c = va.cls(t); q = va.qual(t); }
+            else { const int u = ol + t - len1; c = rc_cls(vb, u); q = vb.qual(vb.len - 1 - u); }
+        });
+    }
+    // counts of the merged read = read1 prefix + the part of read2 that is appended (order is irrelevant)
+    int l1 = 0, n1 = 0, t1 = 0, l2 = 0, n2 = 0, t2 = 0;
+    if(P.qual_filter_enabled){
+        const bool wt = P.average_quality_limit > 0;
+        swar_counts(aqa, astart, len1, P.low_quality_limit, wt, l1, n1, t1);
+        swar_counts(bqa, bstart + (blen - ol - len2), len2, P.low_quality_limit, wt, l2, n2, t2);
+    }
+    return (len1 + len2 == 0) ? FQK_FAIL_LENGTH : filter_from_counts(P, len1 + len2, l1 + l2, n1 + n2, t1 + t2);
+}
+// AdapterTrimmer::trimBySequence / PolyX::trimPolyX out of line (rare option sets): the new length is returned, record
+// fields and tallies go through temporaries so that the caller's stay in registers
+__device__ V4_NI int v4_adapter_seq(const DevParams* D, uint32_t qa, uint32_t ba, int start, int len, int which, fq_read_result* rec, Tally* tl){
+    ReadView v; v.q = smem_ptr(qa); v.b2 = smem_ptr(ba); v.start = start; v.len = len;
+    const bool hit = trim_by_sequence_any(*D, v, which, *rec, *tl);
+    return v.len | (hit ? 0x40000000 : 0);
+}
+__device__ V4_IN int v4_polyx(const fq_params* P, uint32_t qa, uint32_t ba, int start, int len, fq_read_result* rec, Tally* tl){
+    ReadView v; v.q = smem_ptr(qa); v.b2 = smem_ptr(ba); v.start = start; v.len = len;
+    dev_trim_polyx(v, P->polyx_base_mask, P->polyx_min_len, P->polyx_max_mismatch, P->polyx_one_mismatch_each, *rec, *tl);
+    return v.len;
+}
+__device__ __forceinline__ void v4_merge_rec(fq_read_result& rec, Tally& tl, const fq_read_result& r2, const Tally& t2){
+    rec.flags |= r2.flags; 
+    if(r2.flags & FQK_F_ADAPTER_SEQ){ rec.adapter_pos = r2.adapter_pos; rec.adapter_len = r2.adapter_len; }
+    if(r2.flags & FQK_F_POLYX) rec.polyx_len = r2.polyx_len;
+#pragma unroll
+    for(int b = 0; b < 5; ++b){ tl.polyx_reads[b] += t2.polyx_reads[b]; tl.polyx_bases[b] += t2.polyx_bases[b]; }
+    tl.adapter_reads += t2.adapter_reads; tl.adapter_bases += t2.adapter_bases;
 }
 
 // ------------------------------------------------------------------ polyG as a bit mask
@@ -144,14 +201,14 @@ __device__ __forceinline__ uint32_t tail_g_mask(uint32_t ba, int e, int n){
 }
 // PolyX::trimPolyG (single read), src/polyx.cpp:14-38, on the current view.  The reference's loop can only break at
 // a non-G base, so it is walked mismatch by mismatch over a 32-base mask; firstGpos is the highest G below the break.
-__device__ inline void v4_polyg(PeRead& R, int compareReq, int maxMismatch, int oneEach, fq_read_result& rec, Tally& tl){
-    const int rlen = R.len;
+// Returns new length | tallied bases << 12 | trimmed << 31.
+__device__ V4_IN uint32_t v4_polyg_ni(uint32_t ba, int start, int rlen, int compareReq, int maxMismatch, int oneEach){
     int mismatch = 0, lastG = -1, iexit = rlen;
     int quo = 0, nextq = oneEach;                         // quo = (i + 1) / oneEach for the increasing i of the walk
     bool broke = false;
     for(int b0 = 0; b0 < rlen && !broke; b0 += 32){
         const int n = min(32, rlen - b0);
-        const uint32_t gm = tail_g_mask(R.ba, R.start + rlen - b0, n);
+        const uint32_t gm = tail_g_mask(ba, start + rlen - b0, n);
         const uint32_t valid = n >= 32 ? 0xFFFFFFFFu : ((1u << n) - 1u);
         uint32_t m = ~gm & valid, below = valid;
         while(m){
@@ -164,13 +221,10 @@ __device__ inline void v4_polyg(PeRead& R, int compareReq, int maxMismatch, int 
         const uint32_t gb = gm & below;
         if(gb) lastG = b0 + 31 - __clz((int)gb);
     }
-    if(iexit + 1 >= compareReq){
-        const int firstG = lastG >= 0 ? rlen - 1 - lastG : rlen - 1;
-        if(firstG >= 0 && firstG <= R.len) R.len = firstG;             // Read::resize, src/read.h:181-187
-        rec.flags |= FQK_F_POLYG;
-        rec.polyg_len = (uint16_t)(rlen - firstG);
-        tl.polyx_reads[3] += 1; tl.polyx_bases[3] += (uint32_t)(rlen - firstG);
-    }
+    if(iexit + 1 < compareReq) return (uint32_t)rlen;
+    const int firstG = lastG >= 0 ? rlen - 1 - lastG : rlen - 1;
+    const int nl = (firstG >= 0 && firstG <= rlen) ? firstG : rlen;     // Read::resize, src/read.h:181-187
+    return (uint32_t)nl | ((uint32_t)(rlen - firstG) << 12) | 0x80000000u;
 }
 
 // ------------------------------------------------------------------ warp-cooperative overlap analysis
@@ -233,100 +287,190 @@ __device__ __forceinline__ uint32_t v4_shiftw(uint32_t v, int o, int lane){
 }
 // one alignment a[ao + i] vs r[ro + i], i < ol (ao == 0 or ro == 0): lane i counts the mismatches of overlap
 // positions 16i .. 16i+15; the reference accepts iff fewer than brk mismatches among the first min(50, ol)
-// positions and (diff < limit or ol > 50)  (closed form of src/overlapanalysis.cpp:20-67)
-__device__ __forceinline__ bool v4_verify(PkLane a, int ao, PkLane r, int ro, int ol, bool anyN, int limit, int brk, int lane, int& diff){
-    uint32_t xc = a.c, xn = a.n, yc = r.c, yn = r.n;
-    if(ao){ xc = v4_shiftw(a.c, ao, lane); if(anyN) xn = v4_shiftw(a.n, ao, lane); }
-    if(ro){ yc = v4_shiftw(r.c, ro, lane); if(anyN) yn = v4_shiftw(r.n, ro, lane); }
+// positions and (diff < limit or ol > 50)  (closed form of src/overlapanalysis.cpp:20-67).
+// Returns diff | accepted << 31.  Out of line: the kernel's code size matters (instruction-fetch stalls were 21 %
+// of the first version's samples, profiles/r02c_*).
+__device__ V4_NI uint32_t v4_verify(uint32_t ac, uint32_t an, int ao, uint32_t rc, uint32_t rn, int ro, int ol, bool anyN,
+                                           int limit, int brk, int lane){
+    uint32_t xc = ac, xn = an, yc = rc, yn = rn;
+    if(ao){ xc = v4_shiftw(ac, ao, lane); if(anyN) xn = v4_shiftw(an, ao, lane); }
+    if(ro){ yc = v4_shiftw(rc, ro, lane); if(anyN) yn = v4_shiftw(rn, ro, lane); }
     const uint32_t t = xc ^ yc;
     uint32_t mm = (t | (t >> 1)) & 0x55555555u;
     if(anyN) mm |= xn ^ yn;
     mm &= valid_mask(ol - 16 * lane);
     const uint32_t tot = __reduce_add_sync(V4_FULL, (uint32_t)__popc(mm));
     const uint32_t t50 = __reduce_add_sync(V4_FULL, (uint32_t)__popc(mm & valid_mask(50 - 16 * lane)));
-    diff = (int)tot;
-    if((int)t50 >= brk) return false;
-    return (int)tot < limit || ol > 50;
+    const bool acc = (int)t50 < brk && ((int)tot < limit || ol > 50);
+    return tot | (acc ? 0x80000000u : 0u);
 }
-// OverlapAnalysis::analyze (src/overlapanalysis.cpp:7-72): a = read1's view, r = revcomp of read2's view.  Every lane
-// tests four offsets per step against the first word of the other read (N ignored: an N has code 0, so the code-only
-// count never exceeds the true count and the reject is conservative); survivors are verified in scan order.
-__device__ inline OvRes v4_analyze(PkLane a, int len1, PkLane r, int len2, bool anyN, int limit, int require, int lane){
+__device__ __forceinline__ uint2 ov_pack(int overlapped, int offset, int len, int diff){
+    return make_uint2((uint32_t)offset, (uint32_t)len | ((uint32_t)diff << 12) | (overlapped ? 0x80000000u : 0u));
+}
+__device__ __forceinline__ OvRes ov_unpack(uint2 v){
+    OvRes o; o.offset = (int)v.x; o.len = (int)(v.y & 0xFFFu); o.diff = (int)((v.y >> 12) & 0xFFFu); o.overlapped = (int)(v.y >> 31); return o;
+}
+// both views of one pair packed and read2 reverse-complemented by the whole warp
+struct PkPair { PkLane a, r; int l1, l2; bool anyN; };
+__device__ __forceinline__ PkPair v4_pack_pair(uint32_t qa1, uint32_t ba1, uint32_t p1, uint32_t qa2, uint32_t ba2, uint32_t p2, int lane){
+    PkPair k;
+    const int s1 = (int)(p1 & 0xFFFu), s2 = (int)(p2 & 0xFFFu);
+    k.l1 = (int)((p1 >> 12) & 0xFFFu); k.l2 = (int)((p2 >> 12) & 0xFFFu);
+    const bool n1 = (p1 >> 31) != 0u, n2 = (p2 >> 31) != 0u;
+    k.anyN = n1 || n2;
+    k.a = v4_pack(ba1, qa1, s1, k.l1, n1, lane);
+    const PkLane b = v4_pack(ba2, qa2, s2, k.l2, n2, lane);
+    k.r = v4_revcomp(b, k.l2, n2, lane);
+    return k;
+}
+// OverlapAnalysis::analyze (src/overlapanalysis.cpp:7-72) of ONE pair by the whole warp: every lane tests four
+// offsets per step against the first word of the other read (N ignored: an N has code 0 in both packed reads, so the
+// code-only count never exceeds the true count and the reject is conservative); survivors are verified in scan order.
+// Used when only a few pairs of a chunk need an analysis (the merge-time second call).
+__device__ V4_NI uint2 v4_analyze_coop(uint32_t qa1, uint32_t ba1, uint32_t p1, uint32_t qa2, uint32_t ba2, uint32_t p2,
+                                              int limit, int require, int lane){
+    const PkPair K = v4_pack_pair(qa1, ba1, p1, qa2, ba2, p2, lane);
+    const int len1 = K.l1, len2 = K.l2;
     const int brk = max(limit, 1);
-    OvRes o; o.overlapped = 0; o.offset = 0; o.len = 0; o.diff = 0;
     const bool fast = require >= 16 && len1 >= 16 && len2 >= 16;       // then every overlap is at least 16 long
-    const uint32_t y0 = __shfl_sync(V4_FULL, r.c, 0), x0 = __shfl_sync(V4_FULL, a.c, 0);
-    const int nA = len1 - require, nB = len2 - require;
-    for(int base = 0; base < nA; base += 128){                         // src/overlapanalysis.cpp:20-41
-        const int o0 = base + 4 * lane, wi = o0 >> 4;
-        uint32_t lo = __shfl_sync(V4_FULL, a.c, wi & 31), hi = __shfl_sync(V4_FULL, a.c, (wi + 1) & 31);
-        if(wi > 31) lo = 0u;
-        if(wi + 1 > 31) hi = 0u;
-        uint32_t cm = 0;
+    const uint32_t first[2] = {__shfl_sync(V4_FULL, K.r.c, 0), __shfl_sync(V4_FULL, K.a.c, 0)};
+#pragma unroll 1
+    for(int phase = 0; phase < 2; ++phase){                            // 0: :20-41 (read1 slides), 1: :44-67 (offset = -d)
+        const int nmine = (phase ? len2 : len1) - require;
+        const uint32_t sl = phase ? K.r.c : K.a.c, other = first[phase];
+        for(int base = 0; base < nmine; base += 128){
+            const int o0 = base + 4 * lane, wi = o0 >> 4;
+            uint32_t lo = __shfl_sync(V4_FULL, sl, wi & 31), hi = __shfl_sync(V4_FULL, sl, (wi + 1) & 31);
+            if(wi > 31) lo = 0u;
+            if(wi + 1 > 31) hi = 0u;
+            uint32_t cm = 0;
 #pragma unroll
-        for(int k = 0; k < 4; ++k){
-            const int off = o0 + k;
-            const uint32_t t = __funnelshift_r(lo, hi, 2u * (((uint32_t)o0 & 15u) + k)) ^ y0;
-            uint32_t mm = (t | (t >> 1)) & 0x55555555u;
-            if(!fast) mm &= valid_mask(min(min(len1 - off, len2), 16));
-            if(off < nA && __popc(mm) < brk) cm |= 1u << k;
-        }
-        for(;;){
-            const uint32_t bal = __ballot_sync(V4_FULL, cm != 0u);
-            if(!bal) break;
-            const int src = __ffs((int)bal) - 1;
-            const uint32_t c4 = __shfl_sync(V4_FULL, cm, src);
-            const int off = base + 4 * src + (__ffs((int)c4) - 1);
-            const int ol = min(len1 - off, len2);
-            int diff;
-            if(v4_verify(a, off, r, 0, ol, anyN, limit, brk, lane, diff)){ o.overlapped = 1; o.offset = off; o.len = ol; o.diff = diff; return o; }
-            if(lane == src) cm &= cm - 1u;
+            for(int k = 0; k < 4; ++k){
+                const int off = o0 + k;
+                const uint32_t t = __funnelshift_r(lo, hi, 2u * (((uint32_t)o0 & 15u) + k)) ^ other;
+                uint32_t mm = (t | (t >> 1)) & 0x55555555u;
+                if(!fast) mm &= valid_mask(min(phase ? min(len1, len2 - off) : min(len1 - off, len2), 16));
+                if(off < nmine && __popc(mm) < brk) cm |= 1u << k;
+            }
+            for(;;){
+                const uint32_t bal = __ballot_sync(V4_FULL, cm != 0u);
+                if(!bal) break;
+                const int src = __ffs((int)bal) - 1;
+                const uint32_t c4 = __shfl_sync(V4_FULL, cm, src);
+                const int off = base + 4 * src + (__ffs((int)c4) - 1);
+                const int ol = phase ? min(len1, len2 - off) : min(len1 - off, len2);
+                const uint32_t v = v4_verify(K.a.c, K.a.n, phase ? 0 : off, K.r.c, K.r.n, phase ? off : 0, ol, K.anyN, limit, brk, lane);
+                if(v >> 31) return ov_pack(1, phase ? -off : off, ol, (int)(v & 0x7FFFFFFFu));
+                if(lane == src) cm &= cm - 1u;
+            }
         }
     }
-    for(int base = 0; base < nB; base += 128){                         // src/overlapanalysis.cpp:44-67 (offset = -d)
-        const int d0 = base + 4 * lane, wi = d0 >> 4;
-        uint32_t lo = __shfl_sync(V4_FULL, r.c, wi & 31), hi = __shfl_sync(V4_FULL, r.c, (wi + 1) & 31);
-        if(wi > 31) lo = 0u;
-        if(wi + 1 > 31) hi = 0u;
-        uint32_t cm = 0;
-#pragma unroll
-        for(int k = 0; k < 4; ++k){
-            const int d = d0 + k;
-            const uint32_t t = __funnelshift_r(lo, hi, 2u * (((uint32_t)d0 & 15u) + k)) ^ x0;
-            uint32_t mm = (t | (t >> 1)) & 0x55555555u;
-            if(!fast) mm &= valid_mask(min(min(len1, len2 - d), 16));
-            if(d < nB && __popc(mm) < brk) cm |= 1u << k;
-        }
-        for(;;){
-            const uint32_t bal = __ballot_sync(V4_FULL, cm != 0u);
-            if(!bal) break;
-            const int src = __ffs((int)bal) - 1;
-            const uint32_t c4 = __shfl_sync(V4_FULL, cm, src);
-            const int d = base + 4 * src + (__ffs((int)c4) - 1);
-            const int ol = min(len1, len2 - d);
-            int diff;
-            if(v4_verify(a, 0, r, d, ol, anyN, limit, brk, lane, diff)){ o.overlapped = 1; o.offset = -d; o.len = ol; o.diff = diff; return o; }
-            if(lane == src) cm &= cm - 1u;
-        }
-    }
-    return o;
+    return ov_pack(0, 0, 0, 0);
 }
-// analyze() for every lane of `need`, one pair at a time by the whole warp; each lane keeps its own pair's result
-__device__ inline void v4_analyze_chunk(const PeRead& A, const PeRead& B, bool need, int limit, int require, int lane, OvRes& ov){
+// 16 bases of a staged read starting at base position p (p may lie outside the read: the caller masks)
+struct Win3 { uint32_t w0, w1, w2; uint32_t sh; };                     // three words from the word holding position q
+__device__ __forceinline__ Win3 v4_win3(uint32_t ba, int q){
+    Win3 r; const uint32_t a = ba + 4u * (uint32_t)(q >> 4);           // arithmetic shift: q may be negative
+    r.w0 = lds32(a); r.w1 = lds32(a + 4u); r.w2 = lds32(a + 8u); r.sh = (uint32_t)q & 15u;
+    return r;
+}
+__device__ __forceinline__ uint32_t v4_win16(const Win3& w, uint32_t k){   // bases q+k .. q+k+15, k <= 3
+    const uint32_t s = w.sh + k;
+    return s < 16u ? __funnelshift_r(w.w0, w.w1, 2u * s) : __funnelshift_r(w.w1, w.w2, 2u * (s - 16u));
+}
+
+// OverlapAnalysis::analyze (src/overlapanalysis.cpp:7-72) for the pairs of a chunk.
+//   scan   every lane walks ITS pair's offsets in the reference's order, four per step, all lanes in lock step:
+//          the first min(16, ol) overlap positions are one unaligned 32-bit window of the staged 2-bit bases against
+//          the first word of the other read (loop A: read1 slides over revcomp(read2)[0..16); loop B: read2 slides,
+//          compared in read2's orientation against the reverse complement of read1's first word), XOR, fold, popc.
+//          N bases carry code 0, so the code-only count can exceed the true count only where BOTH reads have an N:
+//          an offset is dropped when the count reaches brk + min(#N read1, #N read2)  (conservative);
+//   verify survivors are checked exactly by the whole warp, one pair at a time, in each lane's scan order: both
+//          views packed (lane j owns word j), read2 reverse-complemented with shuffles, one 16-base word per lane,
+//          two warp sums (v4_verify).
+__device__ V4_NI uint2 v4_overlap_lockstep(uint32_t Aqa, uint32_t Aba, uint32_t pa, uint32_t Bqa, uint32_t Bba, uint32_t pb,
+                                           int nboth, bool need, int limit, int require, int lane){
+    // (timing experiments: bits 16.. of nboth carry FQK_V4_DEBUG; 64 = skip the verification of survivors)
+    // every pair of the chunk has overlaps of at least 16 bases (the caller checks): no length masks in the scan
+    const int brk = max(limit, 1);
+    const int s1 = (int)(pa & 0xFFFu), len1 = (int)((pa >> 12) & 0xFFFu), s2 = (int)(pb & 0xFFFu), len2 = (int)((pb >> 12) & 0xFFFu);
+    const int dbgx = nboth >> 16; nboth &= 0xFFFF;
+    const int qbrk = brk + nboth;
+    const int nA = need ? max(len1 - require, 0) : 0, nB = need ? max(len2 - require, 0) : 0;
+    // first word of the other read, in the orientation of the sliding read
+    const uint32_t r0 = rev2(v4_win16(v4_win3(Bba, s2 + len2 - 16), 0)) ^ 0x55555555u;        // revcomp(read2)[0..16)
+    const uint32_t a0rc = rev2(v4_win16(v4_win3(Aba, s1), 0)) ^ 0x55555555u;                  // revcomp of read1[0..16)
+    uint2 res = ov_pack(0, 0, 0, 0);
+    bool done = !need;
+#pragma unroll 1
+    for(int phase = 0; phase < 2; ++phase){                                // 0: src/overlapanalysis.cpp:20-41, 1: :44-67 (offset = -d)
+        const int nmine = phase ? nB : nA;
+        const int nmax = (int)__reduce_max_sync(V4_FULL, done ? 0u : (uint32_t)nmine);
+        const uint32_t other = phase ? a0rc : r0;
+        // Sixteen offsets per step.  Loop A: offset base+k is the window at read position s1+base+k.  Loop B: d = base+k is
+        // the window that ENDS at len2-d, i.e. starts at q+15-k with q = s2+len2-base-31.  The step is 16 bases, so the
+        // position of the lowest window modulo 16 never changes: two aligned words (32 bases from q) per step, and every
+        // window is one funnel shift by a compile-time amount.
+        const int q00 = phase ? s2 + len2 - 31 : s1;
+        const uint32_t sh = 2u * ((uint32_t)q00 & 15u);
+        uint32_t adr = (phase ? Bba : Aba) + 4u * (uint32_t)(q00 >> 4);
+#pragma unroll 1
+        for(int base = 0; base < nmax; base += 16, adr += phase ? 0xFFFFFFFCu : 4u){
+            uint32_t cm = 0;
+            if(!done && base < nmine){
+                const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4u), w2 = lds32(adr + 8u);
+                const uint32_t A0 = __funnelshift_r(w0, w1, sh), A1 = __funnelshift_r(w1, w2, sh);   // bases q .. q+31
+                const int lim = nmine - base;                                 // offsets base+k with k < lim exist
+#pragma unroll
+                for(int k = 0; k < 16; ++k){
+                    const uint32_t win = phase ? (k == 15 ? A0 : __funnelshift_r(A0, A1, 2 * (15 - k))) : (k == 0 ? A0 : __funnelshift_r(A0, A1, 2 * k));
+                    const uint32_t t = win ^ other;
+                    const uint32_t mm = (t | (t >> 1)) & 0x55555555u;
+                    cm |= (__popc(mm) < qbrk && k < lim) ? (1u << k) : 0u;
+                }
+            }
+            if(dbgx & 64) cm = 0u;
+            while(__any_sync(V4_FULL, cm != 0u)){
+                const uint32_t bal = __ballot_sync(V4_FULL, cm != 0u);
+                const int src = __ffs((int)bal) - 1;
+                const PkPair K = v4_pack_pair(__shfl_sync(V4_FULL, Aqa, src), __shfl_sync(V4_FULL, Aba, src), __shfl_sync(V4_FULL, pa, src),
+                                              __shfl_sync(V4_FULL, Bqa, src), __shfl_sync(V4_FULL, Bba, src), __shfl_sync(V4_FULL, pb, src), lane);
+                const uint32_t c16 = __shfl_sync(V4_FULL, cm, src);
+                const int off = base + (__ffs((int)c16) - 1);
+                const int ol = phase ? min(K.l1, K.l2 - off) : min(K.l1 - off, K.l2);
+                const uint32_t v = v4_verify(K.a.c, K.a.n, phase ? 0 : off, K.r.c, K.r.n, phase ? off : 0, ol, K.anyN, limit, brk, lane);
+                if(lane == src){
+                    if(v >> 31){ res = ov_pack(1, phase ? -off : off, ol, (int)(v & 0x7FFFFFFFu)); done = true; cm = 0u; }
+                    else cm &= cm - 1u;
+                }
+            }
+        }
+    }
+    return res;
+}
+// analyze() for the lanes of `need`: a few pairs go through the warp one at a time, a chunk full of them in lock step
+constexpr int V4_COOP_MAX = 10;
+__device__ __forceinline__ void v4_overlap_chunk(const PeRead& A, const PeRead& B, bool need, int limit, int require, int lane, OvRes& ov, int dbg = 0){
+    const uint32_t mk0 = __ballot_sync(V4_FULL, need);
+    if(!mk0) return;
     const uint32_t pa = (uint32_t)A.start | ((uint32_t)A.len << 12) | (A.nmask ? 1u << 31 : 0u);
     const uint32_t pb = (uint32_t)B.start | ((uint32_t)B.len << 12) | (B.nmask ? 1u << 31 : 0u);
-    for(uint32_t mk = __ballot_sync(V4_FULL, need); mk; mk &= mk - 1u){
-        const int src = __ffs((int)mk) - 1;
-        const uint32_t qa1 = __shfl_sync(V4_FULL, A.qa, src), ba1 = __shfl_sync(V4_FULL, A.ba, src), p1 = __shfl_sync(V4_FULL, pa, src);
-        const uint32_t qa2 = __shfl_sync(V4_FULL, B.qa, src), ba2 = __shfl_sync(V4_FULL, B.ba, src), p2 = __shfl_sync(V4_FULL, pb, src);
-        const int s1 = (int)(p1 & 0xFFFu), l1 = (int)((p1 >> 12) & 0xFFFu), s2 = (int)(p2 & 0xFFFu), l2 = (int)((p2 >> 12) & 0xFFFu);
-        const bool n1 = (p1 >> 31) != 0u, n2 = (p2 >> 31) != 0u, anyN = n1 || n2;
-        const PkLane a = v4_pack(ba1, qa1, s1, l1, n1, lane);
-        const PkLane b = v4_pack(ba2, qa2, s2, l2, n2, lane);
-        const PkLane r = v4_revcomp(b, l2, n2, lane);
-        const OvRes o = v4_analyze(a, l1, r, l2, anyN, limit, require, lane);
-        if(lane == src) ov = o;
+    const bool fastl = require >= 16 && A.len >= 16 && B.len >= 16;        // then every overlap of this pair is at least 16 long
+    if(__popc(mk0) <= V4_COOP_MAX || __any_sync(V4_FULL, need && !fastl)){
+        for(uint32_t mk = mk0; mk; mk &= mk - 1u){
+            const int src = __ffs((int)mk) - 1;
+            const uint2 o = v4_analyze_coop(__shfl_sync(V4_FULL, A.qa, src), __shfl_sync(V4_FULL, A.ba, src), __shfl_sync(V4_FULL, pa, src),
+                                            __shfl_sync(V4_FULL, B.qa, src), __shfl_sync(V4_FULL, B.ba, src), __shfl_sync(V4_FULL, pb, src),
+                                            limit, require, lane);
+            if(lane == src) ov = ov_unpack(o);
+        }
+        return;
     }
+    int nboth = 0;
+    if(need && A.nmask && B.nmask) nboth = min(n_count(A.qa, A.rawlen, A.nmask), n_count(B.qa, B.rawlen, B.nmask));
+    const uint2 o = v4_overlap_lockstep(A.qa, A.ba, pa, B.qa, B.ba, pb, nboth | (dbg << 16), need, limit, require, lane);
+    if(need) ov = ov_unpack(o);
 }
 
 // ------------------------------------------------------------------ one chunk of 32 pairs (a trim warp)
@@ -339,6 +483,7 @@ struct V4X {
     BlockCounters* bc;
     fq_read_result* out1; fq_read_result* out2; fq_pair_result* outp;   // records of the tile's first pair
     int nt;                        // pairs in the tile
+    int dbg;                       // timing experiments (FQK_V4_DEBUG): 4 no first analyze, 8 no second, 16 no tail corrections, 32 no polyG
 };
 
 // append the entries of the lanes in `want` to a list of the stage (one shared atomic per chunk)
@@ -361,17 +506,17 @@ __device__ __forceinline__ void v4_hist(bool want, uint32_t len, uint32_t hist_a
 // D of short cut-off tails: raw cycles [plen, dlen) of the lanes in `td` are taken out of the post array, one cycle
 // at a time.  Lane k < 20 owns one (kind, set) counter of the cycle: its value is a popcount of two ballots or one
 // of five warp sums.
-__device__ inline void v4_tail_sub(bool td, const PeRead& R, int plen, uint32_t post32, uint32_t C, int lane){
+__device__ V4_NI void v4_tail_sub(bool td, uint32_t Rqa, uint32_t Rba, int Rrawlen, int plen, uint32_t post32, uint32_t C, int lane){
     const uint32_t cmin = __reduce_min_sync(V4_FULL, td ? (uint32_t)plen : 0xFFFFFFFFu);
-    const uint32_t cmax = __reduce_max_sync(V4_FULL, td ? (uint32_t)R.rawlen : 0u);
+    const uint32_t cmax = __reduce_max_sync(V4_FULL, td ? (uint32_t)Rrawlen : 0u);
     const int myset = lane < 15 ? lane % 5 : lane - 15, mykind = lane < 15 ? lane / 5 : KQS;     // kinds KN, KN20, KN30 then KQS
     const bool lane_on = lane < 20 && !(mykind == KN && myset == S_ALL);                        // n of "all" comes from the length histogram
     const uint32_t cell = post32 + 4u * ((uint32_t)(mykind * NSETS + myset) * C);
     for(uint32_t c = cmin; c < cmax; ++c){
-        const bool in = td && (uint32_t)plen <= c && c < (uint32_t)R.rawlen;
-        const uint32_t by = in ? lds8(R.qa + c) : 0u, q7 = by & 0x7Fu;
+        const bool in = td && (uint32_t)plen <= c && c < (uint32_t)Rrawlen;
+        const uint32_t by = in ? lds8(Rqa + c) : 0u, q7 = by & 0x7Fu;
         const bool isn = (by & 0x80u) != 0u;
-        const uint32_t code = (in && !isn) ? (lds8(R.ba + (c >> 2)) >> (2u * (c & 3u))) & 3u : 0u;
+        const uint32_t code = (in && !isn) ? (lds8(Rba + (c >> 2)) >> (2u * (c & 3u))) & 3u : 0u;
         const uint32_t bIn = __ballot_sync(V4_FULL, in), b20 = __ballot_sync(V4_FULL, in && q7 > 53u), b30 = __ballot_sync(V4_FULL, in && q7 > 63u);
         const uint32_t bB0 = __ballot_sync(V4_FULL, (code & 1u) != 0u), bB1 = __ballot_sync(V4_FULL, (code & 2u) != 0u), bN = __ballot_sync(V4_FULL, in && isn);
         const uint32_t qall = __reduce_add_sync(V4_FULL, in ? q7 : 0u), qb0 = __reduce_add_sync(V4_FULL, (code & 1u) ? q7 : 0u),
@@ -393,9 +538,10 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     const V4L& L = *X.Lp;
     const int i = 32 * j + lane;
     const bool valid = i < X.nt;
-    PeRead R[2];
-#pragma unroll
-    for(int m = 0; m < 2; ++m){
+    PeRead a, b;
+    bool a1 = false, a2 = false;
+#pragma unroll 1
+    for(int m = 0; m < 2; ++m){                                     // one instance of the per-read code for both mates
         const uint32_t So = X.S32 + L.o_off[m], Sl = X.S32 + L.o_len[m];
         const uint32_t a0 = lds32(So), bshift = (a0 >> 2) & 15u;
         uint32_t doff = 0, dlen = 0;
@@ -407,28 +553,39 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             if(ok && i + 1 < X.nt) ok = (lds32(So + 4u * (i + 1)) == o + padded);          // dense, ordered batch
             if(!ok){ atomicOr(D.err, (dlen > L.Cr || dlen > (uint32_t)V4_MAXLEN) ? 1u : 2u); doff = 0; dlen = 0; sts16(Sl + 2u * i, 0u); }
         }
-        R[m].qa = X.S32 + L.o_q[m] + doff; R[m].ba = X.S32 + L.o_b[m] + bshift + (doff >> 2);
-        R[m].doff = doff; R[m].rawlen = (int)dlen; R[m].start = 0; R[m].len = (int)dlen; R[m].ge = 0; R[m].nmask = 0;
-        v4_sweep(R[m], P.qual_filter_enabled != 0, (uint32_t)P.low_quality_limit * 0x01010101u, lane);
+        PeRead r;
+        r.qa = X.S32 + L.o_q[m] + doff; r.ba = X.S32 + L.o_b[m] + bshift + (doff >> 2);
+        r.doff = doff; r.rawlen = (int)dlen; r.start = 0; r.len = (int)dlen;
+        const uint2 sw = v4_sweep(r.qa, (int)dlen, P.qual_filter_enabled != 0, (uint32_t)P.low_quality_limit * 0x01010101u, lane);
+        r.ge = sw.x; r.nmask = sw.y;
+        bool alive = false;
+        if(valid){
+            const uint32_t c = v4_trim_and_cut(&P, r.qa, r.rawlen, m ? P.trim_front2 : P.trim_front1, m ? P.trim_tail2 : P.trim_tail1);
+            alive = (c >> 31) != 0u; r.len = (int)(c & 0xFFFu); r.start = (int)((c >> 12) & 0xFFFu);
+        }
+        if(m){ b = r; a2 = alive; } else { a = r; a1 = alive; }
     }
-    EMU_MARK(0);
-    PeRead& a = R[0]; PeRead& b = R[1];
     fq_read_result rec1 = {}, rec2 = {};
     fq_pair_result pr = {};
     pr.insert_size = 0xFFFF;
-    const bool a1 = valid && s_trim_and_cut(P, a.qa, a.rawlen, P.trim_front1, P.trim_tail1, a.start, a.len);
-    const bool a2 = valid && s_trim_and_cut(P, b.qa, b.rawlen, P.trim_front2, P.trim_tail2, b.start, b.len);
     const bool both = a1 && a2;
-    if(both && P.polyg_enabled){
+    if(both && P.polyg_enabled && !(X.dbg & 32)){
         // src/peprocessor.cpp:297 hands (maxMismatch, oneEach, minLen) to (compareReq, maxMismatch, oneEach)
-        v4_polyg(a, P.polyg_max_mismatch, P.polyg_one_mismatch_each, P.polyg_min_len, rec1, tl);
-        v4_polyg(b, P.polyg_max_mismatch, P.polyg_one_mismatch_each, P.polyg_min_len, rec2, tl);
+#pragma unroll 1
+        for(int m = 0; m < 2; ++m){
+            const uint32_t v = v4_polyg_ni(m ? b.ba : a.ba, m ? b.start : a.start, m ? b.len : a.len,
+                                           P.polyg_max_mismatch, P.polyg_one_mismatch_each, P.polyg_min_len);
+            if(v >> 31){
+                const uint32_t nb = (v >> 12) & 0x1FFFu;
+                if(m){ b.len = (int)(v & 0xFFFu); rec2.flags |= FQK_F_POLYG; rec2.polyg_len = (uint16_t)nb; }
+                else { a.len = (int)(v & 0xFFFu); rec1.flags |= FQK_F_POLYG; rec1.polyg_len = (uint16_t)nb; }
+                tl.polyx_reads[3] += 1; tl.polyx_bases[3] += nb;
+            }
+        }
     }
-    EMU_MARK(1);
     OvRes ov; ov.overlapped = 0; ov.offset = 0; ov.len = 0; ov.diff = 0;
     // first analyze(): :303 when -a/-c, else :330 (insert size only); identical inputs either way
-    v4_analyze_chunk(a, b, both, P.overlap_diff_limit, P.overlap_require, lane, ov);
-    EMU_MARK(2);
+    if(!(X.dbg & 4)) v4_overlap_chunk(a, b, both, P.overlap_diff_limit, P.overlap_require, lane, ov, X.dbg);
     int isize = -1;
     if(both){
         pr.flags |= FQK_P_OV1_DONE | (ov.overlapped ? FQK_P_OV1_OVERLAP : 0);
@@ -443,7 +600,6 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         if(lane == 0 && mx) reds_add(X.ins32 + 4u * (uint32_t)P.insert_size_max, (uint32_t)__popc(mx));
         if(both && isize != P.insert_size_max) reds_add(X.ins32 + 4u * (uint32_t)isize, 1u);
     }
-    EMU_MARK(3);
     bool modified = false;                                   // reads changed since the first analyze()
     if(both && P.adapter_trim_enabled){
         // AdapterTrimmer::trimByOverlapAnalysis, src/adaptertrimmer.cpp:14-27
@@ -455,16 +611,26 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             tl.adapter_reads += 2; tl.adapter_bases += (uint32_t)(t1 + t2);     // filterresult.cpp:159-161
             modified = true;
         }else{
-            if(P.adapter_r1_len > 0){ ReadView v = v4_view(a); modified |= trim_by_sequence_any(D, v, 0, rec1, tl); a.len = v.len; }
-            if(P.adapter_r2_len > 0){ ReadView v = v4_view(b); modified |= trim_by_sequence_any(D, v, 1, rec2, tl); b.len = v.len; }
+            if(P.adapter_r1_len > 0){
+                fq_read_result rt = {}; Tally tt = {};
+                const int v = v4_adapter_seq(&D, a.qa, a.ba, a.start, a.len, 0, &rt, &tt);
+                a.len = v & 0xFFFF; modified |= (v >> 30) != 0; v4_merge_rec(rec1, tl, rt, tt);
+            }
+            if(P.adapter_r2_len > 0){
+                fq_read_result rt = {}; Tally tt = {};
+                const int v = v4_adapter_seq(&D, b.qa, b.ba, b.start, b.len, 1, &rt, &tt);
+                b.len = v & 0xFFFF; modified |= (v >> 30) != 0; v4_merge_rec(rec2, tl, rt, tt);
+            }
         }
     }
     if(both && P.polyx_enabled){
         const int l1 = a.len, l2 = b.len;
-        ReadView v = v4_view(a);
-        dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec1, tl); a.len = v.len;
-        v = v4_view(b);
-        dev_trim_polyx(v, P.polyx_base_mask, P.polyx_min_len, P.polyx_max_mismatch, P.polyx_one_mismatch_each, rec2, tl); b.len = v.len;
+#pragma unroll 1
+        for(int m = 0; m < 2; ++m){
+            fq_read_result rt = {}; Tally tt = {};
+            const int nl = v4_polyx(&P, m ? b.qa : a.qa, m ? b.ba : a.ba, m ? b.start : a.start, m ? b.len : a.len, &rt, &tt);
+            if(m){ b.len = nl; v4_merge_rec(rec2, tl, rt, tt); } else { a.len = nl; v4_merge_rec(rec1, tl, rt, tt); }
+        }
         modified |= (a.len != l1) | (b.len != l2);
     }
     if(both){
@@ -472,10 +638,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         if(P.trim_max_len2 > 0 && P.trim_max_len2 < b.len){ b.len = P.trim_max_len2; modified = true; }
     }
     // second analyze(), :354: same answer as the first when neither read changed
-    EMU_MARK(4);
     OvRes ov2 = ov;
-    v4_analyze_chunk(a, b, P.merge_enabled && both && modified, P.overlap_diff_limit, P.overlap_require, lane, ov2);
-    EMU_MARK(5);
+    if(!(X.dbg & 8)) v4_overlap_chunk(a, b, P.merge_enabled && both && modified, P.overlap_diff_limit, P.overlap_require, lane, ov2);
     bool merge_processed = false; int res1 = 0, res2 = 0;
     int fcA = -1, fnA = 0, fcB = -1, fnB = 0;                // updates of mFilterReadStats: (code, amount) x 2
     bool merged = false;
@@ -489,23 +653,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
                 const int len1 = ov2.len + max(0, ov2.offset);
                 const int len2 = ov2.offset > 0 ? b.len - ov2.len : 0;
                 pr.merge_len1 = (uint16_t)len1; pr.merge_len2 = (uint16_t)len2;
-                if(P.complexity_enabled){
-                    const ReadView va = v4_view(a), vb = v4_view(b);
-                    const int ol = ov2.len;
-                    result = dev_pass_filter(P, len1 + len2, false, [&](int t, int& c, int& q){
-                        if(t < len1){ c = va.cls(t); q = va.qual(t); }
-                        else { const int u = ol + t - len1; c = rc_cls(vb, u); q = vb.qual(vb.len - 1 - u); }
-                    });
-                }else{
-                    // counts of the merged read = read1 prefix + the part of read2 that is appended (order is irrelevant)
-                    int l1 = 0, n1 = 0, t1 = 0, l2 = 0, n2 = 0, t2 = 0;
-                    if(P.qual_filter_enabled){
-                        const bool wt = P.average_quality_limit > 0;
-                        swar_counts(a.qa, a.start, len1, P.low_quality_limit, wt, l1, n1, t1);
-                        swar_counts(b.qa, b.start + (b.len - ov2.len - len2), len2, P.low_quality_limit, wt, l2, n2, t2);
-                    }
-                    result = (len1 + len2 == 0) ? FQK_FAIL_LENGTH : filter_from_counts(P, len1 + len2, l1 + l2, n1 + n2, t1 + t2);
-                }
+                result = v4_merged_filter(&P, a.qa, a.ba, a.start, a.len, b.qa, b.ba, b.start, b.len, ov2.len, len1, len2);
                 if(result == FQK_PASS_FILTER){ pr.flags |= FQK_P_MERGED; merged = true; }
             }
             fcA = result; fnA = 2;                                  // :358
@@ -524,7 +672,6 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         res2 = v4_pass_filter(P, b, !a2);
         fcA = max(res1, res2); fnA = 2;                             // :390, mPaired == true
     }
-    EMU_MARK(6);
     rec1.result = (uint8_t)res1; rec2.result = (uint8_t)res2;
     if(!a1) rec1.flags |= FQK_F_DROPPED; else { rec1.start = (uint16_t)a.start; rec1.len = (uint16_t)a.len; }
     if(!a2) rec2.flags |= FQK_F_DROPPED; else { rec2.start = (uint16_t)b.start; rec2.len = (uint16_t)b.len; }
@@ -538,11 +685,10 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         if(lane == 0 && nm) atomicAdd(&X.bc->merged_pairs, (uint32_t)__popc(nm));
     }
     // ---- what the statistics warps need: length histograms, exception lists, short tails ----
-    EMU_MARK(7);
     const uint32_t cnt32 = X.S32 + L.o_cnt;
 #pragma unroll
     for(int m = 0; m < 2; ++m){
-        const PeRead& Rm = R[m];
+        const PeRead& Rm = m ? b : a;
         const fq_read_result& rm = m ? rec2 : rec1;
         const uint32_t C = m ? L.Cr : L.Cm;                       // cycles of post1 / post2
         const uint32_t dlen = (uint32_t)Rm.rawlen;
@@ -564,7 +710,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             const uint32_t cmin = __reduce_min_sync(V4_FULL, td ? olen : 0xFFFFFFFFu), cmax = __reduce_max_sync(V4_FULL, td ? dlen : 0u);
             if(cmax - cmin > 2u * V4_TAILMAX){ tlong = td; td = false; }              // ragged chunk: through the list
             else { tlong = td && dlen - olen > (uint32_t)V4_TAILMAX; td = td && !tlong; }
-            if(__any_sync(V4_FULL, td)) v4_tail_sub(td, Rm, (int)olen, X.post32[m], C, lane);
+            if(!(X.dbg & 16) && __any_sync(V4_FULL, td)) v4_tail_sub(td, Rm.qa, Rm.ba, Rm.rawlen, (int)olen, X.post32[m], C, lane);
         }
         const Desc d = make_desc(Rm.doff, dlen, whole ? (own ? ostart : 0u) : 0u, whole ? (own ? olen : 0u) : olen, (own ? 2u : 1u));
         v4_push(whole || tlong, cnt32 + 4u * m, X.S32 + L.o_ex[m], d, lane);
@@ -576,3 +722,351 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         v4_push(wm, cnt32 + 8u, X.S32 + L.o_exm, make_desc(b.doff, pmax, pr.merge_len1, pr.merge_len2, 3u), lane);
     }
 }
+
+#ifndef FQK_EMU
+// ====================================================================== the kernel
+constexpr int V4_STATS = 256, V4_TRIM = 256, V4_THREADS = V4_STATS + V4_TRIM;
+constexpr int V4_WORKERS = V4_TRIM / 32 - 1;                      // trim warps 0..6 work on chunks, warp 7 is the copy producer
+static_assert(sizeof(V4L) <= 256, "V4L lives in the first 256 bytes of the block's shared memory");
+
+// accumulators of the quad path -> the two statistics arrays of a mate (different cycle counts: post1 holds merged reads)
+__device__ __noinline__ void quad_drain1_ab(const uint32_t* v, uint32_t* smA, int CA, uint32_t* smB, int CB, int w){
+    auto add2 = [&](int kind, int set, int c, uint32_t x){
+        if(x){ atomicAdd(sm_cell(smA, CA, kind, set) + c, x); atomicAdd(sm_cell(smB, CB, kind, set) + c, x); }
+    };
+    for(int j = 0; j < 4; ++j){
+        const int c = 4 * w + j;
+        add2(KN20, S_ALL, c, v[0 + j] >> 7);
+        add2(KN30, S_ALL, c, v[4 + j] >> 6);
+        add2(KQS, S_ALL, c, v[8 + j]);
+        for(int s = 0; s < 3; ++s){
+            const int sh = 2 * j + (s == 1 ? 1 : 0);
+            add2(KN, S_B0 + s, c, v[12 + s * 4 + j] >> sh);
+            add2(KN20, S_B0 + s, c, v[24 + s * 4 + j] >> (7 + sh));
+            add2(KN30, S_B0 + s, c, v[36 + s * 4 + j] >> (6 + sh));
+            add2(KQS, S_B0 + s, c, v[48 + s * 4 + j] >> sh);
+        }
+        add2(KN, S_N, c, v[60 + j]);
+        add2(KN20, S_N, c, v[64 + j] >> 7);
+        add2(KN30, S_N, c, v[68 + j] >> 6);
+        add2(KQS, S_N, c, v[72 + j]);
+    }
+}
+__device__ __forceinline__ void quad_drain_ab(QuadAcc& A, uint32_t* smA, int CA, uint32_t* smB, int CB, int w){
+    uint32_t v[76];
+#pragma unroll
+    for(int j = 0; j < 4; ++j){
+        v[j] = A.a20[j]; v[4 + j] = A.a30[j]; v[8 + j] = A.aqs[j];
+#pragma unroll
+        for(int s = 0; s < 3; ++s){
+            v[12 + s * 4 + j] = A.n[s][j]; v[24 + s * 4 + j] = A.n20[s][j]; v[36 + s * 4 + j] = A.n30[s][j]; v[48 + s * 4 + j] = A.qs[s][j];
+        }
+        v[60 + j] = A.nn[j]; v[64 + j] = A.nn20[j]; v[68 + j] = A.nn30[j]; v[72 + j] = A.nqs[j];
+    }
+    quad_drain1_ab(v, smA, CA, smB, CB, w);
+    A.zero();
+}
+
+// Named barriers: ids 1..NS tile ready (CH trim-warp arrivals + the statistics warps), NS+1..2NS stage free (the
+// statistics warps arrive, the producer warp waits); `full` (bulk copies landed) is an mbarrier with a transaction count.
+__global__ void __launch_bounds__(V4_THREADS, 1)
+k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_result* __restrict__ out1,
+        fq_read_result* __restrict__ out2, fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
+        int Wr, int Wm, int T, int NS, int pairs_per_block, int dbg){
+    extern __shared__ __align__(128) uint8_t smraw[];
+    const fq_params& P = D.P;
+    if(threadIdx.x == 0) *reinterpret_cast<V4L*>(smraw) = v4_layout(Wr, Wm, T, NS, P.insert_size_max + 1);
+    __syncthreads();
+    const V4L& L = *reinterpret_cast<const V4L*>(smraw);
+    const uint32_t sm32 = smem_u32(smraw);
+    uint32_t* const smPost1 = reinterpret_cast<uint32_t*>(smraw + L.o_post[0]);
+    BlockCounters* bc = reinterpret_cast<BlockCounters*>(smraw + L.o_bc);
+    uint32_t* ins = reinterpret_cast<uint32_t*>(smraw + L.o_ins);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smraw + L.o_bar);
+    const int CH = T / 32;                                       // chunks per tile (T is a multiple of 32)
+
+    for(uint32_t i = L.o_pre[0] / 4 + threadIdx.x; i < L.o_bar / 4; i += V4_THREADS) reinterpret_cast<uint32_t*>(smraw)[i] = 0;   // statistics, counters, insert sizes
+    if(threadIdx.x == 0){
+        *reinterpret_cast<uint32_t*>(smraw + L.o_misc) = 0u;         // next chunk of the trim warps
+        for(int s = 0; s < NS; ++s){
+            mbar_init(&full[s], 1);
+            *reinterpret_cast<uint32_t*>(smraw + L.o_stage + (size_t)s * L.stage_bytes + L.o_cnt + 20) = 0xFFFFFFFFu;   // tile tag: nothing staged yet
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t lo = (uint32_t)min((uint64_t)B1.n, (uint64_t)blockIdx.x * pairs_per_block);
+    const uint32_t hi = (uint32_t)min((uint64_t)B1.n, (uint64_t)lo + pairs_per_block);
+    const int ntiles = (int)((hi - lo + T - 1) / T);
+    const int lane = threadIdx.x & 31;
+
+    const bool is_trim = threadIdx.x >= V4_STATS;
+    const int rtid = is_trim ? threadIdx.x - V4_STATS : threadIdx.x;
+    if(is_trim){
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
+        const int tw = rtid >> 5;
+        if(tw == V4_WORKERS){
+            // ============================== copy producer ==============================
+            auto BM = [&](int m) -> const DevBatch& { return m ? B2 : B1; };
+            uint32_t a[2] = {0, 0}, last[2] = {0, 0}, ll[2] = {0, 0};
+            if(ntiles > 0){
+                const uint32_t nt = min((uint32_t)T, hi - lo);
+#pragma unroll
+                for(int m = 0; m < 2; ++m){ a[m] = BM(m).offsets[lo]; last[m] = BM(m).offsets[lo + nt - 1]; ll[m] = BM(m).lengths[lo + nt - 1]; }
+            }
+            for(int k = 0; k < ntiles; ++k){
+                const int s = k % NS, n = k / NS;
+                const uint32_t t0 = lo + (uint32_t)k * T;
+                const uint32_t nt = min((uint32_t)T, hi - t0);
+                const uint32_t ca[2] = {a[0], a[1]}, clast[2] = {last[0], last[1]}, cll[2] = {ll[0], ll[1]};
+                if(k + 1 < ntiles){                                // next tile's end points: in flight during the wait below
+                    const uint32_t t1 = t0 + T, nt1 = min((uint32_t)T, hi - t1);
+#pragma unroll
+                    for(int m = 0; m < 2; ++m){ a[m] = BM(m).offsets[t1]; last[m] = BM(m).offsets[t1 + nt1 - 1]; ll[m] = BM(m).lengths[t1 + nt1 - 1]; }
+                }
+                if(n >= 1) nb_sync(1 + NS + s, V4_STATS + 32);
+                uint8_t* S = smraw + L.o_stage + (size_t)s * L.stage_bytes;
+                const uint32_t nb = nt & ~7u;                      // bulk copies move multiples of 16 bytes
+#pragma unroll
+                for(int m = 0; m < 2; ++m){
+                    uint32_t* So = reinterpret_cast<uint32_t*>(S + L.o_off[m]);
+                    uint16_t* Sl = reinterpret_cast<uint16_t*>(S + L.o_len[m]);
+                    for(uint32_t i = nb + lane; i < nt; i += 32){ So[i] = BM(m).offsets[t0 + i]; Sl[i] = BM(m).lengths[t0 + i]; }
+                    for(uint32_t i = nt + lane; i < (uint32_t)T; i += 32){ So[i] = ca[m]; Sl[i] = 0; }
+                }
+                __syncwarp();
+                if(lane == 0){
+                    uint32_t* cnt = reinterpret_cast<uint32_t*>(S + L.o_cnt);
+                    uint32_t qbytes[2], b0[2], bbytes[2], uni = 0; bool bad = false;
+#pragma unroll
+                    for(int m = 0; m < 2; ++m){
+                        uint64_t e = (uint64_t)clast[m] + ((cll[m] + 15u) & ~15u);
+                        const bool bd = (ca[m] & 15u) || e < ca[m] || e - ca[m] > L.qcap || e > BM(m).total;
+                        if(bd){ bad = true; e = ca[m]; }
+                        qbytes[m] = (uint32_t)(e - ca[m]);
+                        b0[m] = (ca[m] >> 2) & ~15u;
+                        bbytes[m] = qbytes[m] ? (((uint32_t)(e >> 2) + 15u) & ~15u) - b0[m] : 0u;
+                        if(nt == (uint32_t)T && qbytes[m] == L.qcap) uni |= 1u << m;                // every read exactly Cp padded bytes
+                    }
+                    if(bad){ atomicOr(D.err, 2u); qbytes[0] = qbytes[1] = bbytes[0] = bbytes[1] = 0; uni = 0; }
+                    cnt[0] = 0; cnt[1] = 0; cnt[2] = 0; cnt[3] = uni; cnt[4] = bad ? 0u : nt;
+                    *reinterpret_cast<volatile uint32_t*>(&cnt[5]) = (uint32_t)k;   // tile tag (wait_tile_tag)
+                    mbar_expect_tx(&full[s], qbytes[0] + bbytes[0] + qbytes[1] + bbytes[1] + 2u * nb * 6u);
+#pragma unroll
+                    for(int m = 0; m < 2; ++m){
+                        if(qbytes[m]){
+                            bulk_g2s(S + L.o_q[m], BM(m).qual + ca[m], qbytes[m], &full[s]);
+                            bulk_g2s(S + L.o_b[m], BM(m).bases2 + b0[m], bbytes[m], &full[s]);
+                        }
+                        if(nb){
+                            bulk_g2s(S + L.o_off[m], BM(m).offsets + t0, nb * 4u, &full[s]);
+                            bulk_g2s(S + L.o_len[m], BM(m).lengths + t0, nb * 2u, &full[s]);
+                        }
+                    }
+                }
+            }
+        }else{
+            // ============================== trim warps ==============================
+            Tally tl = {};
+            V4X X;
+            X.D = &D; X.Lp = &L;
+            X.pre32[0] = sm32 + L.o_pre[0]; X.pre32[1] = sm32 + L.o_pre[1];
+            X.post32[0] = sm32 + L.o_post[0]; X.post32[1] = sm32 + L.o_post[1];
+            X.ins32 = sm32 + L.o_ins; X.bc = bc; X.dbg = dbg;
+            const int nchunks = ntiles * CH;
+            // chunks are handed out in order from a shared counter: a chunk that takes long (many candidates to verify)
+            // does not hold back the chunks behind it, and at most V4_WORKERS consecutive chunks are in flight
+            const uint32_t next32 = sm32 + L.o_misc;
+            for(;;){
+                int c = 0;
+                if(lane == 0) c = (int)atoms_add(next32, 1u);
+                c = __shfl_sync(V4_FULL, c, 0);
+                if(c >= nchunks) break;
+                const int k = c / CH, j = c - k * CH, s = k % NS;
+                X.S32 = sm32 + L.o_stage + (uint32_t)s * L.stage_bytes;
+                wait_tile_tag(X.S32 + L.o_cnt + 20, (uint32_t)k);
+                mbar_wait_sleep(&full[s], (uint32_t)(k / NS) & 1u, 20000);
+                X.nt = (int)lds32(X.S32 + L.o_cnt + 16);
+                const uint32_t t0 = lo + (uint32_t)k * T;
+                X.out1 = out1 + t0; X.out2 = out2 + t0; X.outp = outp + t0;
+                if(32 * j < X.nt && !(dbg & 1)) v4_chunk(X, j, lane, tl);
+                __syncwarp();
+                __threadfence_block();
+                nb_arrive(1 + s, CH * 32 + V4_STATS);
+            }
+            counters_add_tally(bc, tl);
+        }
+    }else{
+        // ============================ statistics warps ============================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
+        const int C1 = (int)L.Cr, CM = (int)L.Cm, Cp = (int)L.Cp;
+        const int G = V4_STATS / Wr, Gm = G >> 1;                // groups of Wr threads; even groups read1, odd groups read2
+        const int g = rtid / Wr, w = rtid - g * Wr;
+        const bool active = g < 2 * Gm;
+        const int mate = g & 1, gi = g >> 1;
+        uint32_t* smPre = reinterpret_cast<uint32_t*>(smraw + (mate ? L.o_pre[1] : L.o_pre[0]));
+        uint32_t* smPost = reinterpret_cast<uint32_t*>(smraw + (mate ? L.o_post[1] : L.o_post[0]));
+        const int Cpost = mate ? C1 : CM;
+        // the tails of merged reads land on post1 at cycles up to Cm: a second mapping, Wm threads per entry
+        const int GM = V4_STATS / Wm, gM = rtid / Wm, wM = rtid - gM * Wm;
+        const bool activeM = P.merge_enabled && gM < GM;
+        QuadAcc qa;
+        Acc1 dsub, madd;
+        qa.zero(); dsub.zero(); madd.zero();
+        int usedQ = 0, leftO = 255, leftM = 255;
+        const int quads_per_tile = T / 4;
+        for(int k = 0; k < ntiles; ++k){
+            const int s = k % NS;
+            const uint32_t S32 = sm32 + L.o_stage + (uint32_t)s * L.stage_bytes;
+            nb_sync(1 + s, CH * 32 + V4_STATS);
+            if(!(dbg & 2)){
+                const int nt = (int)lds32(S32 + L.o_cnt + 16);
+                if(active){
+                    const uint32_t a0 = lds32(S32 + L.o_off[mate]);
+                    const uint32_t bshift = (a0 >> 2) & 15u;
+                    const uint32_t sq0 = S32 + L.o_q[mate], sb0 = S32 + L.o_b[mate] + bshift;
+                    const uint32_t sqw = sq0 + 4 * w, sbw = sb0 + w;
+                    const int nex = (int)lds32(S32 + L.o_cnt + 4 * mate), uniform = (int)((lds32(S32 + L.o_cnt + 12) >> mate) & 1u);
+                    const int mine = (quads_per_tile + Gm - 1) / Gm;
+                    if(usedQ + mine > QUAD_LIMIT){ quad_drain_ab(qa, smPre, C1, smPost, Cpost, w); usedQ = 0; }
+                    usedQ += mine;
+                    uint32_t q[4], b[4];
+                    if(uniform){
+                        // every read of the tile occupies exactly Cp bytes: addresses advance by constants, no range checks
+                        const uint32_t qstep = 4u * (uint32_t)Gm * (uint32_t)Cp, bstep = (uint32_t)Gm * (uint32_t)Cp;
+                        uint32_t aq = sqw + 4u * (uint32_t)gi * (uint32_t)Cp, ab = sbw + (uint32_t)gi * (uint32_t)Cp;
+                        const uint32_t c1 = (uint32_t)Cp, c1b = (uint32_t)Cp >> 2;
+                        for(int qd = gi; qd < quads_per_tile; qd += Gm){
+                            q[0] = lds32(aq); q[1] = lds32(aq + c1); q[2] = lds32(aq + 2 * c1); q[3] = lds32(aq + 3 * c1);
+                            b[0] = lds8(ab); b[1] = lds8(ab + c1b); b[2] = lds8(ab + 2 * c1b); b[3] = lds8(ab + 3 * c1b);
+                            aq += qstep; ab += bstep;
+                            quad_accumulate(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
+                        }
+                    }else{
+                        const int nq = (nt + 3) >> 2;
+                        for(int qd = gi; qd < nq; qd += Gm){
+                            const uint4 o = lds128(S32 + L.o_off[mate] + 16u * qd);
+                            const uint2 l2 = lds64(S32 + L.o_len[mate] + 8u * qd);
+                            const uint32_t of[4] = {o.x - a0, o.y - a0, o.z - a0, o.w - a0};
+                            const uint32_t ln[4] = {l2.x & 0xFFFFu, l2.x >> 16, l2.y & 0xFFFFu, l2.y >> 16};
+#pragma unroll
+                            for(int r = 0; r < 4; ++r){
+                                const bool in = (uint32_t)(4 * w) < ln[r];
+                                q[r] = in ? lds32(sqw + of[r]) : 0u;
+                                b[r] = in ? lds8(sbw + (of[r] >> 2)) : 0u;
+                            }
+                            quad_accumulate(qa, q[0], q[1], q[2], q[3], b[0], b[1], b[2], b[3]);
+                        }
+                    }
+                    // ---- exceptions of this mate: D is subtracted from its post array, Z is added to it ----
+                    const uint32_t ex = S32 + L.o_ex[mate];
+                    const uint32_t c0 = 4u * (uint32_t)w;
+                    for(int i = gi; i < nex; i += Gm){
+                        const uint2 dc = lds64(ex + 8 * i);
+                        const uint32_t off = (dc.x & 0x1FFFFu) << 4, len = dc.x >> 17, kind = (dc.y >> 26) & 3u;
+                        const uint32_t start = dc.y & 0x1FFFu, plen = (dc.y >> 13) & 0x1FFFu;
+                        const uint32_t d0 = (kind == 2u && start == 0u) ? plen : 0u;              // D = raw positions [d0, len)
+                        if(c0 < len && c0 + 4 > d0){
+                            uint32_t qq = lds32(sqw + off), bb = lds8(sbw + (off >> 2));
+                            if(c0 < d0){ const uint32_t nbz = d0 - c0; qq &= 0xFFFFFFFFu << (8 * nbz); bb &= 0xFFu << (2 * nbz); }
+                            if(qq) acc_word(dsub, qq, bb);             // a word inside a read never has four zero quality bytes
+                        }
+                        if(kind == 2u && start > 0u){
+                            const int nv = (int)plen - 4 * w;
+                            if(nv > 0){
+                                const uint32_t p = off + start + 4 * w;
+                                const uint32_t a1 = p & ~3u, sh = p & 3u;
+                                const uint32_t w0 = lds32(sq0 + a1);
+                                const uint32_t w1 = sh ? lds32(sq0 + a1 + 4) : 0u;
+                                const uint32_t q2 = __funnelshift_r(w0, w1, sh * 8);
+                                const uint32_t e0 = lds8(sb0 + (p >> 2)), e1 = sh ? lds8(sb0 + (p >> 2) + 1) : 0u;
+                                const uint32_t b2 = ((e0 | (e1 << 8)) >> (2 * sh)) & 0xFF;
+                                z_word_atomic(q2, b2, nv, smPost, Cpost, w);
+                            }
+                        }
+                        if(--leftO == 0){ drain_l1_signed(dsub, smPost, Cpost, w, 1); leftO = 255; }
+                    }
+                }
+                if(activeM){
+                    // ---- M: reverse-complemented tails of read2 appended to merged reads (post1, cycles [len1, len1+len2)) ----
+                    const uint32_t a0 = lds32(S32 + L.o_off[1]);
+                    const uint32_t sq0 = S32 + L.o_q[1], sb0 = S32 + L.o_b[1] + ((a0 >> 2) & 15u);
+                    const int nm = (int)lds32(S32 + L.o_cnt + 8);
+                    const uint32_t exm = S32 + L.o_exm;
+                    for(int i = gM; i < nm; i += GM){
+                        const uint2 dc = lds64(exm + 8 * i);
+                        const uint32_t off = (dc.x & 0x1FFFFu) << 4;
+                        const int pmax = (int)(dc.x >> 17), len1 = (int)(dc.y & 0x1FFFu), len2 = (int)((dc.y >> 13) & 0x1FFFu);
+                        const int c0 = 4 * wM, lo2 = max(len1, c0), hi2 = min(len1 + len2, c0 + 4);
+                        if(lo2 < hi2){
+                            const int addr = (int)off + pmax - c0 - 3;                  // tile position of the byte for cycle c0+3
+                            const int a1 = addr & ~3, sh = addr & 3;
+                            const uint32_t q4 = __funnelshift_r(lds32(sq0 + a1), lds32(sq0 + a1 + 4), sh * 8);
+                            uint32_t q2 = __byte_perm(q4, 0, 0x0123);                  // reversed: byte j <-> cycle c0+j
+                            const uint32_t cb = lds8(sb0 + (addr >> 2)) | (lds8(sb0 + (addr >> 2) + 1) << 8);
+                            uint32_t b2 = (cb >> (2 * sh)) & 0xFF;
+                            b2 = ((b2 & 0x03) << 6) | ((b2 & 0x0C) << 2) | ((b2 & 0x30) >> 2) | ((b2 & 0xC0) >> 6);
+                            b2 ^= 0x55;                                                 // complement: A<->T, C<->G
+                            const int jlo = lo2 - c0, jhi = hi2 - c0;
+                            const uint32_t bm = (jhi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * jhi)) - 1u)) & ~((1u << (8 * jlo)) - 1u);
+                            q2 &= bm;
+                            const uint32_t f = ((((q2 >> 7) & 0x01010101u) * 0x00204081u) >> 21) & 0xFu;   // N flags of the 4 bytes
+                            uint32_t spn = (f & 1u) | ((f & 2u) << 1) | ((f & 4u) << 2) | ((f & 8u) << 3);
+                            spn |= spn << 1;
+                            b2 &= ((1u << (2 * jhi)) - 1u) & ~((1u << (2 * jlo)) - 1u) & ~spn;   // N keeps code 0
+                            acc_word(madd, q2, b2);
+                        }
+                        if(--leftM == 0){ drain_l1(madd, smPost1, nullptr, CM, wM); leftM = 255; }
+                    }
+                }
+            }
+            __syncwarp();
+            if(k + NS < ntiles) nb_arrive(1 + NS + s, V4_STATS + 32);      // the producer waits only for stages it refills
+        }
+        if(active){
+            quad_drain_ab(qa, smPre, C1, smPost, Cpost, w);
+            drain_l1_signed(dsub, smPost, Cpost, w, 1);
+        }
+        if(activeM) drain_l1(madd, smPost1, nullptr, CM, wM);
+    }
+    __syncthreads();
+    retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[0]), (int)L.Cr, D.L, flat + D.L.stats_off[0]);
+    retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[1]), (int)L.Cr, D.L, flat + D.L.stats_off[1]);
+    retire(smPost1, (int)L.Cm, D.L, flat + D.L.stats_off[2]);
+    retire(reinterpret_cast<uint32_t*>(smraw + L.o_post[1]), (int)L.Cr, D.L, flat + D.L.stats_off[3]);
+    counters_flush(bc, D.L, flat);
+    for(int i = threadIdx.x; i <= P.insert_size_max; i += V4_THREADS) if(ins[i]) add_u64(flat + D.L.insert_hist_off + i, ins[i]);
+}
+
+// ---------------------------------------------------------------------- host side
+struct V4Plan { int Wr, Wm, T, NS; size_t smem; bool ok; };
+// tile size and stage count for reads up to maxlen bases (0 = unknown: the capacity max_cycles)
+inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin){
+    V4Plan p = {0, 0, 0, 0, 0, false};
+    const fq_params& P = D.P;
+    const int cap = (int)D.L.max_cycles;
+    if(maxlen <= 0 || maxlen > cap) maxlen = cap;
+    if(maxlen > V4_MAXLEN) return p;
+    if(P.correction_enabled || P.kmer_len) return p;         // -c mutates the batch, k-mers: the two-phase path
+    p.Wr = std::max(8, (maxlen + 3) / 4);
+    p.Wm = P.merge_enabled ? std::max(p.Wr, std::min((cap + 3) / 4, (2 * maxlen + 3) / 4)) : p.Wr;
+    if(p.Wm > V4_STATS || V4_STATS / p.Wr < 2) return p;
+    const size_t budget = smem_optin > 4096 ? smem_optin - 1024 : 0;
+    const int Gm = (V4_STATS / p.Wr) >> 1;
+    int bestT = 0, bestNS = 0; long best = -1;
+    for(int NS = 4; NS >= 2; --NS)
+        for(int T = 256; T >= 32; T -= 32){
+            const V4L l = v4_layout(p.Wr, p.Wm, T, NS, P.insert_size_max + 1);
+            if(l.qcap >= (1u << 21) || (size_t)l.total + 128 > budget) continue;
+            // prefer whole quads per statistics group, then more bytes in flight
+            const long score = (long)T * NS + (((T / 4) % Gm == 0) ? 100000 : 0) + (NS >= 3 ? 50000 : 0);
+            if(score > best){ best = score; bestT = T; bestNS = NS; }
+        }
+    if(best < 0) return p;
+    p.T = bestT; p.NS = bestNS;
+    p.smem = v4_layout(p.Wr, p.Wm, p.T, p.NS, P.insert_size_max + 1).total + 128;
+    p.ok = true;
+    return p;
+}
+#endif  // !FQK_EMU

@@ -287,7 +287,10 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
 #endif
     counters_zero(bc);
     if(threadIdx.x == 0){
-        for(int s = 0; s < V3_NS; ++s){ mbar_init(&full[s], 1); mbar_init(&ready[s], (uint32_t)CH); mbar_init(&freeb[s], V3_STATS / 32); }
+        for(int s = 0; s < V3_NS; ++s){
+            mbar_init(&full[s], 1); mbar_init(&ready[s], (uint32_t)CH); mbar_init(&freeb[s], V3_STATS / 32);
+            *reinterpret_cast<uint32_t*>(sp + (size_t)s * L.stage_bytes + L.o_cnt + 12) = 0xFFFFFFFFu;   // tile tag: nothing staged yet
+        }
         blkmax[0] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -349,6 +352,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     cnt[0] = 0;
                     cnt[1] = (nt == (uint32_t)T && qbytes == L.qcap) ? 1u : 0u;      // every read exactly Cp padded bytes
                     cnt[2] = bad ? 0u : nt;
+                    *reinterpret_cast<volatile uint32_t*>(&cnt[3]) = (uint32_t)k;     // tile tag (wait_tile_tag, fqk_smem.cuh)
                     mbar_expect_tx(&full[s], qbytes + bbytes + nb * 6u);
                     if(qbytes){
                         bulk_g2s(S, B.qual + ca, qbytes, &full[s]);
@@ -373,11 +377,8 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
                 PROF_T(t_tw);
-#ifdef V3_FULL_BACKOFF
-                mbar_wait_backoff(&full[s], (uint32_t)(k / V3_NS) & 1u);
-#else
+                wait_tile_tag(S32 + L.o_cnt + 12, (uint32_t)k);
                 mbar_wait_sleep(&full[s], (uint32_t)(k / V3_NS) & 1u, 20000);
-#endif
                 PROF_ADD(0, t_tw);
                 PROF_T(t_tc);
                 const uint32_t* So = reinterpret_cast<const uint32_t*>(S + L.o_off);

@@ -21,6 +21,14 @@ __device__ __forceinline__ Desc make_desc(uint32_t off, uint32_t len, uint32_t s
 
 #ifndef FQK_EMU
 __device__ __forceinline__ uint32_t lds32(uint32_t a){ uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32_volatile(uint32_t a){ uint32_t v; asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+// A trim warp may run several tiles ahead of the producer.  mbarrier.try_wait.parity cannot tell "phase n has not
+// started" from "phase n-1 is complete" when the waiter is two phases ahead of the barrier (it would return at once
+// and the warp would read a stale stage), so the producer tags the stage with the tile index before it arms the
+// barrier and a consumer waits for the tag first: once the tag is there the barrier is in the right phase.
+__device__ __forceinline__ void wait_tile_tag(uint32_t tag_addr, uint32_t tile){
+    while(lds32_volatile(tag_addr) != tile) __nanosleep(64);
+}
 __device__ __forceinline__ uint32_t lds16(uint32_t a){ uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t lds8(uint32_t a){ uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint2 lds64(uint32_t a){ uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }

@@ -66,7 +66,7 @@ void HotPath::pack(const std::vector<Read>& reads, Buffers& b, fq_batch& batch){
     const int rc = fqk_pack_ascii(n, b.seq.data(), b.qualAscii.data(), b.off.data(), b.offsets, b.lengths, b.bases2, b.qual);
     if(rc == FQK_E_ALPHABET) throw std::runtime_error("read with a base outside {A,C,G,T,N}: outside the input contract of the GPU path");
     if(rc) throw std::runtime_error("read longer than FQK_MAX_READ_LEN");
-    batch.n_reads = n; batch.reserved = 0; batch.first_index = mFirstIndex; batch.total_bases = total;
+    batch.n_reads = n; batch.max_len = 0; batch.first_index = mFirstIndex; batch.total_bases = total;
     batch.offsets = b.offsets; batch.lengths = b.lengths; batch.bases2 = b.bases2; batch.qual = b.qual;
 }
 

@@ -56,6 +56,7 @@ class DeviceBatch:
     def c_struct(self):
         b = abi.FqBatch()
         b.n_reads, b.first_index, b.total_bases = self.n, self.first_index, self.total
+        b.max_len = self.L
         b.offsets, b.lengths = self.offsets.data_ptr(), self.lengths.data_ptr()
         b.bases2, b.qual = self.bases2.data_ptr(), self.qual.data_ptr()
         return b

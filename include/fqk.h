@@ -117,7 +117,9 @@ typedef struct fq_params {
  */
 typedef struct fq_batch {
     uint32_t        n_reads;
-    uint32_t        reserved;
+    uint32_t        max_len;       /* longest read of the batch, 0 = unknown (the host entry points then
+                                      scan lengths[]; the device entry points assume max_cycles, which keeps
+                                      paired-end batches off the fused kernel when max_cycles > 496)      */
     uint64_t        first_index;   /* global index of read 0 (input order)    */
     uint64_t        total_bases;   /* padded extent: bases2 has total/4 bytes */
     const uint32_t* offsets;       /* [n_reads]                               */

@@ -105,7 +105,7 @@ extern "C" __attribute__((visibility("default"))) int emu_pe_run(const fq_params
         sts32(S32 + L.o_cnt + 16u, bad ? 0u : nt);
         V4X X; X.D = &D; X.Lp = &L; X.S32 = S32;
         for(int m = 0; m < 2; ++m){ X.pre32[m] = L.o_pre[m]; X.post32[m] = L.o_post[m]; }
-        X.ins32 = L.o_ins; X.bc = reinterpret_cast<BlockCounters*>(sm.data() + L.o_bc);
+        X.dbg = 0; X.ins32 = L.o_ins; X.bc = reinterpret_cast<BlockCounters*>(sm.data() + L.o_bc);
         X.out1 = o1 + t0; X.out2 = o2 + t0; X.outp = op + t0; X.nt = bad ? 0 : (int)nt;
         for(int j = 0; j < T / 32; ++j){
             if(32 * j >= X.nt) break;

@@ -18,23 +18,37 @@ def test_se(name, impl):
         util.assert_same(util.run_cuda(opt, reads, chunks=3, impl=impl), util.run_oracle(opt, reads))
 
 
+@pytest.mark.parametrize("impl", [0, 1, 3], ids=["auto", "generic", "two_phase"])
 @pytest.mark.parametrize("name", list(configs.PE))
-def test_pe(name):
+def test_pe(name, impl):
     opt = configs.options(name)
     r1, r2 = synth.pe_novaseq(4000, 150, seed=41, frag_mean=220, frag_sd=90)
-    util.assert_same(util.run_cuda(opt, r1, r2, chunks=2), util.run_oracle(opt, r1, r2))
+    util.assert_same(util.run_cuda(opt, r1, r2, chunks=2, impl=impl), util.run_oracle(opt, r1, r2))
     a, b = synth.ragged(4000, seed=42), synth.ragged(4000, seed=43)
-    util.assert_same(util.run_cuda(opt, a, b), util.run_oracle(opt, a, b))
+    util.assert_same(util.run_cuda(opt, a, b, impl=impl), util.run_oracle(opt, a, b))
     a = synth.ragged(3000, seed=44, lmin=20, lmax=200, n_rate=0.01, lowq_rate=0.05)
     b = synth.revcomp_reads(a)
-    util.assert_same(util.run_cuda(opt, a, b), util.run_oracle(opt, a, b))
+    util.assert_same(util.run_cuda(opt, a, b, impl=impl), util.run_oracle(opt, a, b))
 
 
-def test_long_reads_250():
+@pytest.mark.parametrize("impl", [0, 3], ids=["auto", "two_phase"])
+def test_long_reads_250(impl):
     opt = configs.options("cfg5")
     r1, r2 = synth.pe_novaseq(2000, 250, seed=45, frag_mean=420, frag_sd=120)
-    util.assert_same(util.run_cuda(opt, r1, r2), util.run_oracle(opt, r1, r2))
+    util.assert_same(util.run_cuda(opt, r1, r2, impl=impl), util.run_oracle(opt, r1, r2))
     opt = configs.options("cfg3", max_cycles=1024)
+    util.assert_same(util.run_cuda(opt, r1, r2, impl=impl), util.run_oracle(opt, r1, r2))
+
+
+def test_pe_many_tiles_and_blocks():
+    """Enough pairs for several tiles per block of the fused paired-end kernel on every SM, ragged tails included."""
+    for name in ("cfg3", "cfg1", "pe_merge_cut"):
+        opt = configs.options(name)
+        r1, r2 = synth.pe_novaseq(60000, 150, seed=51, frag_mean=260, frag_sd=100)
+        util.assert_same(util.run_cuda(opt, r1, r2), util.run_oracle(opt, r1, r2))
+    # 250 bp: two chunks per tile, so a trim warp runs up to four tiles ahead of the slowest one (tile-tag handshake)
+    opt = configs.options("cfg5", max_cycles=256)
+    r1, r2 = synth.pe_novaseq(40000, 250, seed=52, frag_mean=420, frag_sd=120)
     util.assert_same(util.run_cuda(opt, r1, r2), util.run_oracle(opt, r1, r2))
 
 
