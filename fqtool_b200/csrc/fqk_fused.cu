@@ -18,6 +18,7 @@
 // both - N, T = bit0 - both, C = bit1 - both, G = both.  Per-cycle base totals come from a per-block read-length
 // histogram, which relies on the zero padding of the batch layout.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include "fqk_fused.h"
 #include "fqk_pe.cuh"
@@ -871,5 +872,15 @@ int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_re
     const int grid = (int)((B1.n + ppb - 1) / ppb);
     static const int dbg = getenv("FQK_V4_DEBUG") ? atoi(getenv("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
     k_pe_v4<<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    if(dbg & 256){                                         // section clocks of the trim warps (see V4_PROF)
+        unsigned long long h[16];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(h, g_v4prof, sizeof(h));
+        fprintf(stderr, "v4prof T=%d NS=%d Wr=%d chunks=%llu |", p.T, p.NS, p.Wr, h[15]);
+        for(int i = 0; i < 12; ++i) fprintf(stderr, " %d:%.0f", i, h[15] ? (double)h[i] / (double)h[15] : 0.0);
+        fprintf(stderr, " | verifies/chunk %.2f\n", h[15] ? (double)h[9] / (double)h[15] : 0.0);
+        static const unsigned long long z[16] = {};
+        cudaMemcpyToSymbol(g_v4prof, z, sizeof(z));
+    }
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }

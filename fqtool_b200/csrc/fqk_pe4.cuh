@@ -34,6 +34,19 @@
 #ifndef EMU_MARK
 #define EMU_MARK(k)
 #endif
+// FQK_V4_DEBUG bit 256: per-section clock totals of the trim warps (lane 0) into g_v4prof, printed by pe4_launch
+#ifndef FQK_EMU
+#define V4_GSYNC(X) do{ if((X).sync_id) nb_sync((X).sync_id, (X).sync_n); }while(0)
+__device__ unsigned long long g_v4prof[16];
+#define V4_PROF(on, k) do{ if(on){ const long long t_ = clock64(); if(lane == 0) atomicAdd(&g_v4prof[k], (unsigned long long)(t_ - t0_)); t0_ = clock64(); } }while(0)
+#define V4_PROF0(on) long long t0_ = (on) ? clock64() : 0
+#define V4_PROFC(on, k) do{ if((on) && lane == 0) atomicAdd(&g_v4prof[k], 1ull); }while(0)
+#else
+#define V4_GSYNC(X)
+#define V4_PROF(on, k)
+#define V4_PROF0(on)
+#define V4_PROFC(on, k)
+#endif
 constexpr int V4_TAILMAX = 8;                 // cut-off tails up to this many bases are handled by the trim warps
 constexpr int V4_MAXLEN = 496;                // reads up to this length: one packed word per lane
 
@@ -431,7 +444,9 @@ __device__ V4_NI uint2 v4_overlap_lockstep(uint32_t Aqa, uint32_t Aba, uint32_t 
                 }
             }
             if(dbgx & 64) cm = 0u;
+            V4_PROF0(dbgx & 256);
             while(__any_sync(V4_FULL, cm != 0u)){
+                V4_PROFC(dbgx & 256, 9);
                 const uint32_t bal = __ballot_sync(V4_FULL, cm != 0u);
                 const int src = __ffs((int)bal) - 1;
                 const PkPair K = v4_pack_pair(__shfl_sync(V4_FULL, Aqa, src), __shfl_sync(V4_FULL, Aba, src), __shfl_sync(V4_FULL, pa, src),
@@ -445,6 +460,7 @@ __device__ V4_NI uint2 v4_overlap_lockstep(uint32_t Aqa, uint32_t Aba, uint32_t 
                     else cm &= cm - 1u;
                 }
             }
+            V4_PROF(dbgx & 256, 8);
         }
     }
     return res;
@@ -483,6 +499,7 @@ struct V4X {
     BlockCounters* bc;
     fq_read_result* out1; fq_read_result* out2; fq_pair_result* outp;   // records of the tile's first pair
     int nt;                        // pairs in the tile
+    int sync_id, sync_n;           // named barrier of the warps that work on the same tile (0 = none), threads in it
     int dbg;                       // timing experiments (FQK_V4_DEBUG): 4 no first analyze, 8 no second, 16 no tail corrections, 32 no polyG
 };
 
@@ -540,8 +557,11 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     const bool valid = i < X.nt;
     PeRead a, b;
     bool a1 = false, a2 = false;
+    const bool prof = (X.dbg & 256) != 0;
+    V4_PROF0(prof);
 #pragma unroll 1
     for(int m = 0; m < 2; ++m){                                     // one instance of the per-read code for both mates
+        V4_GSYNC(X);
         const uint32_t So = X.S32 + L.o_off[m], Sl = X.S32 + L.o_len[m];
         const uint32_t a0 = lds32(So), bshift = (a0 >> 2) & 15u;
         uint32_t doff = 0, dlen = 0;
@@ -565,6 +585,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         }
         if(m){ b = r; a2 = alive; } else { a = r; a1 = alive; }
     }
+    V4_GSYNC(X);
+    V4_PROF(prof, 0);
     fq_read_result rec1 = {}, rec2 = {};
     fq_pair_result pr = {};
     pr.insert_size = 0xFFFF;
@@ -583,9 +605,13 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             }
         }
     }
+    V4_GSYNC(X);
+    V4_PROF(prof, 1);
     OvRes ov; ov.overlapped = 0; ov.offset = 0; ov.len = 0; ov.diff = 0;
     // first analyze(): :303 when -a/-c, else :330 (insert size only); identical inputs either way
     if(!(X.dbg & 4)) v4_overlap_chunk(a, b, both, P.overlap_diff_limit, P.overlap_require, lane, ov, X.dbg);
+    V4_GSYNC(X);
+    V4_PROF(prof, 2);
     int isize = -1;
     if(both){
         pr.flags |= FQK_P_OV1_DONE | (ov.overlapped ? FQK_P_OV1_OVERLAP : 0);
@@ -637,9 +663,13 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         if(P.trim_max_len1 > 0 && P.trim_max_len1 < a.len){ a.len = P.trim_max_len1; modified = true; }
         if(P.trim_max_len2 > 0 && P.trim_max_len2 < b.len){ b.len = P.trim_max_len2; modified = true; }
     }
+    V4_GSYNC(X);
+    V4_PROF(prof, 3);
     // second analyze(), :354: same answer as the first when neither read changed
     OvRes ov2 = ov;
     if(!(X.dbg & 8)) v4_overlap_chunk(a, b, P.merge_enabled && both && modified, P.overlap_diff_limit, P.overlap_require, lane, ov2);
+    V4_GSYNC(X);
+    V4_PROF(prof, 4);
     bool merge_processed = false; int res1 = 0, res2 = 0;
     int fcA = -1, fnA = 0, fcB = -1, fnB = 0;                // updates of mFilterReadStats: (code, amount) x 2
     bool merged = false;
@@ -672,6 +702,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         res2 = v4_pass_filter(P, b, !a2);
         fcA = max(res1, res2); fnA = 2;                             // :390, mPaired == true
     }
+    V4_GSYNC(X);
+    V4_PROF(prof, 5);
     rec1.result = (uint8_t)res1; rec2.result = (uint8_t)res2;
     if(!a1) rec1.flags |= FQK_F_DROPPED; else { rec1.start = (uint16_t)a.start; rec1.len = (uint16_t)a.len; }
     if(!a2) rec2.flags |= FQK_F_DROPPED; else { rec2.start = (uint16_t)b.start; rec2.len = (uint16_t)b.len; }
@@ -684,6 +716,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         const uint32_t nm = __ballot_sync(V4_FULL, merged);
         if(lane == 0 && nm) atomicAdd(&X.bc->merged_pairs, (uint32_t)__popc(nm));
     }
+    V4_GSYNC(X);
+    V4_PROF(prof, 6);
     // ---- what the statistics warps need: length histograms, exception lists, short tails ----
     const uint32_t cnt32 = X.S32 + L.o_cnt;
 #pragma unroll
@@ -721,6 +755,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         const uint32_t pmax = (uint32_t)b.start + (uint32_t)b.len - 1u - pr.ov2_len + pr.merge_len1;
         v4_push(wm, cnt32 + 8u, X.S32 + L.o_exm, make_desc(b.doff, pmax, pr.merge_len1, pr.merge_len2, 3u), lane);
     }
+    V4_PROF(prof, 7);
+    V4_PROFC(prof, 15);
 }
 
 #ifndef FQK_EMU
@@ -878,19 +914,42 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
             // chunks are handed out in order from a shared counter: a chunk that takes long (many candidates to verify)
             // does not hold back the chunks behind it, and at most V4_WORKERS consecutive chunks are in flight
             const uint32_t next32 = sm32 + L.o_misc;
+            const int idle_from = V4_WORKERS - ((dbg >> 12) & 7);          // timing experiment: fewer working warps
+            // Tile groups: the CH warps of a group work on the CH chunks of one tile and meet at a named barrier between the
+            // sections of v4_chunk, so that they run the same code at about the same time.  The trim role walks ~48 KB of
+            // code per chunk, more than the SM's instruction cache holds; unsynchronised, every warp takes its own misses
+            // and the role does not speed up with more warps (3 warps 8.4 ms, 7 warps 6.5 ms on cfg3).  In step, one miss
+            // serves the group: 6.7 -> 5.1 ms with two groups of three (profiles/r02_pe_v4_notes.md).  Groups take tiles
+            // round robin.  FQK_V4_DEBUG bit 512 switches back to chunks handed out one by one from a shared counter.
+            // Groups need a spare stage to prefetch into (NS > groups); without one the hand-out from the counter is as fast.
+            const bool gs = !(dbg & 512) && CH >= 2 && CH <= V4_WORKERS && NS > V4_WORKERS / CH;
+            const int NG = gs ? V4_WORKERS / CH : 1, grp = tw / CH, jst = tw - grp * CH;
+            X.sync_id = gs ? 2 * NS + 1 + grp : 0; X.sync_n = CH * 32;
+            int kk = grp;
             for(;;){
-                int c = 0;
-                if(lane == 0) c = (int)atoms_add(next32, 1u);
-                c = __shfl_sync(V4_FULL, c, 0);
-                if(c >= nchunks) break;
-                const int k = c / CH, j = c - k * CH, s = k % NS;
+                if(tw >= idle_from) break;
+                int k, j;
+                if(gs){
+                    if(grp >= NG || kk >= ntiles) break;
+                    k = kk; j = jst; kk += NG;
+                }else{
+                    int c = 0;
+                    if(lane == 0) c = (int)atoms_add(next32, 1u);
+                    c = __shfl_sync(V4_FULL, c, 0);
+                    if(c >= nchunks) break;
+                    k = c / CH; j = c - k * CH;
+                }
+                const int s = k % NS;
                 X.S32 = sm32 + L.o_stage + (uint32_t)s * L.stage_bytes;
+                V4_PROF0(dbg & 256);
                 wait_tile_tag(X.S32 + L.o_cnt + 20, (uint32_t)k);
                 mbar_wait_sleep(&full[s], (uint32_t)(k / NS) & 1u, 20000);
                 X.nt = (int)lds32(X.S32 + L.o_cnt + 16);
+                V4_PROF(dbg & 256, 10);
                 const uint32_t t0 = lo + (uint32_t)k * T;
                 X.out1 = out1 + t0; X.out2 = out2 + t0; X.outp = outp + t0;
-                if(32 * j < X.nt && !(dbg & 1)) v4_chunk(X, j, lane, tl);
+                if((gs || 32 * j < X.nt) && !(dbg & 1)) v4_chunk(X, j, lane, tl);
+                V4_PROF(dbg & 256, 11);
                 __syncwarp();
                 __threadfence_block();
                 nb_arrive(1 + s, CH * 32 + V4_STATS);
@@ -1064,6 +1123,9 @@ inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin){
             if(score > best){ best = score; bestT = T; bestNS = NS; }
         }
     if(best < 0) return p;
+    static const int envT = getenv("FQK_V4_T") ? atoi(getenv("FQK_V4_T")) : 0, envNS = getenv("FQK_V4_NS") ? atoi(getenv("FQK_V4_NS")) : 0;
+    if(envT > 0 && envNS >= 2 && envNS <= 4 && envT % 32 == 0 &&
+       (size_t)v4_layout(p.Wr, p.Wm, envT, envNS, P.insert_size_max + 1).total + 128 <= budget){ bestT = envT; bestNS = envNS; }   // timing experiments
     p.T = bestT; p.NS = bestNS;
     p.smem = v4_layout(p.Wr, p.Wm, p.T, p.NS, P.insert_size_max + 1).total + 128;
     p.ok = true;
