@@ -7,8 +7,18 @@ A step is one pass of the per-read QC+trim hot path over the whole HBM-resident
 synthetic workload of this rank (cfg2 at N=1: 100 M SE reads of 150 bp in 25 batches
 of 4 M reads).  `value` = Gbases/s over all ranks with inputs resident in HBM; `e2e` =
 the same metric through the host-buffer C-ABI call (pinned host batches, H2D + kernels
-+ D2H of the records inside the timed region).  One rank per GPU; accumulators are
-merged by one NCCL all-reduce per run inside fqk_finalize (timed, after the K steps).
++ D2H of the records inside the timed region; median of --e2e-steps steps).  One rank
+per GPU; accumulators are merged by one NCCL all-reduce per run inside fqk_finalize
+(timed, after the K steps).
+
+The same JSON line also carries, under `configs`, the other synthetic BASELINE.json
+configurations measured with the same protocol on smaller resident workloads: cfg3 and
+cfg4 (weak scaling, --extra-units per GPU; cfg4's fqk_finalize runs the four
+duplication-table all-reduces and is timed as `finalize_ms`) and cfg5 as a STRONG
+scaling record (`scaling_cfg5`: a fixed total of --cfg5-total pairs sharded contiguously
+by global pair index over the ranks).  At N > 1 `merge_check` compares the NCCL-merged
+accumulators and duplication table of two small sharded streams bit-exactly with the
+same streams run on one rank.
 """
 import argparse
 import json
@@ -45,8 +55,12 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "generic"])
     ap.add_argument("--reads", type=int, default=0, help="reads (pairs) per GPU; 0 = the config's size capped by HBM")
     ap.add_argument("--cpu-sample", type=int, default=4_000_000, help="reads of the CPU-baseline sample")
-    ap.add_argument("--e2e-steps", type=int, default=1)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the cfg3/cfg4/cfg5 records and the merge check")
+    ap.add_argument("--extra-units", type=int, default=16_000_000, help="reads (pairs) per GPU of the cfg3/cfg4 records")
+    ap.add_argument("--cfg5-total", type=int, default=128_000_000, help="pairs of the cfg5 strong-scaling record (whole job)")
+    ap.add_argument("--extra-steps", type=int, default=5)
     return ap.parse_args()
 
 
@@ -163,130 +177,239 @@ def run_reference_arm(a):
 
 
 # ----------------------------------------------------------------- B200 arm
+def kernel_name(cfg, params, impl):
+    from fqtool_b200 import workload
+    c = workload.CONFIGS[cfg]
+    if c["paired"]:
+        return "k_pe_v4" if impl == "b200" else "k_trim_pe+k_stats_pe"
+    return "k_se_v3" if (not params.kmer_len and impl == "b200") else "k_fused_se_ws"
+
+
+class Job:
+    """One configuration resident in HBM on this rank: engine, batches, record buffers."""
+
+    def __init__(self, ctx, cfg, units, first):
+        import torch
+        from fqtool_b200 import workload
+        self.ctx, self.cfg, self.units, self.c = ctx, cfg, units, workload.CONFIGS[cfg]
+        self.opt = workload.options_for(cfg)
+        self.params = self.opt.to_params()
+        self.eng = ctx.engine(self.params)
+        if ctx.a.impl == "generic":
+            self.eng.set_impl(1)
+        self.stream = torch.cuda.ExternalStream(self.eng.stream, device=ctx.dev)
+        self.batches, self.outs = [], []
+        dev = ctx.dev
+        for i in range((units + BATCH_READS - 1) // BATCH_READS):
+            n = min(BATCH_READS, units - i * BATCH_READS)
+            b1, b2 = workload.generate(cfg, n, first + i * BATCH_READS, dev, self.eng.stream)
+            o1 = torch.empty(n * 16, dtype=torch.uint8, device=dev)
+            o2 = torch.empty(n * 16, dtype=torch.uint8, device=dev) if b2 else None
+            op = torch.empty(n * 24, dtype=torch.uint8, device=dev) if b2 else None
+            self.batches.append((b1, b2, b1.c_struct(), b2.c_struct() if b2 else None)); self.outs.append((o1, o2, op))
+        self.eng.sync()
+        self.nb = len(self.batches)
+        self.bases_per_step = units * self.c["L"] * (2 if self.c["paired"] else 1)
+
+    def step(self):
+        e = self.eng
+        for (b1, b2, s1, s2), (o1, o2, op) in zip(self.batches, self.outs):
+            if b2 is None:
+                e.process_se_device(s1, o1.data_ptr())
+            else:
+                e.process_pe_device(s1, s2, o1.data_ptr(), o2.data_ptr(), op.data_ptr())
+
+    def timed(self, steps, warmup, sampler=None):
+        """warmup untimed steps, then `steps` steps + fqk_finalize between two events; max over ranks."""
+        import torch
+        from fqtool_b200 import abi, workload
+        ctx, eng = self.ctx, self.eng
+        for _ in range(warmup):
+            self.step()
+        eng.finalize()                               # warm-up of the run-level merge too (NCCL connects lazily)
+        eng.reset()
+        eng.set_kernel_timing(True)
+        eng.kernel_times()
+        if sampler:
+            sampler.start()
+        launches0 = eng.launch_count
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        ctx.barrier()
+        e0.record(self.stream)
+        for _ in range(steps):
+            self.step()
+        e1.record(self.stream)
+        flat = eng.finalize()                       # the once-per-run NCCL all-reduce(s) + D2H of the accumulators
+        e2.record(self.stream)
+        ctx.barrier()
+        ms_total = ctx.max_over_ranks(e0.elapsed_time(e2))
+        fin_ms = ctx.max_over_ranks(e1.elapsed_time(e2))
+        launches = eng.launch_count - launches0
+        kms, kn = eng.kernel_times()
+        eng.set_kernel_timing(False)
+        L = eng.layout
+        total_units = ctx.sum_over_ranks(self.units)
+        counted = int(flat[L.stats_off[0] + L.s_reads])
+        assert counted == total_units * steps, (self.cfg, counted, total_units, steps)   # every read of every step was counted
+        total_bases = total_units * self.c["L"] * (2 if self.c["paired"] else 1)
+        # roofline of the dominant kernel: live CUDA-event durations on the launching stream
+        fused = kernel_name(self.cfg, self.params, ctx.a.impl)
+        names = {abi.T_TRIM: "k_trim", abi.T_STATS: "k_stats", abi.T_DUP: "k_dup", abi.T_FUSED: fused}
+        dom = max(names, key=lambda s: kms[s])
+        per_launch_ms = kms[dom] / max(kn[dom], 1)
+        per_launch_units = min(BATCH_READS, self.units)
+        alg = workload.algorithmic_bytes(self.cfg, per_launch_units)
+        achieved = alg / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
+        roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": ctx.peak, "unit": "GB/s",
+                    "frac": achieved / ctx.peak, "traffic": ctx.traffic.get(names[dom]), "peak_source": ctx.peak_src,
+                    "algorithmic_bytes_per_launch": alg, "avg_launch_ms": per_launch_ms,
+                    "kernel_ms_share": {names[s]: kms[s] / max(kms[abi.T_ALL], 1e-9) for s in names if kn[s]},
+                    "ms_per_launch": {names[s]: kms[s] / kn[s] for s in names if kn[s]},
+                    "whole_path_achieved": workload.algorithmic_bytes(self.cfg, self.units) * steps / (kms[abi.T_ALL] / 1e3) / 1e9
+                    if kms[abi.T_ALL] > 0 else None}
+        return {"value": total_bases * steps / (ms_total / 1e3) / 1e9, "unit": "Gbases/s", "ms_per_step": ms_total / steps,
+                "finalize_ms": fin_ms, "steps": steps, "warmup": warmup, "units_per_gpu": self.units,
+                "units_total": total_units, "batches_per_step": self.nb, "gpu_launches": launches, "roofline": roofline,
+                "flags": self.c["cli"]}
+
+    def close(self):
+        self.batches = self.outs = None
+        self.eng.close()
+
+
+class Ctx:
+    """Rank plumbing: torch.distributed for barriers and the ncclUniqueId hand-over; one NCCL communicator per engine
+    inside the library."""
+
+    def __init__(self, a):
+        import torch
+        import torch.distributed as dist
+        self.a, self.torch, self.dist = a, torch, dist
+        self.rank = int(os.environ.get("RANK", "0")); self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+        peaks = {}
+        pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(pk):
+            peaks = json.load(open(pk))
+        self.peak = peaks.get("hbm_gbs", 6650.0)
+        self.peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        self.traffic = json.load(open(tr)) if os.path.exists(tr) else {}
+
+    def engine(self, params, single=False):
+        from fqtool_b200.engine import Engine
+        torch, dist = self.torch, self.dist
+        if self.world == 1 or single:
+            return Engine(params, device=self.local)
+        t = torch.zeros(128, dtype=torch.uint8, device=self.dev)
+        if self.rank == 0:
+            t.copy_(torch.frombuffer(bytearray(Engine.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        return Engine(params, device=self.local, rank=self.rank, nranks=self.world, nccl_unique_id=bytes(t.cpu().numpy().tobytes()))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def _red(self, x, op):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max_over_ranks(self, x):
+        return self._red(x, self.dist.ReduceOp.MAX)
+
+    def sum_over_ranks(self, x):
+        return int(round(self._red(float(x), self.dist.ReduceOp.SUM)))
+
+    def free(self):
+        import gc
+        gc.collect()
+        self.torch.cuda.empty_cache()
+
+
+def merge_check(ctx):
+    """N > 1: the NCCL merge inside fqk_finalize (one sum all-reduce of the flat buffer; min/sum/min/min protocol for the
+    duplication table, Duplicate::addRecord src/duplicate.cpp:46-62, Stats::merge src/stats.cpp:815-863) against the same
+    stream run on ONE rank: flat accumulators and mDups/mCounts/mGC bit-exact on every rank."""
+    import numpy as np
+    from fqtool_b200 import workload
+    torch, dist = ctx.torch, ctx.dist
+    out = {}
+    for cfg, total in (("cfg4", 300_000), ("pe_dup", 150_001)):
+        c = workload.CONFIGS[cfg]
+        params = workload.options_for(cfg).to_params()
+        lo = total * ctx.rank // ctx.world; hi = total * (ctx.rank + 1) // ctx.world
+
+        def run(eng, a, b):
+            b1, b2 = workload.generate(cfg, b - a, a, ctx.dev, eng.stream)
+            o1 = torch.empty((b - a) * 16, dtype=torch.uint8, device=ctx.dev)
+            if b2 is None:
+                eng.process_se_device(b1.c_struct(), o1.data_ptr())
+            else:
+                o2 = torch.empty((b - a) * 16, dtype=torch.uint8, device=ctx.dev)
+                op = torch.empty((b - a) * 24, dtype=torch.uint8, device=ctx.dev)
+                eng.process_pe_device(b1.c_struct(), b2.c_struct(), o1.data_ptr(), o2.data_ptr(), op.data_ptr())
+            eng.sync()
+            flat = eng.finalize()
+            return flat, eng.dup_table()
+        eng = ctx.engine(params)
+        flat, dup = run(eng, lo, hi)
+        flat_again = eng.finalize()                 # the merge leaves the local accumulators and the local table intact
+        dup_again = eng.dup_table()
+        eng.close()
+        ok = np.array_equal(flat, flat_again) and all(np.array_equal(x, y) for x, y in zip(dup, dup_again))
+        if ctx.rank == 0:
+            one = ctx.engine(params, single=True)
+            want, wdup = run(one, 0, total)
+            one.close()
+            ref = [torch.from_numpy(want.view(np.int64)).to(ctx.dev)] + [torch.from_numpy(x.copy()).to(ctx.dev) for x in
+                   (wdup[0].view(np.int64), wdup[1].view(np.int32), wdup[2])]
+        else:
+            ref = [torch.empty(len(flat), dtype=torch.int64, device=ctx.dev), torch.empty(len(dup[0]), dtype=torch.int64, device=ctx.dev),
+                   torch.empty(len(dup[1]), dtype=torch.int32, device=ctx.dev), torch.empty(len(dup[2]), dtype=torch.uint8, device=ctx.dev)]
+        for t in ref:
+            dist.broadcast(t, 0)
+        mine = [flat.view(np.int64), dup[0].view(np.int64), dup[1].view(np.int32), dup[2]]
+        ok = ok and all(np.array_equal(t.cpu().numpy(), m) for t, m in zip(ref, mine))
+        bad = ctx.sum_over_ranks(0 if ok else 1)
+        assert bad == 0, f"merge_check {cfg}: {bad} rank(s) differ from the single-rank run"
+        out[cfg] = {"units": total, "dup_keys_nonzero": int((dup[1] != 0).sum()), "flat_u64": int(len(flat))}
+    return {"status": "ok", "streams": out,
+            "what": "merged flat accumulators + duplication table of N contiguous shards == one-rank run, bit-exact on every rank; second fqk_finalize idempotent"}
+
+
 def main():
     a = parse()
     if a.impl == "reference":
         return run_reference_arm(a)
     import numpy as np
-    import torch
-    import torch.distributed as dist
     from fqtool_b200 import abi, workload
-    from fqtool_b200.engine import Engine
-
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+    ctx = Ctx(a)
+    torch, dist, dev, rank, world = ctx.torch, ctx.dist, ctx.dev, ctx.rank, ctx.world
     cfg = a.config
     c = workload.CONFIGS[cfg]
-    opt = workload.options_for(cfg)
-    params = opt.to_params()
-
-    # one NCCL communicator inside the library (ncclUniqueId travels through torch.distributed)
-    uid = None
-    if world > 1:
-        t = torch.zeros(128, dtype=torch.uint8, device=dev)
-        if rank == 0:
-            t.copy_(torch.frombuffer(bytearray(Engine.nccl_unique_id()), dtype=torch.uint8))
-        dist.broadcast(t, 0)
-        uid = bytes(t.cpu().numpy().tobytes())
-    eng = Engine(params, device=local, rank=rank, nranks=world, nccl_unique_id=uid)
-    if a.impl == "generic":
-        eng.set_impl(1)
-    stream = torch.cuda.ExternalStream(eng.stream, device=dev)
 
     # ---- workload: per-GPU share, resident in HBM (weak scaling: fixed per GPU) ----
     per_read_bytes = ((c["L"] + 15) // 16 * 16) * 1.25 + 6 + 16
     per_unit = per_read_bytes * (2 if c["paired"] else 1) + (24 if c["paired"] else 0)
     free_b, _ = torch.cuda.mem_get_info(dev)
     cap = int(free_b * 0.80 / per_unit)
-    reads = a.reads or min(c["reads"], cap)
-    reads = max(1, reads)
-    nb = (reads + BATCH_READS - 1) // BATCH_READS
-    first = rank * reads
-    batches, outs = [], []
-    for i in range(nb):
-        n = min(BATCH_READS, reads - i * BATCH_READS)
-        b1, b2 = workload.generate(cfg, n, first + i * BATCH_READS, dev, eng.stream)
-        o1 = torch.empty(n * 16, dtype=torch.uint8, device=dev)
-        o2 = torch.empty(n * 16, dtype=torch.uint8, device=dev) if b2 else None
-        op = torch.empty(n * 24, dtype=torch.uint8, device=dev) if b2 else None
-        batches.append((b1, b2, b1.c_struct(), b2.c_struct() if b2 else None)); outs.append((o1, o2, op))
-    eng.sync()
-    units = reads
-    bases_per_step = units * c["L"] * (2 if c["paired"] else 1)
-
-    def step():
-        for (b1, b2, s1, s2), (o1, o2, op) in zip(batches, outs):
-            if b2 is None:
-                eng.process_se_device(s1, o1.data_ptr())
-            else:
-                eng.process_pe_device(s1, s2, o1.data_ptr(), o2.data_ptr(), op.data_ptr())
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(a.warmup):
-        step()
-    eng.finalize()                               # warm-up of the run-level merge too (NCCL connects lazily)
-    eng.reset()
-    eng.set_kernel_timing(True)
-    eng.kernel_times()
-    sampler = ClockSampler(local); sampler.start()
-    launches0 = eng.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(stream)
-    for _ in range(a.steps):
-        step()
-    flat = eng.finalize()                       # the once-per-run NCCL all-reduce + D2H of the accumulators
-    e1.record(stream)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = eng.launch_count - launches0
+    reads = max(1, a.reads or min(c["reads"], cap))
+    job = Job(ctx, cfg, reads, rank * reads)
+    eng, nb, batches = job.eng, job.nb, job.batches
+    sampler = ClockSampler(ctx.local)
+    main_rec = job.timed(a.steps, a.warmup, sampler)
     clocks = sampler.stop()
-    kms, kn = eng.kernel_times()
-    eng.set_kernel_timing(False)
-    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    ms_total = float(tmax.item())
-    value = bases_per_step * world * a.steps / (ms_total / 1e3) / 1e9
-
-    # sanity of the timed work: every read of every step was counted (pre1 reads over all ranks)
-    L = eng.layout
-    reads_counted = int(flat[L.stats_off[0] + L.s_reads])
-    assert reads_counted == units * world * a.steps, (reads_counted, units, world, a.steps)
-
-    # ---- roofline of the dominant kernel (live CUDA-event durations on the launching stream) ----
-    peaks = {}
-    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(pk):
-        peaks = json.load(open(pk))
-    peak = peaks.get("hbm_gbs", 6650.0)
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    fused_name = "k_se_v3" if (not c["paired"] and not opt.to_params().kmer_len and a.impl == "b200") else "k_fused_se_ws"
-    names = {abi.T_TRIM: "k_trim", abi.T_STATS: "k_stats", abi.T_DUP: "k_dup", abi.T_FUSED: fused_name}
-    dom = max(names, key=lambda s: kms[s])
-    per_launch_ms = kms[dom] / max(kn[dom], 1)
-    alg = workload.algorithmic_bytes(cfg, min(BATCH_READS, reads))
-    achieved = alg / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg, "avg_launch_ms": per_launch_ms,
-                "kernel_ms_share": {names[s]: kms[s] / max(kms[abi.T_ALL], 1e-9) for s in names if kn[s]},
-                "whole_path_achieved": workload.algorithmic_bytes(cfg, units) * a.steps / (kms[abi.T_ALL] / 1e3) / 1e9
-                if kms[abi.T_ALL] > 0 else None}
-    tr = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr):
-        roofline["traffic"] = json.load(open(tr)).get(names[dom])
 
     # ---- end to end through the host-buffer C-ABI call ----
     n_host = min(4, nb)
@@ -317,24 +440,26 @@ def main():
             e2e_units += h1.n
         if pending is not None:
             eng.wait(pending)
-    e2e_step()                                   # warm-up (allocates the staging buffers)
+        return eng.finalize()                        # the step's metric: accumulators to the host (NCCL-merged at N > 1)
+    e2e_step()                                       # warm-up (allocates the staging buffers)
     eng.reset()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(a.e2e_steps):
-        e2e_step()
-    flat2 = eng.finalize()
+    times = []
+    for _ in range(max(a.e2e_steps, 1)):
+        ctx.barrier()
+        t0 = time.perf_counter()
+        flat2 = e2e_step()
+        ctx.barrier()
+        times.append(ctx.max_over_ranks(time.perf_counter() - t0))
     d2h_final = flat2.nbytes
-    barrier()
-    dt = time.perf_counter() - t0
-    tt = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    e2e_bases = e2e_units * c["L"] * (2 if c["paired"] else 1) * a.e2e_steps * world
-    e2e = {"value": e2e_bases / float(tt.item()) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h + d2h_final // max(a.e2e_steps, 1), "steps": a.e2e_steps,
-           "ms_per_step": float(tt.item()) * 1e3 / a.e2e_steps,
-           "note": f"{nb} fqk_submit_se/fqk_wait (SE, two packs in flight) or fqk_process_pe calls per step over {n_host} distinct pinned host batches of {BATCH_READS} reads"}
+    ts = sorted(times)
+    med = ts[len(ts) // 2]
+    e2e_bases = e2e_units * c["L"] * (2 if c["paired"] else 1) * world
+    e2e = {"value": e2e_bases / med / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h + d2h_final, "steps": len(ts), "ms_per_step": med * 1e3,
+           "statistic": "median over steps of the max over ranks", "best": e2e_bases / ts[0] / 1e9, "worst": e2e_bases / ts[-1] / 1e9,
+           "ms_per_step_all": [round(t * 1e3, 2) for t in times],
+           "note": f"{nb} fqk_submit_se/fqk_wait (SE, two packs in flight) or fqk_process_pe calls + one fqk_finalize per step over "
+                   f"{n_host} distinct pinned host batches of {BATCH_READS} reads (already in the fq_batch layout; host packing is outside)"}
 
     # ---- the same through the ASCII entry point (FASTQ characters in, packing on the GPU) ----
     e2e_ascii = None
@@ -345,35 +470,65 @@ def main():
         pqual = torch.empty(len(qual), dtype=torch.uint8, pin_memory=True); pqual.numpy()[:] = qual
         areads = (pseq.numpy(), pqual.numpy(), off)
         eng.process_se_ascii(areads)
-        eng.reset(); barrier()
+        eng.reset(); ctx.barrier()
         t0 = time.perf_counter()
         reps = min(nb, 8)
         for _ in range(reps):
             eng.process_se_ascii(areads)
-        eng.finalize(); barrier()
-        dta = time.perf_counter() - t0
-        e2e_ascii = {"value": reps * hbs[0][0].n * c["L"] / dta / 1e9, "unit": "Gbases/s",
+        eng.finalize(); ctx.barrier()
+        dta = ctx.max_over_ranks(time.perf_counter() - t0)
+        e2e_ascii = {"value": world * reps * hbs[0][0].n * c["L"] / dta / 1e9, "unit": "Gbases/s",
                      "h2d_bytes_per_call": int(2 * len(seq) + 10 * hbs[0][0].n), "calls": reps,
                      "note": "fqk_process_se_ascii: FASTQ characters over PCIe (2 B/base), 2-bit packing by k_pack_ascii on the GPU"}
-        del pseq, pqual
+        del pseq, pqual, areads, seq, qual, off
+    del hbs, hout, batches
+    job.close(); del job, eng
+    ctx.free()
+
+    # ---- the other BASELINE.json configurations, same protocol, smaller resident workloads ----
+    extra, scaling_cfg5, mcheck = {}, None, None
+    if not a.no_extra and cfg == "cfg2":
+        for xc in ("cfg3", "cfg4"):
+            j = Job(ctx, xc, a.extra_units, rank * a.extra_units)
+            r = j.timed(a.extra_steps, 3)
+            r["scaling"] = "weak"; r["workload"] = workload.CONFIGS[xc]["desc"]
+            extra[xc] = r
+            j.close(); del j; ctx.free()
+        # cfg5: strong scaling of a fixed total, contiguous shards by global pair index
+        tot = a.cfg5_total
+        free_b, _ = torch.cuda.mem_get_info(dev)
+        tot = min(tot, int(free_b * 0.85 / 708) * world // BATCH_READS * BATCH_READS)
+        lo, hi = tot * rank // world, tot * (rank + 1) // world
+        j = Job(ctx, "cfg5", hi - lo, lo)
+        r = j.timed(max(3, a.extra_steps // 2 + 1), 3)
+        r["scaling"] = "strong"; r["workload"] = workload.CONFIGS["cfg5"]["desc"]; r["pairs_total"] = tot
+        extra["cfg5"] = r
+        scaling_cfg5 = {"n_gpus": world, "pairs_total": tot, "pairs_per_gpu": hi - lo, "value": r["value"], "unit": "Gbases/s",
+                        "ms_per_step": r["ms_per_step"], "finalize_ms": r["finalize_ms"], "scaling": "strong",
+                        "roofline_frac": r["roofline"]["frac"],
+                        "note": "fixed total sharded contiguously by global pair index; one NCCL all-reduce of the flat buffer in fqk_finalize"}
+        j.close(); del j; ctx.free()
+        if world > 1:
+            mcheck = merge_check(ctx)
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        del batches, outs
-        torch.cuda.empty_cache()
-        cb = cpu_reference_run(cfg, a.cpu_sample, 1, 0, dev)
+        ctx.free()
+        cb = cpu_reference_run(cfg, a.cpu_sample, 3, 1, dev)     # same protocol as the reference arm: 1 warm-up, mean of 3
         cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu_baseline["protocol"] = "1 warm-up run, mean of 3 timed runs"
 
     if rank == 0:
-        line = {"metric": "Gbases/s per-read QC+trim", "value": value, "unit": "Gbases/s", "n_gpus": world,
-                "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps, "higher_is_better": True,
+        line = {"metric": "Gbases/s per-read QC+trim", "value": main_rec["value"], "unit": "Gbases/s", "n_gpus": world,
+                "steps": a.steps, "warmup": a.warmup, "ms_per_step": main_rec["ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": c["desc"], "config": cfg, "flags": c["cli"], "reads_per_gpu": reads,
                            "read_length": c["L"], "batches_per_step": nb, "batch_reads": BATCH_READS,
                            "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit / 1e9),
                            "impl": a.impl},
-                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "gpu_launches": launches, "roofline": roofline,
-                "cpu_baseline": cpu_baseline}
+                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "gpu_launches": main_rec["gpu_launches"],
+                "roofline": main_rec["roofline"], "finalize_ms": main_rec["finalize_ms"], "cpu_baseline": cpu_baseline,
+                "configs": extra or None, "scaling_cfg5": scaling_cfg5, "merge_check": mcheck}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

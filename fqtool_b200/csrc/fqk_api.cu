@@ -70,6 +70,9 @@ struct fqk_ctx {
     std::vector<uint32_t> hsrc[2], hdst[2]; std::vector<uint16_t> hlen[2];
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
+    // cross-rank merge scratch, allocated once in fqk_create when nranks > 1 (no allocation between collectives)
+    uint64_t* m_flat = nullptr; uint32_t* m_idx = nullptr; unsigned long long* m_first = nullptr; uint32_t* m_status = nullptr;
+    int sticky = 0; std::string sticky_msg;   // first error of a pipelined pack (fqk_submit_se): reported by every later wait/finalize
     StagedBatch st[2];
     DevBuf res1, res2, resp;
     // pipelined single-end path (fqk_submit_se / fqk_wait): two slots, copies on their own streams
@@ -186,6 +189,8 @@ extern "C" int fqk_reset(fqk_ctx* c){
     CU(cudaSetDevice(c->device));
     CU(cudaMemsetAsync(c->flat, 0, c->D.L.total_u64 * sizeof(uint64_t), c->stream));
     CU(cudaMemsetAsync(c->err, 0, sizeof(uint32_t), c->stream));
+    c->sticky = 0; c->sticky_msg.clear();
+    if(c->perr_host) c->perr_host[0] = c->perr_host[1] = 0;
     if(c->D.L.dup_bins){
         CU(cudaMemsetAsync(c->tab128, 0, c->D.L.dup_bins * 16, c->stream));
         CU(cudaMemsetAsync(c->first64, 0xFF, c->D.L.dup_bins * 8, c->stream));
@@ -236,6 +241,10 @@ extern "C" int fqk_create(fqk_ctx** out, const fq_params* p, int device_ordinal,
     if(c->stats_cs_pe) cudaFuncSetAttribute(k_stats_pe, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 20 * (int)C * 4);
     fused_configure(prop);
     if(nranks > 1){
+        if(cudaMalloc(&c->m_flat, c->D.L.total_u64 * 8) != cudaSuccess || cudaMalloc(&c->m_status, 16) != cudaSuccess ||
+           (c->D.L.dup_bins && (cudaMalloc(&c->m_idx, c->D.L.dup_bins * 4) != cudaSuccess ||
+                                cudaMalloc(&c->m_first, c->D.L.dup_bins * 8) != cudaSuccess)))
+            return bail(FQK_E_NOMEM, "merge scratch alloc failed");
         if(!nccl::load()) return bail(FQK_E_NCCL, "libnccl.so.2 not found");
         nccl::UniqueId id; memcpy(&id, nccl_unique_id, sizeof(id));
         int e = nccl::CommInitRank(&c->comm, nranks, id, rank);
@@ -268,6 +277,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(int i = 0; i < 2; ++i){ c->aseq[i].release(); c->aqual[i].release(); c->asrc[i].release(); }
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
+    cudaFree(c->m_flat); cudaFree(c->m_idx); cudaFree(c->m_first); cudaFree(c->m_status);
     if(c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -384,14 +394,25 @@ static int launch_pe(fqk_ctx* c, const DevBatch& B1, const DevBatch& B2, fq_read
     return 0;
 }
 
+static int err_bits(uint32_t e, const char** msg){
+    if(e & 1){ *msg = "a read (or merged read) is longer than max_cycles"; return FQK_E_LIMIT; }
+    if(e & 2){ *msg = "batch is not dense/ordered/16-byte aligned (see fq_batch)"; return FQK_E_INVALID; }
+    if(e & 4){ *msg = "base outside {A,C,G,T,N} or quality >= 128 in an ASCII batch"; return FQK_E_ALPHABET; }
+    return 0;
+}
 static int check_err_flag(fqk_ctx* c){
     uint32_t e = 0;
     CU(cudaMemcpyAsync(&e, c->err, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if(e & 1) return fail(c, FQK_E_LIMIT, "a read (or merged read) is longer than max_cycles");
-    if(e & 2) return fail(c, FQK_E_INVALID, "batch offsets must be multiples of FQK_PAD");
-    if(e & 4) return fail(c, FQK_E_ALPHABET, "base outside {A,C,G,T,N} or quality >= 128 in an ASCII batch");
-    return 0;
+    const char* m = nullptr;
+    const int rc = err_bits(e, &m);
+    return rc ? fail(c, rc, m) : 0;
+}
+// error flag snapshot of a pipelined pack: the first one sticks to the context until fqk_reset
+static void note_pack_error(fqk_ctx* c, uint32_t e){
+    const char* m = nullptr;
+    const int rc = err_bits(e, &m);
+    if(rc && !c->sticky){ c->sticky = rc; c->sticky_msg = m; }
 }
 
 extern "C" int fqk_sync(fqk_ctx* c){
@@ -546,11 +567,14 @@ extern "C" int fqk_submit_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out
         CU(cudaHostAlloc((void**)&c->perr_host, 2 * sizeof(uint32_t), cudaHostAllocDefault));
         c->perr_host[0] = c->perr_host[1] = 0;
     }
-    const int s = (int)(c->submitted & 1);
-    *ticket = c->submitted++;
+    const uint64_t t = c->submitted;                                    // the ticket is handed out only when the pack is enqueued
+    const int s = (int)(t & 1);
     const size_t n = in->n_reads;
-    if(n == 0){ CU(cudaEventRecord(c->evD2H[s], c->d2h)); return 0; }
-    if(c->submitted > 2) CU(cudaEventSynchronize(c->evD2H[s]));        // the slot's previous pack has left the device
+    if(t >= 2){                                                         // the slot's previous pack has left the device
+        CU(cudaEventSynchronize(c->evD2H[s]));
+        note_pack_error(c, c->perr_host[s]);
+    }
+    if(n == 0){ CU(cudaEventRecord(c->evD2H[s], c->d2h)); *ticket = t; c->submitted = t + 1; return 0; }
     if(c->pres[s].ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
     CU(cudaStreamWaitEvent(c->h2d, c->evK[s], 0));                      // staging of this slot is free again
     int rc = stage(c, c->pst[s], in, c->h2d); if(rc) return rc;
@@ -562,19 +586,19 @@ extern "C" int fqk_submit_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out
     CU(cudaMemcpyAsync(out, c->pres[s].p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
     CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->d2h));
     CU(cudaEventRecord(c->evD2H[s], c->d2h));
+    *ticket = t; c->submitted = t + 1;
     return 0;
 }
 
 extern "C" int fqk_wait(fqk_ctx* c, uint64_t ticket){
     if(!c || ticket >= c->submitted) return FQK_E_INVALID;
-    if(ticket + 2 < c->submitted) return 0;                             // already recycled, hence complete
     CU(cudaSetDevice(c->device));
-    const int s = (int)(ticket & 1);
-    CU(cudaEventSynchronize(c->evD2H[s]));
-    const uint32_t e = c->perr_host[s];
-    if(e & 1) return fail(c, FQK_E_LIMIT, "a read (or merged read) is longer than max_cycles");
-    if(e & 2) return fail(c, FQK_E_INVALID, "batch is not dense/ordered/16-byte aligned (see fq_batch)");
-    return 0;
+    if(ticket + 2 >= c->submitted){                                     // not recycled yet: wait for its download
+        const int s = (int)(ticket & 1);
+        CU(cudaEventSynchronize(c->evD2H[s]));
+        note_pack_error(c, c->perr_host[s]);
+    }
+    return c->sticky ? fail(c, c->sticky, c->sticky_msg) : 0;           // sticky: an older pack's error is not lost either
 }
 
 extern "C" int fqk_process_pe(fqk_ctx* c, const fq_batch* r1, const fq_batch* r2, fq_read_result* o1,
@@ -613,39 +637,47 @@ __global__ void k_dup_mask(uint64_t bins, const unsigned long long* tab128, cons
         cnt[k] = keep ? c : 0; idx[k] = keep ? (uint32_t)hi : 0xFFFFFFFFu;
     }
 }
-__global__ void k_dup_join(uint64_t bins, unsigned long long* tab128, const unsigned long long* kmin,
-                           const uint32_t* cnt, const uint32_t* idx){
+// merged (kmer32 minimum, count, index of the first read carrying it, first read of the key) -> mDups / mCounts / mGC;
+// dups aliases kmin.  The local table (tab128, first64) is left untouched, so a later finalize merges it again correctly.
+__global__ void k_dup_finish_merged(uint64_t bins, unsigned long long* kmin_dups, const uint32_t* cnt, const uint32_t* idx,
+                                    const unsigned long long* first, uint8_t* gcs){
     for(uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < bins; k += (uint64_t)gridDim.x * blockDim.x){
-        tab128[2 * k] = cnt[k] ? kmin[k] : 0;
-        tab128[2 * k + 1] = ((unsigned long long)cnt[k] << 32) | idx[k];
+        const uint32_t c = cnt[k];
+        const unsigned long long f = first[k];
+        kmin_dups[k] = c ? kmin_dups[k] : 0ull;
+        gcs[k] = (c && (uint32_t)(f >> 8) == idx[k]) ? (uint8_t)(f & 0xFF) : 0;
     }
 }
 
-static int dup_finalize(fqk_ctx* c){
+// Every rank runs the same sequence of collectives or none of them (fqk_finalize agrees on that first), nothing is
+// allocated and no rank can leave between two all-reduces; launch and NCCL errors are collected and reported at the end.
+static int dup_finalize(fqk_ctx* c, bool collective = false){
     const uint64_t n = c->D.L.dup_bins;
-    if(!n || c->dup_final) return 0;
+    if(!n || (c->dup_final && !collective)) return 0;            // ranks must not disagree on whether the collectives run
     const int g = c->sms * 8;
     if(c->nranks > 1){
         // min over kmer32, then sum of the counts / min of the indices that carry the global minimum,
         // and min over the packed (first index, gc) word: 4 all-reduces, once per run
-        unsigned long long* kmin = (unsigned long long*)c->d_dups;       // reuse output arrays as scratch
-        uint32_t* cnt = c->d_counts; uint32_t* idx = nullptr;
-        CU(cudaMalloc(&idx, n * 4));
-        k_dup_split<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin);
-        int e = nccl::AllReduce(kmin, kmin, n, nccl::Uint64, nccl::Min, c->comm, c->stream);
-        k_dup_mask<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin, cnt, idx);
-        if(!e) e = nccl::AllReduce(cnt, cnt, n, nccl::Uint32, nccl::Sum, c->comm, c->stream);
-        if(!e) e = nccl::AllReduce(idx, idx, n, nccl::Uint32, nccl::Min, c->comm, c->stream);
-        if(!e) e = nccl::AllReduce(c->first64, c->first64, n, nccl::Uint64, nccl::Min, c->comm, c->stream);
-        k_dup_join<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin, cnt, idx);
+        unsigned long long* kmin = (unsigned long long*)c->d_dups;       // the output arrays double as merge buffers
+        uint32_t* cnt = c->d_counts; uint32_t* idx = c->m_idx;
+        int e = 0; cudaError_t ce = cudaSuccess;
+        auto chk = [&](){ cudaError_t x = cudaGetLastError(); if(ce == cudaSuccess) ce = x; };
+        k_dup_split<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin); chk();
+        { int x = nccl::AllReduce(kmin, kmin, n, nccl::Uint64, nccl::Min, c->comm, c->stream); if(!e) e = x; }
+        k_dup_mask<<<g, 256, 0, c->stream>>>(n, c->tab128, kmin, cnt, idx); chk();
+        { int x = nccl::AllReduce(cnt, cnt, n, nccl::Uint32, nccl::Sum, c->comm, c->stream); if(!e) e = x; }
+        { int x = nccl::AllReduce(idx, idx, n, nccl::Uint32, nccl::Min, c->comm, c->stream); if(!e) e = x; }
+        { int x = nccl::AllReduce(c->first64, c->m_first, n, nccl::Uint64, nccl::Min, c->comm, c->stream); if(!e) e = x; }
+        k_dup_finish_merged<<<g, 256, 0, c->stream>>>(n, kmin, cnt, idx, c->m_first, c->d_gc); chk();
         c->launches += 3;
-        cudaStreamSynchronize(c->stream);
-        cudaFree(idx);
+        { cudaError_t x = cudaStreamSynchronize(c->stream); if(ce == cudaSuccess) ce = x; }
         if(e) return fail(c, FQK_E_NCCL, "ncclAllReduce (dup table) failed");
+        if(ce != cudaSuccess) return fail(c, FQK_E_CUDA, std::string("dup table merge: ") + cudaGetErrorString(ce));
+    }else{
+        k_dup_finish<<<g, 256, 0, c->stream>>>(n, c->tab128, c->first64, c->d_dups, c->d_counts, c->d_gc);
+        c->launches++;
+        CU(cudaGetLastError());
     }
-    k_dup_finish<<<g, 256, 0, c->stream>>>(n, c->tab128, c->first64, c->d_dups, c->d_counts, c->d_gc);
-    c->launches++;
-    CU(cudaGetLastError());
     c->dup_final = true;
     return 0;
 }
@@ -653,22 +685,35 @@ static int dup_finalize(fqk_ctx* c){
 extern "C" int fqk_finalize(fqk_ctx* c, uint64_t* flat){
     if(!c || !flat) return FQK_E_INVALID;
     CU(cudaSetDevice(c->device));
-    int rc = check_err_flag(c); if(rc) return rc;
+    int rc = c->sticky ? fail(c, c->sticky, c->sticky_msg) : check_err_flag(c);
     const size_t n = c->D.L.total_u64;
     if(c->nranks > 1){
+        // Agree first: one all-reduce(max) of a status word.  A rank whose shard failed (over-length read, bad batch)
+        // must not leave the others blocked inside ncclAllReduce: either every rank runs all collectives or none does.
+        uint32_t st = rc ? 1u : 0u, gst = 1u;
+        int e = 0;
+        cudaError_t ce = cudaMemcpyAsync(c->m_status, &st, 4, cudaMemcpyHostToDevice, c->stream);
+        if(ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);      // st is a stack variable
+        e = nccl::AllReduce(c->m_status, c->m_status + 1, 1, nccl::Uint32, nccl::Max, c->comm, c->stream);
+        if(ce == cudaSuccess) ce = cudaMemcpyAsync(&gst, c->m_status + 1, 4, cudaMemcpyDeviceToHost, c->stream);
+        if(ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
+        if(rc) return rc;
+        if(e) return fail(c, FQK_E_NCCL, "ncclAllReduce (status) failed");
+        if(ce != cudaSuccess) return fail(c, FQK_E_CUDA, std::string("finalize: ") + cudaGetErrorString(ce));
+        if(gst) return fail(c, FQK_E_INVALID, "another rank reported an error: the run-level merge was skipped on every rank");
         // Stats::merge / FilterResult::merge are plain sums: one all-reduce of the flat buffer.
         // The result is left in a scratch copy so that finalize can be called again.
-        uint64_t* tmp = nullptr;
-        CU(cudaMalloc(&tmp, n * 8));
-        int e = nccl::AllReduce(c->flat, tmp, n, nccl::Uint64, nccl::Sum, c->comm, c->stream);
-        if(e){ cudaFree(tmp); return fail(c, FQK_E_NCCL, "ncclAllReduce (stats) failed"); }
-        cudaMemcpyAsync(flat, tmp, n * 8, cudaMemcpyDeviceToHost, c->stream);
-        cudaStreamSynchronize(c->stream);
-        cudaFree(tmp);
-    }else{
-        CU(cudaMemcpyAsync(flat, c->flat, n * 8, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        e = nccl::AllReduce(c->flat, c->m_flat, n, nccl::Uint64, nccl::Sum, c->comm, c->stream);
+        ce = cudaMemcpyAsync(flat, c->m_flat, n * 8, cudaMemcpyDeviceToHost, c->stream);
+        { cudaError_t x = cudaStreamSynchronize(c->stream); if(ce == cudaSuccess) ce = x; }
+        const int rd = dup_finalize(c, true);                                  // runs on every rank whatever happened above
+        if(e) return fail(c, FQK_E_NCCL, "ncclAllReduce (stats) failed");
+        if(ce != cudaSuccess) return fail(c, FQK_E_CUDA, std::string("finalize: ") + cudaGetErrorString(ce));
+        return rd;
     }
+    if(rc) return rc;
+    CU(cudaMemcpyAsync(flat, c->flat, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     return dup_finalize(c);
 }
 
@@ -677,6 +722,7 @@ extern "C" int fqk_dup_table(fqk_ctx* c, uint64_t* dups, uint32_t* counts, uint8
     const uint64_t n = c->D.L.dup_bins;
     if(!n) return fail(c, FQK_E_INVALID, "duplication analysis is not enabled");
     CU(cudaSetDevice(c->device));
+    if(c->nranks > 1 && !c->dup_final) return fail(c, FQK_E_INVALID, "call fqk_finalize first: the cross-rank merge is collective");
     int rc = dup_finalize(c); if(rc) return rc;
     if(dups) CU(cudaMemcpyAsync(dups, c->d_dups, n * 8, cudaMemcpyDeviceToHost, c->stream));
     if(counts) CU(cudaMemcpyAsync(counts, c->d_counts, n * 4, cudaMemcpyDeviceToHost, c->stream));

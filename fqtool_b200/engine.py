@@ -62,10 +62,11 @@ class Engine:
 
     @staticmethod
     def _ascii(reads, first_index):
-        seq, qual, off = (np.ascontiguousarray(x) for x in reads)
+        seq, qual = np.ascontiguousarray(reads[0]), np.ascontiguousarray(reads[1])
+        off = np.ascontiguousarray(reads[2], dtype=np.uint64)      # converted ONCE; the caller keeps this array alive
         b = abi.FqAsciiBatch()
         b.n_reads = len(off) - 1; b.first_index = first_index
-        b.off, b.seq, b.qual = abi.ptr(off.astype(np.uint64, copy=False)), abi.ptr(seq), abi.ptr(qual)
+        b.off, b.seq, b.qual = abi.ptr(off), abi.ptr(seq), abi.ptr(qual)
         return b, (seq, qual, off)
 
     def process_se_ascii(self, reads, first_index=0):

@@ -27,6 +27,9 @@ CONFIGS = {
                  desc="synthetic SE 100bp, explicit adapter, polyX, duplication key 12, k-mer 6"),
     "cfg5": dict(paired=True, L=250, model=SYNTH_PE_NOVASEQ, seed=20261104, frag=(420.0, 120.0), reads=1_000_000_000,
                  cli="-q -g -a", desc="synthetic PE 2x250bp 1B pairs sharded across GPUs"),
+    # not a BASELINE config: small paired stream with the duplication table and k-mers on, for bench.py's merge check
+    "pe_dup": dict(paired=True, L=150, model=SYNTH_PE_NOVASEQ, seed=20261105, frag=(260.0, 80.0), reads=1_000_000,
+                   cli="-d --kmer --kmer_length 5 -q -F 2 -T 3 -f 1", desc="synthetic PE 2x150bp, duplication + k-mer 5 (merge check)"),
 }
 
 

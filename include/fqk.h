@@ -268,7 +268,9 @@ int  fqk_process_pe_ascii(fqk_ctx* ctx, const fq_ascii_batch* r1, const fq_ascii
  * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's
  * records are in `out`.  The upload of pack k+1 overlaps the kernels and the download of pack k.
  * Buffers of a pack (pinned host memory) must stay valid until its fqk_wait returns.  Do not mix
- * with fqk_process_se on the same context without waiting for every ticket first.
+ * with fqk_process_se on the same context without waiting for every ticket first.  A ticket is handed out only when the
+ * pack was enqueued (a failed fqk_submit_se consumes none).  The first error of any pack sticks to the context: every
+ * later fqk_wait (also for tickets already recycled) and fqk_finalize return it until fqk_reset.
  */
 int  fqk_submit_se(fqk_ctx* ctx, const fq_batch* in, fq_read_result* out, uint64_t* ticket);
 int  fqk_wait(fqk_ctx* ctx, uint64_t ticket);
@@ -278,6 +280,10 @@ int  fqk_wait(fqk_ctx* ctx, uint64_t ticket);
  * context's GPU, fq_batch itself is a host struct): kernels only, launched on
  * the context's stream without synchronising.  fqk_sync waits for them.
  */
+/* With correction_enabled (-c) fqk_process_pe_device REWRITES the bases and qualities of the caller's device
+ * buffers in place (BaseCorrector::correctByOverlapAnalysis mutates the Read objects too, src/basecorrector.cpp:14-70);
+ * the fq_batch pointers are const only for the other option sets.  A resident batch must therefore not be processed
+ * twice with -c: the second pass would see corrected data.  The host entry points work on their own staged copy. */
 int  fqk_process_se_device(fqk_ctx* ctx, const fq_batch* in_dev, fq_read_result* out_dev);
 int  fqk_process_pe_device(fqk_ctx* ctx, const fq_batch* r1_dev, const fq_batch* r2_dev,
                            fq_read_result* out1_dev, fq_read_result* out2_dev,
@@ -314,7 +320,12 @@ int  fqk_reset(fqk_ctx* ctx);
 /*
  * End of run: merge accumulators over ranks (one NCCL all-reduce of the flat
  * buffer; min/sum passes for the duplication table) and copy them to the host.
- * flat has fq_stats_layout.total_u64 entries.
+ * flat has fq_stats_layout.total_u64 entries.  With nranks > 1 the call is COLLECTIVE: every rank must call it the
+ * same number of times.  The ranks first agree (one all-reduce(max) of a status word) on whether every shard is
+ * error-free; if one is not, every rank skips the merge and returns an error (its own, or FQK_E_INVALID "another rank
+ * reported an error"), so a bad read on one shard cannot leave the other ranks blocked inside NCCL.  The local
+ * accumulators and the local duplication table are not modified by the merge: processing may continue and a later
+ * fqk_finalize merges again.  fqk_dup_table returns the table of the last fqk_finalize.
  */
 int  fqk_finalize(fqk_ctx* ctx, uint64_t* flat);
 /* Duplicate::mDups / mCounts / mGC (src/duplicate.h:64-66) after fqk_finalize;

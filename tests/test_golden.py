@@ -22,7 +22,7 @@ def test_oracle_port_matches_golden(path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("impl", [0, 1, 2, 3], ids=["auto", "generic", "fused_single_role", "fused_ws"])
+@pytest.mark.parametrize("impl", [0, 1, 3], ids=["auto", "generic", "fused_ws"])
 @pytest.mark.parametrize("path", FILES, ids=IDS)
 def test_cuda_matches_golden(path, impl):
     g = util.load_golden(path)

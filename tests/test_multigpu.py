@@ -71,3 +71,50 @@ def test_nccl_merge(cfg, paired):
         if dup is not None:
             for a, b in zip(dup, o.dup_table()):
                 assert np.array_equal(a, b), f"rank {rank}"
+
+
+def _worker_err(rank, world, port, q):
+    """rank 1's shard holds a read longer than max_cycles: every rank must come back from fqk_finalize with an error."""
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fqtool_b200.engine import Engine, FqkError
+    uid = [Engine.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, 0)
+    opt = configs.options("cfg2", max_cycles=128)
+    reads = synth.se_hiseq(2000, 150 if rank == 1 else 100, seed=11 + rank)
+    e = Engine(opt.to_params(), device=rank, rank=rank, nranks=world, nccl_unique_id=uid[0])
+    msgs = []
+    try:
+        e.process_se(batch.pack(reads, rank * 2000))
+    except FqkError as ex:
+        msgs.append("process: " + str(ex))
+    try:
+        e.finalize()
+        msgs.append("finalize: ok")
+    except FqkError as ex:
+        msgs.append("finalize: " + str(ex))
+    q.put((rank, msgs))
+    dist.barrier()
+    e.close()
+    dist.destroy_process_group()
+
+
+def test_error_on_one_shard_does_not_hang():
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31600 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker_err, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert any("longer than max_cycles" in m for m in outs[1])
+    assert outs[1][-1].startswith("finalize: fqk_finalize rc=")
+    assert "another rank reported an error" in outs[0][-1]
