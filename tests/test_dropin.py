@@ -1,0 +1,88 @@
+"""The literal drop-in: the reference's own program with the bodies of
+SingleEndProcessor::processSingleEnd / PairEndProcessor::processPairEnd replaced by calls into libfqk.so
+(integration/, built as oracle/_ref/fqtool_fqk by `make -C oracle dropin`) against the unmodified reference program
+(oracle/_ref/fqtool_ref -w 1) on the reference's own test data: every output file byte-identical and report.json
+identical except for the "Software" block (command line and working directory).  That compares, through
+JsonReporter (src/jsonreporter.cpp:23-162), everything the hot path feeds: summary counts, filter result counters,
+adapter-text maps, polyX tallies, duplication rate/histogram/mean GC, insert-size histogram and peak, the per-cycle
+quality/content curves and the k-mer table of all four Stats objects."""
+import json
+import os
+import subprocess
+
+import pytest
+
+from tests.golden import make_e2e
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.path.join(ROOT, "oracle", "_ref", "fqtool_ref")
+FQK = os.path.join(ROOT, "oracle", "_ref", "fqtool_fqk")
+FQ1 = os.path.join(HERE, "golden", "fq", "r1.fq.gz")
+FQ2 = os.path.join(HERE, "golden", "fq", "r2.fq.gz")
+
+EXTRA = {
+    # option sets beyond tests/golden/make_e2e.py: duplication + k-mers on pairs, explicit adapters + polyX on pairs
+    "pe_dup_kmer": (True, "-d --kmer --kmer_length 5 -q -F 2 -T 3 -f 1"),
+    "pe_adapters_polyx": (True, f"-a --adapter_of_read1 {make_e2e.A1} --adapter_of_read2 {make_e2e.A2} -x -q --enable_cut_front --enable_cut_tail -B 120 -b 130"),
+    "se_polyg_polyx": (False, "-g --min_len_detect_polyG 6 -x --base_to_trim AGN --min_len_detect_polyX 5 -q"),
+    "cfg5": (True, "-q -g -a"),
+}
+CASES = dict(make_e2e.CASES, **EXTRA)
+
+
+def _have():
+    return os.path.exists(REF) and os.path.exists(FQK)
+
+
+def test_seam_generator_anchors():
+    """make_seam.py finds each anchor exactly once in the reference's sources (when they are present)."""
+    if not os.path.isdir("/root/reference/src"):
+        pytest.skip("reference sources absent")
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        r = subprocess.run(["python", os.path.join(ROOT, "integration", "make_seam.py"), "/root/reference/src", d],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        for f in ("seprocessor_fqk.cpp", "peprocessor_fqk.cpp"):
+            t = open(os.path.join(d, f)).read()
+            assert "fqkseam::finish" in t and "_body.inc" in t
+            assert "trimAndCut" not in t and "statRead" not in t.split("Stats::merge")[0].split("_body.inc")[-1]
+
+
+def test_dropin_binary_links_against_libfqk():
+    if not _have():
+        pytest.skip("drop-in binaries not built (reference sources absent)")
+    r = subprocess.run(["ldd", FQK], capture_output=True, text=True)
+    assert "libfqk.so" in r.stdout and "not found" not in r.stdout
+
+
+def _run(exe, case, d, pack):
+    paired, flags = CASES[case]
+    os.makedirs(d, exist_ok=True)
+    make_e2e.CASES.setdefault(case, CASES[case])
+    cmd = make_e2e.command(exe, case, FQ1, FQ2, d) + ["-w", "1", "-J", os.path.join(d, "report.json"),
+                                                       "-H", os.path.join(d, "report.html"), "--max_item_in_pack", str(pack)]
+    r = subprocess.run(cmd, capture_output=True, text=True, cwd=d)
+    assert r.returncode == 0, f"{' '.join(cmd)}\n{r.stdout}\n{r.stderr}"
+    return r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_dropin_matches_reference_program(case, tmp_path):
+    if not _have():
+        pytest.skip("drop-in binaries not built (reference sources absent)")
+    dr, dg = str(tmp_path / "ref"), str(tmp_path / "fqk")
+    _run(REF, case, dr, 700)
+    _run(FQK, case, dg, 700)
+    names = sorted(f for f in os.listdir(dr) if f.endswith(".fq"))
+    assert names, "the reference wrote no output"
+    for f in names:
+        a, b = open(os.path.join(dr, f), "rb").read(), open(os.path.join(dg, f), "rb").read()
+        assert a == b, f"{case}: {f} differs ({len(a)} vs {len(b)} bytes)"
+    ja, jb = json.load(open(os.path.join(dr, "report.json"))), json.load(open(os.path.join(dg, "report.json")))
+    ja.pop("Software"); jb.pop("Software")
+    for k in ja:
+        assert ja[k] == jb.get(k), f"{case}: report.json section {k} differs"
+    assert set(ja) == set(jb)

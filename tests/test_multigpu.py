@@ -115,6 +115,6 @@ def test_error_on_one_shard_does_not_hang():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert any("longer than max_cycles" in m for m in outs[1])
-    assert outs[1][-1].startswith("finalize: fqk_finalize rc=")
-    assert "another rank reported an error" in outs[0][-1]
+    assert outs[1][0].startswith("process: fqk_process_se rc="), outs          # the shard with the over-length read fails ...
+    assert outs[1][-1].startswith("finalize: fqk_finalize rc="), outs          # ... keeps failing in finalize ...
+    assert "another rank reported an error" in outs[0][-1], outs               # ... and the healthy rank is told so instead of hanging
