@@ -83,6 +83,11 @@ def test_dropin_matches_reference_program(case, tmp_path):
         assert a == b, f"{case}: {f} differs ({len(a)} vs {len(b)} bytes)"
     ja, jb = json.load(open(os.path.join(dr, "report.json"))), json.load(open(os.path.join(dg, "report.json")))
     ja.pop("Software"); jb.pop("Software")
+    if not CASES[case][0] and "Duplication" in ja:
+        # SingleEndProcessor::process zeroes dupHist with sizeof(int) * histSize (src/seprocessor.cpp:244-245): the upper
+        # half of the size_t array is uninitialised heap in the reference itself, so only the lower half is comparable
+        for j in (ja, jb):
+            j["Duplication"]["Histogram"] = j["Duplication"]["Histogram"][:len(j["Duplication"]["Histogram"]) // 2]
     for k in ja:
         assert ja[k] == jb.get(k), f"{case}: report.json section {k} differs"
     assert set(ja) == set(jb)
