@@ -759,7 +759,8 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_pe_v4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<true>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<false>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -871,7 +872,11 @@ int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_re
     ppb = (ppb + p.T - 1) / p.T * p.T;
     const int grid = (int)((B1.n + ppb - 1) / ppb);
     static const int dbg = getenv("FQK_V4_DEBUG") ? atoi(getenv("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
-    k_pe_v4<<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    static const bool nolean = getenv("FQK_V4_GENERIC") != nullptr;       // A/B switch: the general code for every option set
+    if(v4_lean_options(D.P) && !nolean)
+        k_pe_v4<V4Spec<false>><<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    else
+        k_pe_v4<V4Spec<true>><<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
     if(dbg & 256){                                         // section clocks of the trim warps (see V4_PROF)
         unsigned long long h[16];
         cudaStreamSynchronize(st);

@@ -47,6 +47,18 @@ __device__ unsigned long long g_v4prof[16];
 #define V4_PROF0(on)
 #define V4_PROFC(on, k)
 #endif
+// Option specialisation.  V4Spec<true> is the general code.  V4Spec<false> is compiled for option sets WITHOUT forced
+// trims, sliding-window cuts, polyX, adapter-by-sequence, complexity filter, average-quality limit and max-length trims
+// (the BASELINE configurations cfg3 and cfg5): those statements and the helpers behind them vanish from the kernel, and
+// every read keeps start == 0.  The trim role is bound by instruction fetch (the code a warp walks per chunk is larger
+// than the instruction cache, profiles/r02_pe_v4_notes.md), so smaller code is faster code here.
+template<bool GENERIC> struct V4Spec { static constexpr bool generic = GENERIC; };
+inline bool v4_lean_options(const fq_params& P){
+    return !P.trim_front1 && !P.trim_tail1 && !P.trim_front2 && !P.trim_tail2 && !P.trim_max_len1 && !P.trim_max_len2 &&
+           !P.cut_front_enabled && !P.cut_tail_enabled && !P.cut_right_enabled && !P.polyx_enabled &&
+           !(P.adapter_trim_enabled && (P.adapter_r1_len > 0 || P.adapter_r2_len > 0)) && !P.complexity_enabled &&
+           !(P.average_quality_limit > 0);
+}
 constexpr int V4_TAILMAX = 8;                 // cut-off tails up to this many bases are handled by the trim warps
 constexpr int V4_MAXLEN = 496;                // reads up to this length: one packed word per lane
 
@@ -129,12 +141,13 @@ __device__ V4_IN uint32_t v4_trim_and_cut(const fq_params* P, uint32_t qa, int l
 
 // Filter::passFilter's counts (src/filter.cpp:15-25) of the current view: the sweep of the raw read minus what the
 // trims removed; the exact range scan when the average-quality test needs the sum
+template<class SP>
 __device__ __forceinline__ void v4_view_counts(const fq_params& P, const PeRead& R, int& lowq, int& nn, int& total){
     total = 0;
-    if(P.average_quality_limit > 0){ swar_counts(R.qa, R.start, R.len, P.low_quality_limit, true, lowq, nn, total); return; }
+    if(SP::generic && P.average_quality_limit > 0){ swar_counts(R.qa, R.start, R.len, P.low_quality_limit, true, lowq, nn, total); return; }
     lowq = R.rawlen - (int)(R.ge >> 7);
     nn = R.nmask ? n_count(R.qa, R.rawlen, R.nmask) : 0;
-    if(R.start > 0){ int l1, n1; range_counts(R.qa, 0, R.start, P.low_quality_limit, l1, n1); lowq -= l1; nn -= n1; }
+    if(SP::generic && R.start > 0){ int l1, n1; range_counts(R.qa, 0, R.start, P.low_quality_limit, l1, n1); lowq -= l1; nn -= n1; }
     const int e = R.start + R.len;
     if(e < R.rawlen){ int l2, n2; range_counts(R.qa, e, R.rawlen - e, P.low_quality_limit, l2, n2); lowq -= l2; nn -= n2; }
 }
@@ -142,25 +155,28 @@ __device__ __forceinline__ ReadView v4_view(const PeRead& R){
     ReadView v; v.q = smem_ptr(R.qa); v.b2 = smem_ptr(R.ba); v.start = R.start; v.len = R.len; return v;
 }
 // Filter::passFilter of the current view (same decisions as pass_filter_fast, fqk_pe.cuh)
+template<class SP>
 __device__ V4_NI int v4_pass_filter_ni(const fq_params* Pp, uint32_t qa, uint32_t ba, int rawlen, int start, int len, uint32_t ge, uint32_t nmask, bool isnull){
     const fq_params& P = *Pp;
     PeRead R; R.qa = qa; R.ba = ba; R.doff = 0; R.rawlen = rawlen; R.start = start; R.len = len; R.ge = ge; R.nmask = nmask;
     if(isnull || R.len == 0) return FQK_FAIL_LENGTH;
-    if(P.complexity_enabled) return dev_pass_filter_view(P, v4_view(R), false);
+    if(SP::generic && P.complexity_enabled) return dev_pass_filter_view(P, v4_view(R), false);
     if(!P.qual_filter_enabled && !P.length_filter_enabled) return FQK_PASS_FILTER;
     int lowq = 0, nn = 0, total = 0;
-    if(P.qual_filter_enabled) v4_view_counts(P, R, lowq, nn, total);
+    if(P.qual_filter_enabled) v4_view_counts<SP>(P, R, lowq, nn, total);
     return filter_from_counts(P, R.len, lowq, nn, total);
 }
+template<class SP>
 __device__ __forceinline__ int v4_pass_filter(const fq_params& P, const PeRead& R, bool isnull){
-    return v4_pass_filter_ni(&P, R.qa, R.ba, R.rawlen, R.start, R.len, R.ge, R.nmask, isnull);
+    return v4_pass_filter_ni<SP>(&P, R.qa, R.ba, R.rawlen, SP::generic ? R.start : 0, R.len, R.ge, R.nmask, isnull);
 }
 // passFilter of the merged read (OverlapAnalysis::merge, src/overlapanalysis.cpp:74-93): read1's first len1 bases + the
 // last len2 bases of revcomp(read2's view)
+template<class SP>
 __device__ V4_NI int v4_merged_filter(const fq_params* Pp, uint32_t aqa, uint32_t aba, int astart, int alen,
                                              uint32_t bqa, uint32_t bba, int bstart, int blen, int ol, int len1, int len2){
     const fq_params& P = *Pp;
-    if(P.complexity_enabled){
+    if(SP::generic && P.complexity_enabled){
         ReadView va; va.q = smem_ptr(aqa); va.b2 = smem_ptr(aba); va.start = astart; va.len = alen;
         ReadView vb; vb.q = smem_ptr(bqa); vb.b2 = smem_ptr(bba); vb.start = bstart; vb.len = blen;
         return dev_pass_filter(P, len1 + len2, false, [&](int t, int& c, int& q){
@@ -171,7 +187,7 @@ __device__ V4_NI int v4_merged_filter(const fq_params* Pp, uint32_t aqa, uint32_
     // counts of the merged read = read1 prefix + the part of read2 that is appended (order is irrelevant)
     int l1 = 0, n1 = 0, t1 = 0, l2 = 0, n2 = 0, t2 = 0;
     if(P.qual_filter_enabled){
-        const bool wt = P.average_quality_limit > 0;
+        const bool wt = SP::generic && P.average_quality_limit > 0;
         swar_counts(aqa, astart, len1, P.low_quality_limit, wt, l1, n1, t1);
         swar_counts(bqa, bstart + (blen - ol - len2), len2, P.low_quality_limit, wt, l2, n2, t2);
     }
@@ -549,6 +565,7 @@ __device__ V4_NI void v4_tail_sub(bool td, uint32_t Rqa, uint32_t Rba, int Rrawl
 
 // The loop body of PairEndProcessor::processPairEnd (src/peprocessor.cpp:292-429, threadId 0) for pairs
 // 32j .. 32j+31 of a staged tile, lane = pair; same statements as k_trim_pe (fqk_kernels.cu).
+template<class SP>
 __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally& tl){
     const DevParams& D = *X.D;
     const fq_params& P = D.P;
@@ -579,7 +596,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         const uint2 sw = v4_sweep(r.qa, (int)dlen, P.qual_filter_enabled != 0, (uint32_t)P.low_quality_limit * 0x01010101u, lane);
         r.ge = sw.x; r.nmask = sw.y;
         bool alive = false;
-        if(valid){
+        if(!SP::generic) alive = valid;                             // Filter::trimAndCut returns the read itself (src/filter.cpp:70-73)
+        else if(valid){
             const uint32_t c = v4_trim_and_cut(&P, r.qa, r.rawlen, m ? P.trim_front2 : P.trim_front1, m ? P.trim_tail2 : P.trim_tail1);
             alive = (c >> 31) != 0u; r.len = (int)(c & 0xFFFu); r.start = (int)((c >> 12) & 0xFFFu);
         }
@@ -636,7 +654,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             rec2.flags |= FQK_F_ADAPTER_OV; rec2.adapter_pos = (int16_t)ov.len; rec2.adapter_len = (uint16_t)t2;
             tl.adapter_reads += 2; tl.adapter_bases += (uint32_t)(t1 + t2);     // filterresult.cpp:159-161
             modified = true;
-        }else{
+        }else if(SP::generic){
             if(P.adapter_r1_len > 0){
                 fq_read_result rt = {}; Tally tt = {};
                 const int v = v4_adapter_seq(&D, a.qa, a.ba, a.start, a.len, 0, &rt, &tt);
@@ -649,7 +667,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             }
         }
     }
-    if(both && P.polyx_enabled){
+    if(SP::generic && both && P.polyx_enabled){
         const int l1 = a.len, l2 = b.len;
 #pragma unroll 1
         for(int m = 0; m < 2; ++m){
@@ -659,7 +677,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         }
         modified |= (a.len != l1) | (b.len != l2);
     }
-    if(both){
+    if(SP::generic && both){
         if(P.trim_max_len1 > 0 && P.trim_max_len1 < a.len){ a.len = P.trim_max_len1; modified = true; }
         if(P.trim_max_len2 > 0 && P.trim_max_len2 < b.len){ b.len = P.trim_max_len2; modified = true; }
     }
@@ -683,7 +701,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
                 const int len1 = ov2.len + max(0, ov2.offset);
                 const int len2 = ov2.offset > 0 ? b.len - ov2.len : 0;
                 pr.merge_len1 = (uint16_t)len1; pr.merge_len2 = (uint16_t)len2;
-                result = v4_merged_filter(&P, a.qa, a.ba, a.start, a.len, b.qa, b.ba, b.start, b.len, ov2.len, len1, len2);
+                result = v4_merged_filter<SP>(&P, a.qa, a.ba, a.start, a.len, b.qa, b.ba, b.start, b.len, ov2.len, len1, len2);
                 if(result == FQK_PASS_FILTER){ pr.flags |= FQK_P_MERGED; merged = true; }
             }
             fcA = result; fnA = 2;                                  // :358
@@ -691,15 +709,15 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
             res1 = res2 = result;
             merge_processed = true;
         }else if(!P.merge_discard_unmerged){
-            res1 = v4_pass_filter(P, a, false); fcA = res1; fnA = 1;
-            res2 = v4_pass_filter(P, b, false); fcB = res2; fnB = 1;
+            res1 = v4_pass_filter<SP>(P, a, false); fcA = res1; fnA = 1;
+            res2 = v4_pass_filter<SP>(P, b, false); fcB = res2; fnB = 1;
             merge_processed = true;
         }
         if(merge_processed) pr.flags |= FQK_P_MERGE_PROC;
     }
     if(valid && !merge_processed){
-        res1 = v4_pass_filter(P, a, !a1);
-        res2 = v4_pass_filter(P, b, !a2);
+        res1 = v4_pass_filter<SP>(P, a, !a1);
+        res2 = v4_pass_filter<SP>(P, b, !a2);
         fcA = max(res1, res2); fnA = 2;                             // :390, mPaired == true
     }
     V4_GSYNC(X);
@@ -726,7 +744,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         const fq_read_result& rm = m ? rec2 : rec1;
         const uint32_t C = m ? L.Cr : L.Cm;                       // cycles of post1 / post2
         const uint32_t dlen = (uint32_t)Rm.rawlen;
-        bool own = false; uint32_t ostart = rm.start, olen = rm.len, hlen = rm.len;
+        bool own = false; uint32_t ostart = SP::generic ? rm.start : 0u, olen = rm.len, hlen = rm.len;
         if(both){                                                   // src/peprocessor.cpp:353-429
             if(!P.merge_enabled) own = res1 == FQK_PASS_FILTER && res2 == FQK_PASS_FILTER;
             else if(pr.flags & FQK_P_OV2_OVERLAP){
@@ -805,6 +823,7 @@ __device__ __forceinline__ void quad_drain_ab(QuadAcc& A, uint32_t* smA, int CA,
 
 // Named barriers: ids 1..NS tile ready (CH trim-warp arrivals + the statistics warps), NS+1..2NS stage free (the
 // statistics warps arrive, the producer warp waits); `full` (bulk copies landed) is an mbarrier with a transaction count.
+template<class SP>
 __global__ void __launch_bounds__(V4_THREADS, 1)
 k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_result* __restrict__ out1,
         fq_read_result* __restrict__ out2, fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
@@ -948,7 +967,7 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
                 V4_PROF(dbg & 256, 10);
                 const uint32_t t0 = lo + (uint32_t)k * T;
                 X.out1 = out1 + t0; X.out2 = out2 + t0; X.outp = outp + t0;
-                if((gs || 32 * j < X.nt) && !(dbg & 1)) v4_chunk(X, j, lane, tl);
+                if((gs || 32 * j < X.nt) && !(dbg & 1)) v4_chunk<SP>(X, j, lane, tl);
                 V4_PROF(dbg & 256, 11);
                 __syncwarp();
                 __threadfence_block();
