@@ -759,8 +759,10 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_pe_v4<V4Spec<true>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
-    cudaFuncSetAttribute(k_pe_v4<V4Spec<false>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<false>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
 }
 
 bool fused_supported_se(const DevParams& D, const DevBatch& B){
@@ -861,22 +863,41 @@ bool pe4_supported(const DevParams& D, const DevBatch& B1, const DevBatch& B2){
         reinterpret_cast<uintptr_t>(B1.lengths) | reinterpret_cast<uintptr_t>(B2.qual) | reinterpret_cast<uintptr_t>(B2.bases2) |
         reinterpret_cast<uintptr_t>(B2.offsets) | reinterpret_cast<uintptr_t>(B2.lengths)) & 15) return false;   // bulk copies: 16-byte aligned sources
     if(B1.total % FQK_BATCH_PAD || B2.total % FQK_BATCH_PAD) return false;
-    return v4_plan(D, pe4_maxlen(B1, B2), g_smem_optin).ok;
+    const int ml = pe4_maxlen(B1, B2);
+    return v4_plan(D, ml, g_smem_optin, 0).ok && v4_plan(D, ml, g_smem_optin, 1).ok;
+}
+// pairs per block: an equal share per SM, a whole number of tiles
+static int pe4_ppb(uint32_t n, int sms, int T){
+    int ppb = (int)((n + sms - 1) / sms);
+    ppb = std::min(ppb, 1 << 23);                          // 32-bit per-block sums of quality characters
+    return (ppb + T - 1) / T * T;
 }
 int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_read_result* o1, fq_read_result* o2,
                fq_pair_result* op, uint64_t* flat, int sms, cudaStream_t st){
-    const V4Plan p = v4_plan(D, pe4_maxlen(B1, B2), g_smem_optin);
-    if(!p.ok) return -1;
-    int ppb = (int)((B1.n + sms - 1) / sms);
-    ppb = std::min(ppb, 1 << 23);                          // 32-bit per-block sums of quality characters
-    ppb = (ppb + p.T - 1) / p.T * p.T;
-    const int grid = (int)((B1.n + ppb - 1) / ppb);
     static const int dbg = getenv("FQK_V4_DEBUG") ? atoi(getenv("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
+    static const bool fusedOnly = getenv("FQK_V4_SPLIT") && atoi(getenv("FQK_V4_SPLIT")) == 0;   // A/B switch: the one-kernel form
     static const bool nolean = getenv("FQK_V4_GENERIC") != nullptr;       // A/B switch: the general code for every option set
-    if(v4_lean_options(D.P) && !nolean)
-        k_pe_v4<V4Spec<false>><<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
-    else
-        k_pe_v4<V4Spec<true>><<<grid, V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    const int ml = pe4_maxlen(B1, B2);
+    V4Plan p = v4_plan(D, ml, g_smem_optin, 0);
+    if(!p.ok) return -1;
+    int nl = 1;
+    if(fusedOnly){
+        const int ppb = pe4_ppb(B1.n, sms, p.T);
+        k_pe_v4<V4Spec<true>, 0><<<(int)((B1.n + ppb - 1) / ppb), V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb, dbg);
+    }else{
+        // split path: the trim kernel writes the records, the statistics kernel reads them back
+        const V4Plan q = v4_plan(D, ml, g_smem_optin, 1);
+        if(!q.ok) return -1;
+        const int ppb1 = pe4_ppb(B1.n, sms, q.T), grid1 = (int)((B1.n + ppb1 - 1) / ppb1);
+        if(v4_lean_options(D.P) && !nolean)
+            k_pe_v4<V4Spec<false>, 1><<<grid1, V4_THREADS, q.smem, st>>>(D, B1, B2, o1, o2, op, flat, q.Wr, q.Wm, q.T, q.NS, ppb1, dbg);
+        else
+            k_pe_v4<V4Spec<true>, 1><<<grid1, V4_THREADS, q.smem, st>>>(D, B1, B2, o1, o2, op, flat, q.Wr, q.Wm, q.T, q.NS, ppb1, dbg);
+        const int ppb2 = pe4_ppb(B1.n, sms, p.T);
+        k_pe_v4<V4Spec<true>, 2><<<(int)((B1.n + ppb2 - 1) / ppb2), V4_THREADS, p.smem, st>>>(D, B1, B2, o1, o2, op, flat, p.Wr, p.Wm, p.T, p.NS, ppb2, dbg & ~256);
+        nl = 2;
+        if(dbg & 256) p = q;
+    }
     if(dbg & 256){                                         // section clocks of the trim warps (see V4_PROF)
         unsigned long long h[16];
         cudaStreamSynchronize(st);
@@ -887,5 +908,5 @@ int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_re
         static const unsigned long long z[16] = {};
         cudaMemcpyToSymbol(g_v4prof, z, sizeof(z));
     }
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    return cudaGetLastError() == cudaSuccess ? nl : -1;
 }

@@ -70,11 +70,11 @@ struct V4L {
     uint32_t qcap, o_q[2], o_b[2], o_off[2], o_len[2], o_ex[2], o_exm, o_cnt, stage_bytes, total;
     int T, NS;
 };
-__host__ __device__ inline V4L v4_layout(int Wr, int Wm, int T, int NS, int ins_len){
+__host__ __device__ inline V4L v4_layout(int Wr, int Wm, int T, int NS, int ins_len, bool stats = true){
     V4L l;
     l.T = T; l.NS = NS;
     l.Cr = 4u * (uint32_t)Wr; l.Cm = 4u * (uint32_t)Wm; l.Cp = (l.Cr + 15u) & ~15u;
-    l.statw_r = 4 * NSETS * l.Cr + l.Cr + 1; l.statw_m = 4 * NSETS * l.Cm + l.Cm + 1;
+    l.statw_r = stats ? 4 * NSETS * l.Cr + l.Cr + 1 : 0; l.statw_m = stats ? 4 * NSETS * l.Cm + l.Cm + 1 : 0;   // the trim-only kernel keeps no statistics
     uint32_t o = 256;                         // the head of the block's shared memory holds this struct
     l.o_pre[0] = o; o += 4 * l.statw_r;
     l.o_pre[1] = o; o += 4 * l.statw_r;
@@ -82,7 +82,7 @@ __host__ __device__ inline V4L v4_layout(int Wr, int Wm, int T, int NS, int ins_
     l.o_post[1] = o; o += 4 * l.statw_r;
     o = (o + 7u) & ~7u; l.o_bc = o; o += (uint32_t)sizeof(BlockCounters);
     o = (o + 7u) & ~7u; l.o_ins = o; o += 4u * (uint32_t)ins_len;
-    o = (o + 7u) & ~7u; l.o_bar = o; o += 8u * (uint32_t)NS;
+    o = (o + 7u) & ~7u; l.o_bar = o; o += 16u * (uint32_t)NS;             // full[NS] + empty[NS]
     l.o_misc = o; o += 16;
     o = (o + 127u) & ~127u; l.o_stage = o;
     l.qcap = (uint32_t)T * l.Cp;
@@ -565,7 +565,10 @@ __device__ V4_NI void v4_tail_sub(bool td, uint32_t Rqa, uint32_t Rba, int Rrawl
 
 // The loop body of PairEndProcessor::processPairEnd (src/peprocessor.cpp:292-429, threadId 0) for pairs
 // 32j .. 32j+31 of a staged tile, lane = pair; same statements as k_trim_pe (fqk_kernels.cu).
-template<class SP>
+// MODE 0: the whole body (fused kernel).  MODE 1: everything up to the records (trim kernel of the split path).
+// MODE 2: views and results are read back from the records and only the statistics bookkeeping runs (statistics
+// kernel of the split path).
+template<class SP, int MODE>
 __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally& tl){
     const DevParams& D = *X.D;
     const fq_params& P = D.P;
@@ -574,6 +577,10 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     const bool valid = i < X.nt;
     PeRead a, b;
     bool a1 = false, a2 = false;
+    fq_read_result rec1 = {}, rec2 = {};
+    fq_pair_result pr = {};
+    int res1 = 0, res2 = 0;
+    bool merged = false;
     const bool prof = (X.dbg & 256) != 0;
     V4_PROF0(prof);
 #pragma unroll 1
@@ -593,9 +600,18 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         PeRead r;
         r.qa = X.S32 + L.o_q[m] + doff; r.ba = X.S32 + L.o_b[m] + bshift + (doff >> 2);
         r.doff = doff; r.rawlen = (int)dlen; r.start = 0; r.len = (int)dlen;
+        bool alive = false;
+        if(MODE == 2){                                              // the final view, from the record of the trim kernel
+            r.ge = 0; r.nmask = 0;
+            fq_read_result rr = {};
+            if(valid) rr = m ? X.out2[i] : X.out1[i];
+            alive = valid && !(rr.flags & FQK_F_DROPPED); r.start = rr.start; r.len = rr.len;
+            if(m) rec2 = rr; else rec1 = rr;
+            if(m){ b = r; a2 = alive; } else { a = r; a1 = alive; }
+            continue;
+        }
         const uint2 sw = v4_sweep(r.qa, (int)dlen, P.qual_filter_enabled != 0, (uint32_t)P.low_quality_limit * 0x01010101u, lane);
         r.ge = sw.x; r.nmask = sw.y;
-        bool alive = false;
         if(!SP::generic) alive = valid;                             // Filter::trimAndCut returns the read itself (src/filter.cpp:70-73)
         else if(valid){
             const uint32_t c = v4_trim_and_cut(&P, r.qa, r.rawlen, m ? P.trim_front2 : P.trim_front1, m ? P.trim_tail2 : P.trim_tail1);
@@ -605,10 +621,13 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     }
     V4_GSYNC(X);
     V4_PROF(prof, 0);
-    fq_read_result rec1 = {}, rec2 = {};
-    fq_pair_result pr = {};
-    pr.insert_size = 0xFFFF;
     const bool both = a1 && a2;
+    if(MODE == 2){
+        if(valid) pr = X.outp[i];
+        res1 = rec1.result; res2 = rec2.result;
+        merged = (pr.flags & FQK_P_MERGED) != 0;
+    }else{
+    pr.insert_size = 0xFFFF;
     if(both && P.polyg_enabled && !(X.dbg & 32)){
         // src/peprocessor.cpp:297 hands (maxMismatch, oneEach, minLen) to (compareReq, maxMismatch, oneEach)
 #pragma unroll 1
@@ -688,9 +707,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     if(!(X.dbg & 8)) v4_overlap_chunk(a, b, P.merge_enabled && both && modified, P.overlap_diff_limit, P.overlap_require, lane, ov2);
     V4_GSYNC(X);
     V4_PROF(prof, 4);
-    bool merge_processed = false; int res1 = 0, res2 = 0;
+    bool merge_processed = false;
     int fcA = -1, fnA = 0, fcB = -1, fnB = 0;                // updates of mFilterReadStats: (code, amount) x 2
-    bool merged = false;
     if(P.merge_enabled && both){
         pr.flags |= FQK_P_OV2_DONE | (ov2.overlapped ? FQK_P_OV2_OVERLAP : 0);
         pr.ov2_offset = (int16_t)ov2.offset; pr.ov2_len = (uint16_t)ov2.len; pr.ov2_diff = (uint16_t)ov2.diff;
@@ -736,6 +754,8 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     }
     V4_GSYNC(X);
     V4_PROF(prof, 6);
+    }   // MODE != 2
+    if(MODE == 1) return;
     // ---- what the statistics warps need: length histograms, exception lists, short tails ----
     const uint32_t cnt32 = X.S32 + L.o_cnt;
 #pragma unroll
@@ -781,6 +801,7 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
 // ====================================================================== the kernel
 constexpr int V4_STATS = 256, V4_TRIM = 256, V4_THREADS = V4_STATS + V4_TRIM;
 constexpr int V4_WORKERS = V4_TRIM / 32 - 1;                      // trim warps 0..6 work on chunks, warp 7 is the copy producer
+constexpr int V4_WORKERS_SPLIT = V4_THREADS / 32 - 1;             // trim kernel of the split path: 15 working warps + the producer
 static_assert(sizeof(V4L) <= 256, "V4L lives in the first 256 bytes of the block's shared memory");
 
 // accumulators of the quad path -> the two statistics arrays of a mate (different cycle counts: post1 holds merged reads)
@@ -823,14 +844,23 @@ __device__ __forceinline__ void quad_drain_ab(QuadAcc& A, uint32_t* smA, int CA,
 
 // Named barriers: ids 1..NS tile ready (CH trim-warp arrivals + the statistics warps), NS+1..2NS stage free (the
 // statistics warps arrive, the producer warp waits); `full` (bulk copies landed) is an mbarrier with a transaction count.
-template<class SP>
+// MODE 0: fused (8 statistics warps + 7 trim warps + producer).  The split path runs the same code as two kernels:
+// MODE 1, the trim kernel: no statistics warps and no statistics arrays, 15 trim warps + producer, the shared memory
+// goes to a deeper ring of tiles; stages are handed back to the producer through `empty` mbarriers.  MODE 2, the
+// statistics kernel: the trim warps only rebuild the exception lists from the records, everything else as MODE 0.
+// Why two kernels: the trim role is latency bound (one warp per scheduler and a half, dependent integer chains,
+// profiles/r02n_*) and the register file of an SM cannot hold more than 7 trim warps next to 8 statistics warps of
+// 168 registers; reading the batch twice costs 0.3 ms of HBM time per 4 M pairs, the idle issue slots cost 3 ms.
+template<class SP, int MODE>
 __global__ void __launch_bounds__(V4_THREADS, 1)
 k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_result* __restrict__ out1,
         fq_read_result* __restrict__ out2, fq_pair_result* __restrict__ outp, uint64_t* __restrict__ flat,
         int Wr, int Wm, int T, int NS, int pairs_per_block, int dbg){
     extern __shared__ __align__(128) uint8_t smraw[];
     const fq_params& P = D.P;
-    if(threadIdx.x == 0) *reinterpret_cast<V4L*>(smraw) = v4_layout(Wr, Wm, T, NS, P.insert_size_max + 1);
+    constexpr int NSTAT = MODE == 1 ? 0 : V4_STATS;               // statistics threads
+    constexpr int NWORK = (V4_THREADS - NSTAT) / 32 - 1;          // working trim warps (the last trim warp is the copy producer)
+    if(threadIdx.x == 0) *reinterpret_cast<V4L*>(smraw) = v4_layout(Wr, Wm, T, NS, P.insert_size_max + 1, MODE != 1);
     __syncthreads();
     const V4L& L = *reinterpret_cast<const V4L*>(smraw);
     const uint32_t sm32 = smem_u32(smraw);
@@ -838,6 +868,7 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
     BlockCounters* bc = reinterpret_cast<BlockCounters*>(smraw + L.o_bc);
     uint32_t* ins = reinterpret_cast<uint32_t*>(smraw + L.o_ins);
     uint64_t* full = reinterpret_cast<uint64_t*>(smraw + L.o_bar);
+    uint64_t* empty = full + NS;                                 // MODE 1: all chunks of the staged tile are done
     const int CH = T / 32;                                       // chunks per tile (T is a multiple of 32)
 
     for(uint32_t i = L.o_pre[0] / 4 + threadIdx.x; i < L.o_bar / 4; i += V4_THREADS) reinterpret_cast<uint32_t*>(smraw)[i] = 0;   // statistics, counters, insert sizes
@@ -845,6 +876,7 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
         *reinterpret_cast<uint32_t*>(smraw + L.o_misc) = 0u;         // next chunk of the trim warps
         for(int s = 0; s < NS; ++s){
             mbar_init(&full[s], 1);
+            mbar_init(&empty[s], (uint32_t)CH);
             *reinterpret_cast<uint32_t*>(smraw + L.o_stage + (size_t)s * L.stage_bytes + L.o_cnt + 20) = 0xFFFFFFFFu;   // tile tag: nothing staged yet
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -856,12 +888,12 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
     const int ntiles = (int)((hi - lo + T - 1) / T);
     const int lane = threadIdx.x & 31;
 
-    const bool is_trim = threadIdx.x >= V4_STATS;
-    const int rtid = is_trim ? threadIdx.x - V4_STATS : threadIdx.x;
+    const bool is_trim = MODE == 1 || threadIdx.x >= NSTAT;
+    const int rtid = is_trim ? threadIdx.x - NSTAT : threadIdx.x;
     if(is_trim){
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
+        if(MODE != 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
         const int tw = rtid >> 5;
-        if(tw == V4_WORKERS){
+        if(tw == NWORK){
             // ============================== copy producer ==============================
             auto BM = [&](int m) -> const DevBatch& { return m ? B2 : B1; };
             uint32_t a[2] = {0, 0}, last[2] = {0, 0}, ll[2] = {0, 0};
@@ -880,7 +912,10 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
 #pragma unroll
                     for(int m = 0; m < 2; ++m){ a[m] = BM(m).offsets[t1]; last[m] = BM(m).offsets[t1 + nt1 - 1]; ll[m] = BM(m).lengths[t1 + nt1 - 1]; }
                 }
-                if(n >= 1) nb_sync(1 + NS + s, V4_STATS + 32);
+                if(n >= 1){
+                    if(MODE == 1) mbar_wait_lane0(&empty[s], (uint32_t)(n - 1) & 1u, 20000);
+                    else nb_sync(1 + NS + s, NSTAT + 32);
+                }
                 uint8_t* S = smraw + L.o_stage + (size_t)s * L.stage_bytes;
                 const uint32_t nb = nt & ~7u;                      // bulk copies move multiples of 16 bytes
 #pragma unroll
@@ -933,7 +968,7 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
             // chunks are handed out in order from a shared counter: a chunk that takes long (many candidates to verify)
             // does not hold back the chunks behind it, and at most V4_WORKERS consecutive chunks are in flight
             const uint32_t next32 = sm32 + L.o_misc;
-            const int idle_from = V4_WORKERS - ((dbg >> 12) & 7);          // timing experiment: fewer working warps
+            const int idle_from = NWORK - ((dbg >> 12) & 15);              // timing experiment: fewer working warps
             // Tile groups: the CH warps of a group work on the CH chunks of one tile and meet at a named barrier between the
             // sections of v4_chunk, so that they run the same code at about the same time.  The trim role walks ~48 KB of
             // code per chunk, more than the SM's instruction cache holds; unsynchronised, every warp takes its own misses
@@ -941,9 +976,11 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
             // serves the group: 6.7 -> 5.1 ms with two groups of three (profiles/r02_pe_v4_notes.md).  Groups take tiles
             // round robin.  FQK_V4_DEBUG bit 512 switches back to chunks handed out one by one from a shared counter.
             // Groups need a spare stage to prefetch into (NS > groups); without one the hand-out from the counter is as fast.
-            const bool gs = !(dbg & 512) && CH >= 2 && CH <= V4_WORKERS && NS > V4_WORKERS / CH;
-            const int NG = gs ? V4_WORKERS / CH : 1, grp = tw / CH, jst = tw - grp * CH;
-            X.sync_id = gs ? 2 * NS + 1 + grp : 0; X.sync_n = CH * 32;
+            // The trim kernel (MODE 1) has no ready/free named barriers, so group g syncs on id 1 + g, and it runs as many
+            // groups as there are stages to work on while one is being refilled.
+            const bool gs = !(dbg & 512) && CH >= 2 && CH <= NWORK && (MODE == 1 ? NS >= 2 : NS > NWORK / CH);
+            const int NG = gs ? (MODE == 1 ? min(min(NWORK / CH, NS - 1), 14) : NWORK / CH) : 1, grp = tw / CH, jst = tw - grp * CH;
+            X.sync_id = gs ? (MODE == 1 ? 1 + grp : 2 * NS + 1 + grp) : 0; X.sync_n = CH * 32;
             int kk = grp;
             for(;;){
                 if(tw >= idle_from) break;
@@ -967,17 +1004,18 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
                 V4_PROF(dbg & 256, 10);
                 const uint32_t t0 = lo + (uint32_t)k * T;
                 X.out1 = out1 + t0; X.out2 = out2 + t0; X.outp = outp + t0;
-                if((gs || 32 * j < X.nt) && !(dbg & 1)) v4_chunk<SP>(X, j, lane, tl);
+                if((gs || 32 * j < X.nt) && !(dbg & 1)) v4_chunk<SP, MODE>(X, j, lane, tl);
                 V4_PROF(dbg & 256, 11);
                 __syncwarp();
                 __threadfence_block();
-                nb_arrive(1 + s, CH * 32 + V4_STATS);
+                if(MODE == 1){ if(lane == 0 && k + NS < ntiles) mbar_arrive(&empty[s]); }   // the producer waits only for stages it refills
+                else nb_arrive(1 + s, CH * 32 + NSTAT);
             }
-            counters_add_tally(bc, tl);
+            if(MODE != 2) counters_add_tally(bc, tl);
         }
     }else{
         // ============================ statistics warps ============================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
+        if(MODE != 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
         const int C1 = (int)L.Cr, CM = (int)L.Cm, Cp = (int)L.Cp;
         const int G = V4_STATS / Wr, Gm = G >> 1;                // groups of Wr threads; even groups read1, odd groups read2
         const int g = rtid / Wr, w = rtid - g * Wr;
@@ -1109,18 +1147,22 @@ k_pe_v4(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, fq_read_r
         if(activeM) drain_l1(madd, smPost1, nullptr, CM, wM);
     }
     __syncthreads();
-    retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[0]), (int)L.Cr, D.L, flat + D.L.stats_off[0]);
-    retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[1]), (int)L.Cr, D.L, flat + D.L.stats_off[1]);
-    retire(smPost1, (int)L.Cm, D.L, flat + D.L.stats_off[2]);
-    retire(reinterpret_cast<uint32_t*>(smraw + L.o_post[1]), (int)L.Cr, D.L, flat + D.L.stats_off[3]);
-    counters_flush(bc, D.L, flat);
-    for(int i = threadIdx.x; i <= P.insert_size_max; i += V4_THREADS) if(ins[i]) add_u64(flat + D.L.insert_hist_off + i, ins[i]);
+    if(MODE != 1){
+        retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[0]), (int)L.Cr, D.L, flat + D.L.stats_off[0]);
+        retire(reinterpret_cast<uint32_t*>(smraw + L.o_pre[1]), (int)L.Cr, D.L, flat + D.L.stats_off[1]);
+        retire(smPost1, (int)L.Cm, D.L, flat + D.L.stats_off[2]);
+        retire(reinterpret_cast<uint32_t*>(smraw + L.o_post[1]), (int)L.Cr, D.L, flat + D.L.stats_off[3]);
+    }
+    if(MODE != 2){                                               // run counters and insert sizes belong to the kernel that trims
+        counters_flush(bc, D.L, flat);
+        for(int i = threadIdx.x; i <= P.insert_size_max; i += V4_THREADS) if(ins[i]) add_u64(flat + D.L.insert_hist_off + i, ins[i]);
+    }
 }
 
 // ---------------------------------------------------------------------- host side
 struct V4Plan { int Wr, Wm, T, NS; size_t smem; bool ok; };
 // tile size and stage count for reads up to maxlen bases (0 = unknown: the capacity max_cycles)
-inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin){
+inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin, int mode = 0){
     V4Plan p = {0, 0, 0, 0, 0, false};
     const fq_params& P = D.P;
     const int cap = (int)D.L.max_cycles;
@@ -1133,20 +1175,30 @@ inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin){
     const size_t budget = smem_optin > 4096 ? smem_optin - 1024 : 0;
     const int Gm = (V4_STATS / p.Wr) >> 1;
     int bestT = 0, bestNS = 0; long best = -1;
-    for(int NS = 4; NS >= 2; --NS)
+    const bool st = mode != 1;
+    for(int NS = (st ? 4 : 12); NS >= 2; --NS)
         for(int T = 256; T >= 32; T -= 32){
-            const V4L l = v4_layout(p.Wr, p.Wm, T, NS, P.insert_size_max + 1);
+            const V4L l = v4_layout(p.Wr, p.Wm, T, NS, P.insert_size_max + 1, st);
             if(l.qcap >= (1u << 21) || (size_t)l.total + 128 > budget) continue;
-            // prefer whole quads per statistics group, then more bytes in flight
-            const long score = (long)T * NS + (((T / 4) % Gm == 0) ? 100000 : 0) + (NS >= 3 ? 50000 : 0);
+            long score;
+            if(st) score = (long)T * NS + (((T / 4) % Gm == 0) ? 100000 : 0) + (NS >= 3 ? 50000 : 0);   // whole quads per statistics group, then bytes in flight
+            else{
+                // trim kernel: as many working warps as possible, in groups that walk the code together (CH >= 2)
+                const int CH = T / 32;
+                const bool gs = CH >= 2 && CH <= V4_WORKERS_SPLIT;
+                const int busy = gs ? std::min(std::min(V4_WORKERS_SPLIT / CH, NS - 1), 14) * CH : std::min(V4_WORKERS_SPLIT, (NS - 1) * CH);
+                // measured on cfg3 (4 M pairs, trim + statistics kernel): T=64 NS=8 (7 groups of 2) 5.65 ms, T=96 NS=5 (4 x 3)
+                // 5.27 ms, T=128 NS=4 (3 x 4) 5.24 ms: warps that walk the code together count for more than warps
+                score = (long)busy * 1000 + (gs ? (long)std::min(CH, 4) * 1200 : 0) + NS;
+            }
             if(score > best){ best = score; bestT = T; bestNS = NS; }
         }
     if(best < 0) return p;
     static const int envT = getenv("FQK_V4_T") ? atoi(getenv("FQK_V4_T")) : 0, envNS = getenv("FQK_V4_NS") ? atoi(getenv("FQK_V4_NS")) : 0;
-    if(envT > 0 && envNS >= 2 && envNS <= 4 && envT % 32 == 0 &&
-       (size_t)v4_layout(p.Wr, p.Wm, envT, envNS, P.insert_size_max + 1).total + 128 <= budget){ bestT = envT; bestNS = envNS; }   // timing experiments
+    if(mode == (getenv("FQK_V4_TMODE") ? atoi(getenv("FQK_V4_TMODE")) : 0) && envT > 0 && envNS >= 2 && envNS <= (st ? 4 : 12) && envT % 32 == 0 &&
+       (size_t)v4_layout(p.Wr, p.Wm, envT, envNS, P.insert_size_max + 1, st).total + 128 <= budget){ bestT = envT; bestNS = envNS; }   // timing experiments
     p.T = bestT; p.NS = bestNS;
-    p.smem = v4_layout(p.Wr, p.Wm, p.T, p.NS, P.insert_size_max + 1).total + 128;
+    p.smem = v4_layout(p.Wr, p.Wm, p.T, p.NS, P.insert_size_max + 1, st).total + 128;
     p.ok = true;
     return p;
 }

@@ -15,7 +15,7 @@ static struct { unsigned x, y, z; } threadIdx = {0, 0, 0}, blockIdx = {0, 0, 0},
 
 namespace {
 struct ChunkArg { const V4X* X; int j; Tally* tl; };
-void chunk_body(int lane, void* p){ ChunkArg* a = (ChunkArg*)p; v4_chunk<V4Spec<true>>(*a->X, a->j, lane, a->tl[lane]); }
+void chunk_body(int lane, void* p){ ChunkArg* a = (ChunkArg*)p; v4_chunk<V4Spec<true>, 0>(*a->X, a->j, lane, a->tl[lane]); }
 
 // statistics arrays in the kernel's representation: u32 [kind][set][C] then lenhist[C+1]
 struct SmStats { uint32_t base; uint32_t C; };
