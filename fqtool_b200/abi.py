@@ -103,6 +103,7 @@ EXPORTS = [
     "fqk_process_pe_device", "fqk_sync", "fqk_stream", "fqk_launch_count",
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
+    "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits",
 ]
 
 _lib = None
@@ -148,6 +149,8 @@ def load():
     lib.fqk_packed_bases.argtypes = [u32, vp]; lib.fqk_packed_bases.restype = u64
     lib.fqk_pack_ascii.argtypes = [u32, vp, vp, vp, vp, vp, vp, vp]; lib.fqk_pack_ascii.restype = i32
     lib.fqk_host_alloc.argtypes = [C.c_size_t]; lib.fqk_host_alloc.restype = vp
+    lib.fqk_prepass_kmer_counts.argtypes = [i32, vp, i32, i32, i32, vp]; lib.fqk_prepass_kmer_counts.restype = i32
+    lib.fqk_prepass_seed_hits.argtypes = [i32, vp, i32, i32, i32, u32, vp, vp, u32, vp]; lib.fqk_prepass_seed_hits.restype = i32
     lib.fqk_host_free.argtypes = [vp]; lib.fqk_host_free.restype = None
     _lib = lib
     return lib

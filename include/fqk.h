@@ -343,6 +343,22 @@ uint64_t fqk_packed_bases(uint32_t n, const uint64_t* src_off);
 int  fqk_pack_ascii(uint32_t n, const char* seq, const char* qual, const uint64_t* src_off,
                     uint32_t* offsets, uint16_t* lengths, uint8_t* bases2, uint8_t* qual_out);
 
+/*
+ * Adapter auto-detection pre-pass, device part.  Replaces the two per-base loops of
+ * Evaluator::evaluateAdapterSeq (/root/reference/src/evaluator.cpp:229-390: k-mer counting over the first 256 K reads,
+ * k = 10, positions 20 .. len - k - shiftTail) and Evaluator::getAdapterWithSeed (src/evaluator.cpp:392-407: every
+ * window whose key equals the seed).  Keys are Evaluator::seq2int's (A0 T1 C2 G3, first base most significant); a
+ * window holding any other character is not counted.  Context-free (the pre-pass runs before the processors exist):
+ * `device` is a CUDA ordinal; there is no CPU fallback.  The host keeps ranking the keys and the NucleotideTree walk.
+ *   fqk_prepass_kmer_counts  counts[4^keylen] (caller allocated), keylen 1..15
+ *   fqk_prepass_seed_hits    *n = number of windows equal to seed; the first min(*n, cap) found are written to
+ *                            read_idx[] / pos[] in no particular order
+ */
+int  fqk_prepass_kmer_counts(int device, const fq_ascii_batch* reads, int keylen, int first_pos, int shift_tail,
+                             uint64_t* counts);
+int  fqk_prepass_seed_hits(int device, const fq_ascii_batch* reads, int keylen, int first_pos, int shift_tail, uint32_t seed,
+                           uint32_t* read_idx, uint32_t* pos, uint32_t cap, uint32_t* n);
+
 /* pinned host memory helpers for callers without a CUDA toolchain */
 void* fqk_host_alloc(size_t bytes);
 void  fqk_host_free(void* p);

@@ -31,6 +31,7 @@ namespace fqkseam {
     std::exit(3);
 }
 
+#ifdef FQK_SEAM_PROCESSOR   /* the parts that need Stats / FilterResult / ThreadConfig: seprocessor.cpp, peprocessor.cpp */
 // Options (after Options::update and the Evaluator pre-passes of main.cpp:124-142) -> fq_params
 inline fq_params paramsFromOptions(Options* o){
     fq_params p;
@@ -222,5 +223,7 @@ inline void finishCommon(Options* opt, ThreadConfig** configs, Duplicate* dup, l
 }
 inline void finishSE(Options* opt, ThreadConfig** configs, Duplicate* dup){ finishCommon(opt, configs, dup, nullptr); }
 inline void finishPE(Options* opt, ThreadConfig** configs, Duplicate* dup, long* insertHist){ finishCommon(opt, configs, dup, insertHist); }
+
+#endif /* FQK_SEAM_PROCESSOR */
 
 } // namespace fqkseam

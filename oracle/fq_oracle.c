@@ -729,3 +729,56 @@ int fqo_merge(fqo_ctx* c, const fqo_ctx* o){
     for(uint64_t i = 0; i < c->L.total_u64; ++i) c->flat[i] += o->flat[i];
     return 0;
 }
+
+/* ------------------------------------------------ adapter detection pre-pass */
+/* Evaluator::seq2int, src/evaluator.cpp:3-49: rolling 2-bit key, -1 while the window holds a character outside ATCG */
+static int ad_code(char c){ return c == 'A' ? 0 : c == 'T' ? 1 : c == 'C' ? 2 : c == 'G' ? 3 : -1; }
+static int ad_seq2int(const char* s, int pos, int keylen, int last){
+    if(last >= 0){
+        const int mask = (1 << (keylen * 2)) - 1;
+        const int c = ad_code(s[pos + keylen - 1]);
+        return c < 0 ? -1 : (((last << 2) & mask) + c);
+    }
+    int key = 0;
+    for(int i = pos; i < pos + keylen; ++i){
+        const int c = ad_code(s[i]);
+        if(c < 0) return -1;
+        key = (key << 2) + c;
+    }
+    return key;
+}
+/* the counting loop of Evaluator::evaluateAdapterSeq, src/evaluator.cpp:271-283 */
+int fqo_adapter_kmer_counts(uint32_t n, const char* seq, const uint64_t* off, int keylen, int first_pos, int shift_tail,
+                            uint64_t* counts){
+    if(keylen < 1 || keylen > 15) return FQK_E_INVALID;
+    memset(counts, 0, sizeof(uint64_t) << (2 * keylen));
+    for(uint32_t r = 0; r < n; ++r){
+        const char* s = seq + off[r];
+        const int len = (int)(off[r + 1] - off[r]);
+        int key = -1;
+        for(int pos = first_pos; pos <= len - keylen - shift_tail; ++pos){
+            key = ad_seq2int(s, pos, keylen, key);
+            if(key >= 0) ++counts[key];
+        }
+    }
+    return 0;
+}
+/* the scan of Evaluator::getAdapterWithSeed, src/evaluator.cpp:396-407 */
+int fqo_adapter_seed_hits(uint32_t n, const char* seq, const uint64_t* off, int keylen, int first_pos, int shift_tail,
+                          uint32_t seed, uint32_t* read_idx, uint32_t* pos_out, uint32_t cap, uint32_t* nhits){
+    uint32_t k = 0;
+    for(uint32_t r = 0; r < n; ++r){
+        const char* s = seq + off[r];
+        const int len = (int)(off[r + 1] - off[r]);
+        int key = -1;
+        for(int pos = first_pos; pos <= len - keylen - shift_tail; ++pos){
+            key = ad_seq2int(s, pos, keylen, key);
+            if(key >= 0 && (uint32_t)key == seed){
+                if(k < cap){ read_idx[k] = r; pos_out[k] = (uint32_t)pos; }
+                ++k;
+            }
+        }
+    }
+    *nhits = k;
+    return 0;
+}

@@ -45,6 +45,16 @@ int  fqo_dup_table(fqo_ctx* c, uint64_t* dups, uint32_t* counts, uint8_t* gc);
  * dup tables by the (min kmer32, count) rule); used by the multi-thread baseline */
 int  fqo_merge(fqo_ctx* c, const fqo_ctx* other);
 
+
+/* Adapter auto-detection pre-pass (Evaluator::evaluateAdapterSeq, src/evaluator.cpp:229-390): counts[4^keylen] of the
+ * windows [pos, pos+keylen), pos = first_pos .. len - keylen - shift_tail, whose characters are all in ATCG (key =
+ * Evaluator::seq2int, src/evaluator.cpp:3-49); and the (read, pos) list of the windows equal to `seed`
+ * (Evaluator::getAdapterWithSeed, src/evaluator.cpp:392-407), in input order. */
+int  fqo_adapter_kmer_counts(uint32_t n, const char* seq, const uint64_t* off, int keylen, int first_pos, int shift_tail,
+                             uint64_t* counts);
+int  fqo_adapter_seed_hits(uint32_t n, const char* seq, const uint64_t* off, int keylen, int first_pos, int shift_tail,
+                           uint32_t seed, uint32_t* read_idx, uint32_t* pos, uint32_t cap, uint32_t* nhits);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,3 +148,42 @@ def bench_reference(params, threads, reads1, reads2=None):
     if rc:
         raise RuntimeError("fqr_bench failed")
     return sec.value, passed.value
+
+
+# ---------------------------------------------------------------- adapter detection pre-pass
+def adapter_kmer_counts(reads, keylen=10, first_pos=20, shift_tail=1, kind="port"):
+    """counts[4^keylen]: oracle port (kind="port") or the loop run with the reference's own Evaluator::seq2int."""
+    import numpy as np
+    lib = C.CDLL(PORT_LIB if kind == "port" else REF_LIB)
+    f = lib.fqo_adapter_kmer_counts if kind == "port" else lib.fqr_adapter_kmer_counts
+    seq = np.ascontiguousarray(reads[0]); off = np.ascontiguousarray(reads[2], dtype=np.uint64)
+    counts = np.zeros(1 << (2 * keylen), dtype=np.uint64)
+    f.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    rc = f(len(off) - 1, abi.ptr(seq), abi.ptr(off), keylen, first_pos, shift_tail, abi.ptr(counts))
+    assert rc == 0
+    return counts
+
+
+def adapter_seed_hits(reads, seed, keylen=10, first_pos=20, shift_tail=1):
+    import numpy as np
+    lib = C.CDLL(PORT_LIB)
+    seq = np.ascontiguousarray(reads[0]); off = np.ascontiguousarray(reads[2], dtype=np.uint64)
+    n = C.c_uint32(0)
+    f = lib.fqo_adapter_seed_hits
+    f.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    f(len(off) - 1, abi.ptr(seq), abi.ptr(off), keylen, first_pos, shift_tail, seed, None, None, 0, C.byref(n))
+    ri = np.zeros(max(n.value, 1), dtype=np.uint32); po = np.zeros(max(n.value, 1), dtype=np.uint32)
+    f(len(off) - 1, abi.ptr(seq), abi.ptr(off), keylen, first_pos, shift_tail, seed, abi.ptr(ri), abi.ptr(po), n.value, C.byref(n))
+    return ri[:n.value], po[:n.value]
+
+
+def reference_adapter_with_seed(reads, seed, keylen=10, trim_tail1=0):
+    """Evaluator::getAdapterWithSeed of the reference build on these reads."""
+    import numpy as np
+    lib = C.CDLL(REF_LIB)
+    seq = np.ascontiguousarray(reads[0]); off = np.ascontiguousarray(reads[2], dtype=np.uint64)
+    out = C.create_string_buffer(256)
+    f = lib.fqr_adapter_with_seed
+    f.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_uint32]
+    assert f(len(off) - 1, abi.ptr(seq), abi.ptr(off), seed, keylen, trim_tail1, out, 256) == 0
+    return out.value.decode()

@@ -557,3 +557,35 @@ extern "C" int fqr_bench(const fq_params* p, int threads, uint32_t n,
     delete dup;
     return 0;
 }
+
+// ---------------------------------------------------------------- adapter detection pre-pass (reference functions)
+// counts with the reference's own Evaluator::seq2int in the loop of Evaluator::evaluateAdapterSeq (src/evaluator.cpp:271-283)
+extern "C" int fqr_adapter_kmer_counts(uint32_t n, const char* seq, const uint64_t* off, int keylen, int first_pos, int shift_tail,
+                                       uint64_t* counts){
+    memset(counts, 0, sizeof(uint64_t) << (2 * keylen));
+    for(uint32_t r = 0; r < n; ++r){
+        const std::string s(seq + off[r], (size_t)(off[r + 1] - off[r]));
+        int key = -1;
+        for(int pos = first_pos; pos <= (int)s.length() - keylen - shift_tail; ++pos){
+            key = Evaluator::seq2int(s, pos, keylen, key);
+            if(key >= 0) ++counts[key];
+        }
+    }
+    return 0;
+}
+// Evaluator::getAdapterWithSeed (src/evaluator.cpp:392-425) itself on a set of reads: the adapter the reference derives from a seed
+extern "C" int fqr_adapter_with_seed(uint32_t n, const char* seq, const uint64_t* off, int seed, int keylen, int trim_tail1,
+                                     char* out, uint32_t cap){
+    Options opt;
+    Evaluator ev(&opt);
+    std::vector<Read*> reads(n);
+    for(uint32_t r = 0; r < n; ++r){
+        const std::string s(seq + off[r], (size_t)(off[r + 1] - off[r]));
+        reads[r] = new Read("@r", s, "+", std::string(s.size(), 'I'));
+    }
+    const std::string a = ev.getAdapterWithSeed(seed, reads.data(), (long)n, keylen, trim_tail1);
+    for(auto r : reads) delete r;
+    if(a.size() + 1 > cap) return -1;
+    memcpy(out, a.c_str(), a.size() + 1);
+    return 0;
+}

@@ -91,3 +91,31 @@ def test_dropin_matches_reference_program(case, tmp_path):
     for k in ja:
         assert ja[k] == jb.get(k), f"{case}: report.json section {k} differs"
     assert set(ja) == set(jb)
+
+
+@pytest.mark.gpu
+def test_dropin_adapter_autodetection(tmp_path):
+    """Evaluator::evaluateAdapterSeq needs 10000 records: the 2000 test pairs six times over.  The pre-pass of the drop-in
+    (integration/evaluator_body.inc: 10-mer counts and seed hits from fqk_prepass_*) must report the same detected adapters
+    (here: none for read 1, TruSeq universal for read 2) and the whole run must stay identical."""
+    if not _have():
+        pytest.skip("drop-in binaries not built (reference sources absent)")
+    import gzip
+    big = []
+    for i, src in enumerate((FQ1, FQ2)):
+        p = str(tmp_path / f"big{i + 1}.fq")
+        data = gzip.open(src, "rb").read()
+        open(p, "wb").write(data * 6)
+        big.append(p)
+    outs = {}
+    for tag, exe in (("ref", REF), ("fqk", FQK)):
+        d = str(tmp_path / tag); os.makedirs(d)
+        cmd = [exe, "-i", big[0], "-I", big[1], "-o", f"{d}/out1.fq", "-O", f"{d}/out2.fq", "-w", "1", "-J", f"{d}/report.json",
+               "-H", f"{d}/report.html", "-a", "-q", "-g"]
+        r = subprocess.run(cmd, capture_output=True, text=True, cwd=d)
+        assert r.returncode == 0, r.stderr
+        j = json.load(open(f"{d}/report.json")); j.pop("Software")
+        outs[tag] = (j, open(f"{d}/out1.fq", "rb").read(), open(f"{d}/out2.fq", "rb").read())
+    assert outs["ref"][0]["AdapterTrim"]["Read2AdapterSequence"].startswith("AGATCGGAAGAGC")     # the pre-pass did find one
+    assert outs["ref"][0]["AdapterTrim"] == outs["fqk"][0]["AdapterTrim"]
+    assert outs["ref"] == outs["fqk"]
