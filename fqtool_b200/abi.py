@@ -73,6 +73,19 @@ class FqAsciiBatch(C.Structure):
                 ("off", C.c_void_p), ("seq", C.c_void_p), ("qual", C.c_void_p)]
 
 
+class FqTextBatch(C.Structure):
+    _fields_ = [("reads", FqAsciiBatch), ("name_off", C.c_void_p), ("names", C.c_void_p),
+                ("strand_off", C.c_void_p), ("strands", C.c_void_p)]
+
+
+class FqTextOut(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("cap", C.c_uint64), ("len", C.c_uint64), ("records", C.c_uint64)]
+
+
+CH_OUT1, CH_OUT2, CH_MERGED, CH_FAILED, CH_UNPAIRED1, CH_UNPAIRED2, CH_SINGLE, CH_COUNT = 0, 1, 2, 3, 4, 5, 6, 7
+W_FAILED, W_UNPAIRED1, W_STDOUT = 1, 2, 4
+
+
 class FqStatsLayout(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "total_u64", "max_cycles", "kmer_bins")] + [("stats_off", C.c_uint64 * 4)] + [
@@ -103,7 +116,7 @@ EXPORTS = [
     "fqk_process_pe_device", "fqk_sync", "fqk_stream", "fqk_launch_count",
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
-    "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits",
+    "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits", "fqk_process_se_text", "fqk_process_pe_text",
 ]
 
 _lib = None
@@ -149,6 +162,9 @@ def load():
     lib.fqk_packed_bases.argtypes = [u32, vp]; lib.fqk_packed_bases.restype = u64
     lib.fqk_pack_ascii.argtypes = [u32, vp, vp, vp, vp, vp, vp, vp]; lib.fqk_pack_ascii.restype = i32
     lib.fqk_host_alloc.argtypes = [C.c_size_t]; lib.fqk_host_alloc.restype = vp
+    lib.fqk_process_se_text.argtypes = [vp, P(FqTextBatch), u32, vp, P(FqTextOut), P(u64)]; lib.fqk_process_se_text.restype = i32
+    lib.fqk_process_pe_text.argtypes = [vp, P(FqTextBatch), P(FqTextBatch), u32, vp, vp, vp, P(FqTextOut), P(u64)]
+    lib.fqk_process_pe_text.restype = i32
     lib.fqk_prepass_kmer_counts.argtypes = [i32, vp, i32, i32, i32, vp]; lib.fqk_prepass_kmer_counts.restype = i32
     lib.fqk_prepass_seed_hits.argtypes = [i32, vp, i32, i32, i32, u32, vp, vp, u32, vp]; lib.fqk_prepass_seed_hits.restype = i32
     lib.fqk_host_free.argtypes = [vp]; lib.fqk_host_free.restype = None

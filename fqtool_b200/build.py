@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libfqk.so")
-SOURCES = ["fqk_api.cu", "fqk_kernels.cu", "fqk_fused.cu", "fqk_synth.cu", "fqk_prepass.cu"]
+SOURCES = ["fqk_api.cu", "fqk_kernels.cu", "fqk_fused.cu", "fqk_synth.cu", "fqk_prepass.cu", "fqk_text.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

@@ -9,6 +9,7 @@
 #include "fqk_kernels.h"
 #include "fqk_fused.h"
 #include "fqk_hostutil.h"
+#include "fqk_text.h"
 
 // ------------------------------------------------------------------- NCCL
 // NCCL is bound at run time (dlopen) so that the library also loads on hosts
@@ -68,6 +69,9 @@ struct fqk_ctx {
     // ASCII ingest staging (fqk_process_*_ascii): raw characters and source offsets per mate, pinned index arrays
     DevBuf aseq[2], aqual[2], asrc[2];
     std::vector<uint32_t> hsrc[2], hdst[2]; std::vector<uint16_t> hlen[2];
+    // text entry points (fqk_process_*_text): names and third lines per mate, sizes/offsets, per-channel text blocks
+    DevBuf tnames[2], tnoff[2], tstr[2], tsoff[2], tsizes, tscratch, ttot, tout[FQK_CH_COUNT];
+    std::vector<uint32_t> hnoff[2], hsoff[2];
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
     // cross-rank merge scratch, allocated once in fqk_create when nranks > 1 (no allocation between collectives)
@@ -275,6 +279,9 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(int i = 0; i < 2; ++i){ c->st[i].off.release(); c->st[i].len.release(); c->st[i].b2.release(); c->st[i].q.release(); }
     c->res1.release(); c->res2.release(); c->resp.release(); c->corr.release();
     for(int i = 0; i < 2; ++i){ c->aseq[i].release(); c->aqual[i].release(); c->asrc[i].release(); }
+    for(int i = 0; i < 2; ++i){ c->tnames[i].release(); c->tnoff[i].release(); c->tstr[i].release(); c->tsoff[i].release(); }
+    c->tsizes.release(); c->tscratch.release(); c->ttot.release();
+    for(int i = 0; i < FQK_CH_COUNT; ++i) c->tout[i].release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
     cudaFree(c->m_flat); cudaFree(c->m_idx); cudaFree(c->m_first); cudaFree(c->m_status);
@@ -547,6 +554,120 @@ extern "C" int fqk_process_pe_ascii(fqk_ctx* c, const fq_ascii_batch* r1, const 
     CU(cudaMemcpyAsync(o1, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(o2, c->res2.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(op, c->resp.p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
+    return check_err_flag(c);
+}
+
+
+// ---------------------------------------------------------------- text entry points (fqk_text.cu)
+// names and third lines of one mate to the device (offsets rebased and narrowed to 32 bit)
+static int stage_text(fqk_ctx* c, int m, const fq_text_batch* b){
+    const uint32_t n = b->reads.n_reads;
+    if(!b->name_off || !b->strand_off || (!b->names && b->name_off[n] > b->name_off[0]) || (!b->strands && b->strand_off[n] > b->strand_off[0]))
+        return fail(c, FQK_E_INVALID, "text batch without names / third lines");
+    const uint64_t nb = b->name_off[n] - b->name_off[0], sb = b->strand_off[n] - b->strand_off[0];
+    if(nb > 0xFFFFFFF0ull || sb > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "more than 2^32 name characters in a pack");
+    if(c->tnames[m].ensure(nb + 16) || c->tstr[m].ensure(sb + 16) || c->tnoff[m].ensure((size_t)(n + 1) * 4) || c->tsoff[m].ensure((size_t)(n + 1) * 4))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    if(nb) CU(cudaMemcpyAsync(c->tnames[m].p, b->names + b->name_off[0], nb, cudaMemcpyHostToDevice, c->stream));
+    if(sb) CU(cudaMemcpyAsync(c->tstr[m].p, b->strands + b->strand_off[0], sb, cudaMemcpyHostToDevice, c->stream));
+    c->hnoff[m].resize(n + 1); c->hsoff[m].resize(n + 1);
+    for(uint32_t i = 0; i <= n; ++i){
+        c->hnoff[m][i] = (uint32_t)(b->name_off[i] - b->name_off[0]); c->hsoff[m][i] = (uint32_t)(b->strand_off[i] - b->strand_off[0]);
+    }
+    CU(cudaMemcpyAsync(c->tnoff[m].p, c->hnoff[m].data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->tsoff[m].p, c->hsoff[m].data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));                  // hnoff / hsoff are pageable and reused by the next call
+    return 0;
+}
+static TextMate text_mate(fqk_ctx* c, int m){
+    TextMate t;
+    t.seq = (const char*)c->aseq[m].p; t.qual = (const char*)c->aqual[m].p; t.src = (const uint32_t*)c->asrc[m].p;
+    t.len = (const uint16_t*)c->st[m].len.p;
+    t.names = (const char*)c->tnames[m].p; t.name_off = (const uint32_t*)c->tnoff[m].p;
+    t.strands = (const char*)c->tstr[m].p; t.strand_off = (const uint32_t*)c->tsoff[m].p;
+    return t;
+}
+// records on the device -> per-channel text blocks in the caller's buffers
+static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq_text_out* outs, uint64_t* read_passed){
+    const TextMate m1 = text_mate(c, 0), m2 = paired ? text_mate(c, 1) : m1;
+    const fq_read_result* r1 = (const fq_read_result*)c->res1.p;
+    const fq_read_result* r2 = paired ? (const fq_read_result*)c->res2.p : nullptr;
+    const fq_pair_result* rp = paired ? (const fq_pair_result*)c->resp.p : nullptr;
+    if(c->tsizes.ensure((size_t)FQK_CH_COUNT * n * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(n) * 8) || c->ttot.ensure(256))
+        return fail(c, FQK_E_NOMEM, "text scratch allocation failed");
+    uint64_t* totals = (uint64_t*)c->ttot.p;                               // [FQK_CH_COUNT] bytes, then TEXT_SLOTS u32 counters
+    uint32_t* counters = (uint32_t*)(totals + FQK_CH_COUNT);
+    CU(cudaMemsetAsync(c->ttot.p, 0, 256, c->stream));
+    if(paired && c->D.P.correction_enabled && c->corr.p)
+        text_launch_apply_edits(c->stream, (const fq_correction*)c->corr.p, c->maxlen2 + 2, c->corr_cap, (char*)c->aseq[0].p, (char*)c->aqual[0].p,
+                                m1.src, (char*)c->aseq[1].p, (char*)c->aqual[1].p, m2.src);
+    text_launch_sizes(c->stream, paired, n, writers, m1, m2, r1, r2, rp, (uint32_t*)c->tsizes.p, counters);
+    text_launch_scan(c->stream, n, (uint32_t*)c->tsizes.p, totals, (uint64_t*)c->tscratch.p);
+    c->launches += paired && c->D.P.correction_enabled ? 5 : 4;
+    struct { uint64_t tot[FQK_CH_COUNT]; uint32_t cnt[TEXT_SLOTS]; } h;
+    CU(cudaMemcpyAsync(&h, c->ttot.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    int rc = 0;
+    TextOut to;
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){
+        outs[ch].len = h.tot[ch]; outs[ch].records = h.cnt[ch];
+        to.p[ch] = nullptr;
+        if(!h.tot[ch]) continue;
+        if(h.tot[ch] > 0xFFFFFFF0ull) rc = fail(c, FQK_E_LIMIT, "a text channel of a pack exceeds 4 GiB: use smaller packs");
+        else if(!outs[ch].data || outs[ch].cap < h.tot[ch]) rc = fail(c, FQK_E_LIMIT, "text output buffer too small (fq_text_out.len holds the size needed)");
+        else if(c->tout[ch].ensure(h.tot[ch] + 16)) rc = fail(c, FQK_E_NOMEM, "text block allocation failed");
+        to.p[ch] = (char*)c->tout[ch].p;
+    }
+    if(read_passed) *read_passed = h.cnt[FQK_CH_COUNT];
+    if(rc) return rc;
+    text_launch_copy(c->stream, paired, n, writers, m1, m2, r1, r2, rp, (const uint32_t*)c->tsizes.p, to);
+    c->launches++;
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch)
+        if(h.tot[ch]) CU(cudaMemcpyAsync(outs[ch].data, c->tout[ch].p, h.tot[ch], cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int fqk_process_se_text(fqk_ctx* c, const fq_text_batch* in, uint32_t writers, fq_read_result* out, fq_text_out* outs,
+                                   uint64_t* read_passed){
+    if(!c || !in || !in->reads.off || !outs) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    if(read_passed) *read_passed = 0;
+    const size_t n = in->reads.n_reads;
+    if(n == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    int rc = stage_ascii(c, 0, &in->reads); if(rc) return rc;
+    rc = stage_text(c, 0, in); if(rc) return rc;
+    if(c->res1.ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
+    if(out) CU(cudaMemcpyAsync(out, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    rc = text_finish(c, false, (uint32_t)n, writers, outs, read_passed); if(rc) return rc;
+    return check_err_flag(c);
+}
+
+extern "C" int fqk_process_pe_text(fqk_ctx* c, const fq_text_batch* r1, const fq_text_batch* r2, uint32_t writers, fq_read_result* o1,
+                                   fq_read_result* o2, fq_pair_result* op, fq_text_out* outs, uint64_t* read_passed){
+    if(!c || !r1 || !r2 || !r1->reads.off || !r2->reads.off || !outs) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    if(r1->reads.n_reads != r2->reads.n_reads) return fail(c, FQK_E_INVALID, "read1/read2 batches differ in size");
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    if(read_passed) *read_passed = 0;
+    const size_t n = r1->reads.n_reads;
+    if(n == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    int rc = stage_ascii(c, 0, &r1->reads); if(rc) return rc;
+    rc = stage_ascii(c, 1, &r2->reads); if(rc) return rc;
+    rc = stage_text(c, 0, r1); if(rc) return rc;
+    rc = stage_text(c, 1, r2); if(rc) return rc;
+    if(c->res1.ensure(n * sizeof(fq_read_result)) || c->res2.ensure(n * sizeof(fq_read_result)) ||
+       c->resp.ensure(n * sizeof(fq_pair_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_pe(c, c->st[0].dev, c->st[1].dev, (fq_read_result*)c->res1.p, (fq_read_result*)c->res2.p, (fq_pair_result*)c->resp.p);
+    if(rc) return rc;
+    if(o1) CU(cudaMemcpyAsync(o1, c->res1.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    if(o2) CU(cudaMemcpyAsync(o2, c->res2.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    if(op) CU(cudaMemcpyAsync(op, c->resp.p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
+    rc = text_finish(c, true, (uint32_t)n, writers, outs, read_passed); if(rc) return rc;
     return check_err_flag(c);
 }
 

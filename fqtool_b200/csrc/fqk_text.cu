@@ -1,0 +1,302 @@
+// fqk_text.cu -- device-side output compaction and FASTQ record assembly.
+//
+// What the reference does per read on the host after the hot path: Read::toString / toStringWithTag
+// (/root/reference/src/read.h:166-176), the routing ladders of SingleEndProcessor::processSingleEnd
+// (src/seprocessor.cpp:340-349) and PairEndProcessor::processPairEnd (src/peprocessor.cpp:353-429) and the assembly
+// of merged reads (OverlapAnalysis::merge, src/overlapanalysis.cpp:74-104, with its name quirk).  Here the records
+// of the trim kernels and the FASTQ characters already staged on the device become, per output channel, ONE
+// contiguous block of FASTQ text in input order:
+//   k_text_sizes   a thread per read (pair): the routing ladder -> bytes per channel
+//   k_scan_*       exclusive prefix sums per channel (three small kernels, 2048 items per block)
+//   k_text_copy    a warp per read (pair): the same ladder -> the pieces, copied with lane-strided byte moves
+// so that the host's writer threads only hand blocks to gzwrite; no per-read string is built on the host.
+#include "fqk_text.h"
+
+namespace {
+
+// failure tags, /root/reference/src/common.h:21-30; index 32 = "paired_read_is_failing" (src/peprocessor.cpp:409,424)
+__constant__ char c_tags[33][24] = {
+    "passed", "", "", "", "failed_polyx_filter", "", "", "", "failed_bad_overlap", "", "", "",
+    "failed_too_many_n_bases", "", "", "", "failed_too_short", "failed_too_long", "", "",
+    "failed_quality_filter", "", "", "", "failed_low_complexity", "", "", "", "", "", "", "", "paired_read_is_failing"};
+__device__ __forceinline__ uint32_t tag_len(int t){ uint32_t n = 0; while(c_tags[t][n]) ++n; return n; }
+__device__ __forceinline__ uint32_t dec_digits(uint32_t v){ uint32_t n = 1; while(v >= 10){ v /= 10; ++n; } return n; }
+
+struct Piece { int ch; int kind; int tag; };          // kind 0 read1, 1 read2, 2 merged read; tag -1 none
+constexpr int TAG_PAIR = 32;
+
+// the if/else ladder of src/peprocessor.cpp:353-429 (and fqtool_b200/host/fqk_host.cpp) -> at most two pieces
+__device__ __forceinline__ int route_pe(const fq_read_result& x1, const fq_read_result& x2, const fq_pair_result& pr, uint32_t writers,
+                                        Piece* pc, bool& passed){
+    const bool a1 = !(x1.flags & FQK_F_DROPPED), a2 = !(x2.flags & FQK_F_DROPPED);
+    const int r1 = x1.result, r2 = x2.result;
+    const bool wf = writers & FQK_W_FAILED, wu = writers & FQK_W_UNPAIRED1;
+    int n = 0; passed = false;
+    if(pr.flags & FQK_P_MERGE_PROC){
+        if(pr.flags & FQK_P_OV2_OVERLAP){
+            if((pr.flags & FQK_P_MERGED) && pr.ov2_len){ pc[n++] = {FQK_CH_MERGED, 2, -1}; passed = true; }
+        }else{
+            if(r1 == FQK_PASS_FILTER) pc[n++] = {FQK_CH_MERGED, 0, -1};
+            if(r2 == FQK_PASS_FILTER) pc[n++] = {FQK_CH_MERGED, 1, -1};
+            passed = r1 == FQK_PASS_FILTER && r2 == FQK_PASS_FILTER;
+        }
+    }else if(a1 && r1 == FQK_PASS_FILTER && a2 && r2 == FQK_PASS_FILTER){
+        if(writers & FQK_W_STDOUT){ pc[n++] = {FQK_CH_SINGLE, 0, -1}; pc[n++] = {FQK_CH_SINGLE, 1, -1}; }
+        else { pc[n++] = {FQK_CH_OUT1, 0, -1}; pc[n++] = {FQK_CH_OUT2, 1, -1}; }
+        passed = true;
+    }else if(a1 && r1 == FQK_PASS_FILTER){
+        if(wu){ pc[n++] = {FQK_CH_UNPAIRED1, 0, -1}; if(wf) pc[n++] = {FQK_CH_FAILED, 1, r2}; }
+        else if(wf){ pc[n++] = {FQK_CH_FAILED, 0, TAG_PAIR}; pc[n++] = {FQK_CH_FAILED, 1, r2}; }
+    }else if(a2 && r2 == FQK_PASS_FILTER){
+        // as written in the reference: the LEFT unpaired writer is tested and read1 is tagged with result2
+        if(wu){ pc[n++] = {FQK_CH_UNPAIRED2, 1, -1}; if(wf) pc[n++] = {FQK_CH_FAILED, 0, r2}; }
+        else if(wf){ pc[n++] = {FQK_CH_FAILED, 0, r1}; pc[n++] = {FQK_CH_FAILED, 1, TAG_PAIR}; }
+    }
+    return n;
+}
+__device__ __forceinline__ int route_se(const fq_read_result& x, uint32_t writers, Piece* pc, bool& passed){
+    passed = !(x.flags & FQK_F_DROPPED) && x.result == FQK_PASS_FILTER;
+    if(passed){ pc[0] = {FQK_CH_OUT1, 0, -1}; return 1; }
+    if(writers & FQK_W_FAILED){ pc[0] = {FQK_CH_FAILED, 0, (int)x.result}; return 1; }
+    return 0;
+}
+
+// the part of a read that its Read object holds after the trimming chain: the view, or everything when trimAndCut dropped it
+__device__ __forceinline__ void view_of(const fq_read_result& x, uint32_t rawlen, uint32_t& start, uint32_t& len){
+    if(x.flags & FQK_F_DROPPED){ start = 0; len = rawlen; } else { start = x.start; len = x.len; }
+}
+// position of the first ' ' of a name (or the length when there is none)
+__device__ __forceinline__ uint32_t first_space(const char* s, uint32_t n){ uint32_t p = 0; while(p < n && s[p] != ' ') ++p; return p; }
+
+// bytes of the merged read's name: OverlapAnalysis::merge builds "_merged_<len1>_<len2>" and splices it before the first
+// space of read1's name MINUS ONE character (substr(0, pos - 1)); without a space the name itself is lost
+__device__ __forceinline__ uint32_t merged_name_len(const char* name, uint32_t nl, uint32_t len1, uint32_t len2){
+    const uint32_t tagl = 8 + dec_digits(len1) + 1 + dec_digits(len2);
+    const uint32_t sp = first_space(name, nl);
+    if(sp >= nl) return tagl;
+    return (sp - 1) + tagl + (nl - sp);
+}
+
+__device__ __forceinline__ uint32_t piece_bytes(const Piece& p, const TextMate& m1, const TextMate& m2, uint32_t i,
+                                                const fq_read_result& x1, const fq_read_result& x2, const fq_pair_result& pr){
+    if(p.kind == 2){
+        const uint32_t nl = m1.name_off[i + 1] - m1.name_off[i], sl = m1.strand_off[i + 1] - m1.strand_off[i];
+        const uint32_t L = (uint32_t)pr.merge_len1 + pr.merge_len2;
+        return merged_name_len(m1.names + m1.name_off[i], nl, pr.merge_len1, pr.merge_len2) + 1 + L + 1 + sl + 1 + L + 1;
+    }
+    const TextMate& m = p.kind ? m2 : m1;
+    const fq_read_result& x = p.kind ? x2 : x1;
+    uint32_t st, ln; view_of(x, m.len[i], st, ln);
+    const uint32_t nl = m.name_off[i + 1] - m.name_off[i], sl = m.strand_off[i + 1] - m.strand_off[i];
+    return nl + (p.tag >= 0 ? 1 + tag_len(p.tag) : 0) + 1 + ln + 1 + sl + 1 + ln + 1;
+}
+
+__global__ void k_text_sizes(bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* __restrict__ r1,
+                             const fq_read_result* __restrict__ r2, const fq_pair_result* __restrict__ rp,
+                             uint32_t* __restrict__ sizes, uint32_t* __restrict__ counters){
+    const int lane = threadIdx.x & 31;
+    for(uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x){
+        const uint32_t i = base + lane;
+        uint32_t sz[FQK_CH_COUNT] = {0, 0, 0, 0, 0, 0, 0};
+        uint32_t rc[FQK_CH_COUNT] = {0, 0, 0, 0, 0, 0, 0};
+        bool passed = false;
+        if(i < n){
+            Piece pc[2]; int np;
+            const fq_read_result x1 = r1[i];
+            fq_read_result x2 = {}; fq_pair_result pr = {};
+            if(paired){ x2 = r2[i]; pr = rp[i]; np = route_pe(x1, x2, pr, writers, pc, passed); }
+            else np = route_se(x1, writers, pc, passed);
+            for(int k = 0; k < np; ++k){
+                const uint32_t b = piece_bytes(pc[k], m1, m2, i, x1, x2, pr);
+#pragma unroll
+                for(int c = 0; c < FQK_CH_COUNT; ++c) if(pc[k].ch == c){ sz[c] += b; rc[c] += 1; }
+            }
+#pragma unroll
+            for(int c = 0; c < FQK_CH_COUNT; ++c) sizes[(size_t)c * n + i] = sz[c];
+        }
+#pragma unroll
+        for(int c = 0; c < FQK_CH_COUNT; ++c){
+            const uint32_t t = __reduce_add_sync(0xffffffffu, rc[c]);
+            if(lane == 0 && t) atomicAdd(&counters[c], t);
+        }
+        const uint32_t np_ = __reduce_add_sync(0xffffffffu, passed ? 1u : 0u);
+        if(lane == 0 && np_) atomicAdd(&counters[FQK_CH_COUNT], np_);
+    }
+}
+
+// ------------------------------------------------------------------ exclusive scans (one per channel)
+constexpr int SCAN_T = 256, SCAN_ITEMS = 8, SCAN_BLOCK = SCAN_T * SCAN_ITEMS;
+
+__device__ __forceinline__ uint64_t block_excl_scan(uint64_t v, uint64_t* total){     // exclusive scan of one value per thread
+    __shared__ uint64_t wsum[SCAN_T / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint64_t x = v;
+#pragma unroll
+    for(int d = 1; d < 32; d <<= 1){ const uint64_t y = __shfl_up_sync(0xffffffffu, x, d); if(lane >= d) x += y; }
+    if(lane == 31) wsum[w] = x;
+    __syncthreads();
+    uint64_t before = 0, all = 0;
+#pragma unroll
+    for(int k = 0; k < SCAN_T / 32; ++k){ if(k < w) before += wsum[k]; all += wsum[k]; }
+    __syncthreads();
+    if(total) *total = all;
+    return before + x - v;
+}
+// blocksum[ch][b] = sum of block b's items
+__global__ void k_scan_reduce(uint32_t n, const uint32_t* __restrict__ sizes, uint64_t* __restrict__ blocksum, uint32_t nblocks){
+    const uint32_t ch = blockIdx.y, b = blockIdx.x;
+    const uint32_t* s = sizes + (size_t)ch * n;
+    uint64_t v = 0;
+    for(int k = 0; k < SCAN_ITEMS; ++k){
+        const uint64_t i = (uint64_t)b * SCAN_BLOCK + (uint64_t)k * SCAN_T + threadIdx.x;
+        if(i < n) v += s[i];
+    }
+    uint64_t tot;
+    block_excl_scan(v, &tot);
+    if(threadIdx.x == 0) blocksum[(size_t)ch * nblocks + b] = tot;
+}
+// exclusive scan of the block sums of a channel (one block per channel), totals[ch] = bytes of the channel
+__global__ void k_scan_tops(uint64_t* __restrict__ blocksum, uint32_t nblocks, uint64_t* __restrict__ totals){
+    const uint32_t ch = blockIdx.x;
+    uint64_t* s = blocksum + (size_t)ch * nblocks;
+    uint64_t carry = 0;
+    for(uint32_t b0 = 0; b0 < nblocks; b0 += SCAN_T){
+        const uint32_t i = b0 + threadIdx.x;
+        const uint64_t v = i < nblocks ? s[i] : 0;
+        uint64_t tot;
+        const uint64_t ex = block_excl_scan(v, &tot);
+        if(i < nblocks) s[i] = carry + ex;
+        carry += tot;
+    }
+    if(threadIdx.x == 0) totals[ch] = carry;
+}
+// sizes -> offsets in place.  Offsets are 32 bit: the caller rejects channels of 4 GiB and more (totals are 64 bit)
+__global__ void k_scan_apply(uint32_t n, uint32_t* __restrict__ sizes, const uint64_t* __restrict__ blocksum, uint32_t nblocks){
+    const uint32_t ch = blockIdx.y, b = blockIdx.x;
+    uint32_t* s = sizes + (size_t)ch * n;
+    // thread t owns SCAN_ITEMS consecutive items
+    const uint64_t i0 = (uint64_t)b * SCAN_BLOCK + (uint64_t)threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS]; uint64_t sum = 0;
+#pragma unroll
+    for(int k = 0; k < SCAN_ITEMS; ++k){ v[k] = (i0 + k < n) ? s[i0 + k] : 0u; sum += v[k]; }
+    uint64_t run = blocksum[(size_t)ch * nblocks + b] + block_excl_scan(sum, nullptr);
+#pragma unroll
+    for(int k = 0; k < SCAN_ITEMS; ++k){ if(i0 + k < n) s[i0 + k] = (uint32_t)run; run += v[k]; }
+}
+
+// ------------------------------------------------------------------ copy
+__device__ __forceinline__ void put(char* dst, uint32_t& o, const char* src, uint32_t n, int lane){     // warp copy, advances o
+    for(uint32_t k = lane; k < n; k += 32) dst[o + k] = src[k];
+    o += n;
+}
+__device__ __forceinline__ void put_ch(char* dst, uint32_t& o, char c, int lane){ if(lane == 0) dst[o] = c; o += 1; }
+__device__ __forceinline__ void put_dec(char* dst, uint32_t& o, uint32_t v, int lane){
+    const uint32_t nd = dec_digits(v);
+    if(lane == 0){ uint32_t x = v; for(uint32_t k = 0; k < nd; ++k){ dst[o + nd - 1 - k] = (char)('0' + x % 10); x /= 10; } }
+    o += nd;
+}
+__device__ __forceinline__ char comp_base(char c){          // Seq::reverseComplement, src/seq.h:24-48
+    switch(c){ case 'A': case 'a': return 'T'; case 'T': case 't': return 'A'; case 'C': case 'c': return 'G';
+               case 'G': case 'g': return 'C'; default: return 'N'; }
+}
+
+__device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMate& m1, const TextMate& m2, uint32_t i,
+                            const fq_read_result& x1, const fq_read_result& x2, const fq_pair_result& pr, int lane){
+    if(p.kind == 2){
+        // OverlapAnalysis::merge: read1[0, len1) + revcomp(read2 view)[ol, ol + len2), qualities reversed alike
+        const char* name = m1.names + m1.name_off[i]; const uint32_t nl = m1.name_off[i + 1] - m1.name_off[i];
+        const char* strand = m1.strands + m1.strand_off[i]; const uint32_t sl = m1.strand_off[i + 1] - m1.strand_off[i];
+        const uint32_t len1 = pr.merge_len1, len2 = pr.merge_len2, ol = pr.ov2_len;
+        const uint32_t sp = first_space(name, nl);
+        if(sp < nl) put(dst, o, name, sp - 1, lane);
+        put(dst, o, "_merged_", 8, lane); put_dec(dst, o, len1, lane); put_ch(dst, o, '_', lane); put_dec(dst, o, len2, lane);
+        if(sp < nl) put(dst, o, name + sp, nl - sp, lane);
+        put_ch(dst, o, '\n', lane);
+        uint32_t s1, l1, s2, l2; view_of(x1, m1.len[i], s1, l1); view_of(x2, m2.len[i], s2, l2);
+        const char* a = m1.seq + m1.src[i] + s1; const char* aq = m1.qual + m1.src[i] + s1;
+        const char* b = m2.seq + m2.src[i] + s2; const char* bq = m2.qual + m2.src[i] + s2;
+        put(dst, o, a, len1, lane);
+        for(uint32_t t = lane; t < len2; t += 32) dst[o + t] = comp_base(b[l2 - 1 - ol - t]);
+        o += len2;
+        put_ch(dst, o, '\n', lane);
+        put(dst, o, strand, sl, lane); put_ch(dst, o, '\n', lane);
+        put(dst, o, aq, len1, lane);
+        for(uint32_t t = lane; t < len2; t += 32) dst[o + t] = bq[l2 - 1 - ol - t];
+        o += len2;
+        put_ch(dst, o, '\n', lane);
+        return;
+    }
+    const TextMate& m = p.kind ? m2 : m1;
+    const fq_read_result& x = p.kind ? x2 : x1;
+    uint32_t st, ln; view_of(x, m.len[i], st, ln);
+    put(dst, o, m.names + m.name_off[i], m.name_off[i + 1] - m.name_off[i], lane);
+    if(p.tag >= 0){ put_ch(dst, o, ' ', lane); put(dst, o, c_tags[p.tag], tag_len(p.tag), lane); }
+    put_ch(dst, o, '\n', lane);
+    put(dst, o, m.seq + m.src[i] + st, ln, lane); put_ch(dst, o, '\n', lane);
+    put(dst, o, m.strands + m.strand_off[i], m.strand_off[i + 1] - m.strand_off[i], lane); put_ch(dst, o, '\n', lane);
+    put(dst, o, m.qual + m.src[i] + st, ln, lane); put_ch(dst, o, '\n', lane);
+}
+
+__global__ void k_text_copy(bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* __restrict__ r1,
+                            const fq_read_result* __restrict__ r2, const fq_pair_result* __restrict__ rp,
+                            const uint32_t* __restrict__ offsets, TextOut out){
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for(uint32_t i = warp; i < n; i += nwarps){
+        Piece pc[2]; int np; bool passed;
+        const fq_read_result x1 = r1[i];
+        fq_read_result x2 = {}; fq_pair_result pr = {};
+        if(paired){ x2 = r2[i]; pr = rp[i]; np = route_pe(x1, x2, pr, writers, pc, passed); }
+        else np = route_se(x1, writers, pc, passed);
+        uint32_t used[FQK_CH_COUNT] = {0, 0, 0, 0, 0, 0, 0};          // a second piece of the same channel follows the first
+        for(int k = 0; k < np; ++k){
+            const int ch = pc[k].ch;
+            uint32_t u = 0;
+#pragma unroll
+            for(int c = 0; c < FQK_CH_COUNT; ++c) if(ch == c) u = used[c];
+            write_piece(pc[k], out.p[ch], offsets[(size_t)ch * n + i] + u, m1, m2, i, x1, x2, pr, lane);
+            const uint32_t b = piece_bytes(pc[k], m1, m2, i, x1, x2, pr);
+#pragma unroll
+            for(int c = 0; c < FQK_CH_COUNT; ++c) if(ch == c) used[c] += b;
+        }
+    }
+}
+
+// BaseCorrector::correctByOverlapAnalysis rewrote bases of the PACKED batch; the same edits on the staged characters
+__global__ void k_text_apply_edits(const fq_correction* __restrict__ edits, const uint32_t* __restrict__ n_edits, uint32_t cap,
+                                   char* seq1, char* qual1, const uint32_t* __restrict__ src1,
+                                   char* seq2, char* qual2, const uint32_t* __restrict__ src2){
+    const uint32_t n = min(*n_edits, cap);
+    for(uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x){
+        const fq_correction c = edits[e];
+        const bool m2 = (c.mate_base & 0x80) != 0;
+        const uint32_t at = (m2 ? src2 : src1)[c.pair] + c.pos;
+        (m2 ? seq2 : seq1)[at] = (char)(c.mate_base & 0x7F);
+        (m2 ? qual2 : qual1)[at] = (char)c.qual;
+    }
+}
+
+} // namespace
+
+// ------------------------------------------------------------------ launchers
+static int text_grid(uint32_t n, int per_block){ const long long g = ((long long)n + per_block - 1) / per_block; return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g)); }
+
+void text_launch_sizes(cudaStream_t st, bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* r1,
+                       const fq_read_result* r2, const fq_pair_result* rp, uint32_t* sizes, uint32_t* counters){
+    k_text_sizes<<<text_grid(n, 256), 256, 0, st>>>(paired, n, writers, m1, m2, r1, r2, rp, sizes, counters);
+}
+size_t text_scan_scratch_u64(uint32_t n){ return (size_t)FQK_CH_COUNT * (((size_t)n + SCAN_BLOCK - 1) / SCAN_BLOCK) + 8; }
+void text_launch_scan(cudaStream_t st, uint32_t n, uint32_t* sizes, uint64_t* totals, uint64_t* scratch){
+    const uint32_t nb = (uint32_t)(((size_t)n + SCAN_BLOCK - 1) / SCAN_BLOCK);
+    k_scan_reduce<<<dim3(nb, FQK_CH_COUNT), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
+    k_scan_tops<<<FQK_CH_COUNT, SCAN_T, 0, st>>>(scratch, nb, totals);
+    k_scan_apply<<<dim3(nb, FQK_CH_COUNT), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
+}
+void text_launch_copy(cudaStream_t st, bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* r1,
+                      const fq_read_result* r2, const fq_pair_result* rp, const uint32_t* offsets, TextOut out){
+    k_text_copy<<<text_grid(n, 8), 256, 0, st>>>(paired, n, writers, m1, m2, r1, r2, rp, offsets, out);
+}
+void text_launch_apply_edits(cudaStream_t st, const fq_correction* edits, const uint32_t* n_edits, uint32_t cap,
+                             char* seq1, char* qual1, const uint32_t* src1, char* seq2, char* qual2, const uint32_t* src2){
+    k_text_apply_edits<<<148, 256, 0, st>>>(edits, n_edits, cap, seq1, qual1, src1, seq2, qual2, src2);
+}

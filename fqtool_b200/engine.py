@@ -85,6 +85,48 @@ class Engine:
                                                   abi.ptr(out[2])), "fqk_process_pe_ascii")
         return out
 
+    # ---- text entry points: FASTQ records assembled on the device (fqk_process_*_text) ----
+    @staticmethod
+    def _text(rec, first_index):
+        """rec = (names, name_off, seq, qual, off, strands, strand_off) as uint8 / uint64 numpy arrays."""
+        names, noff, seq, qual, off, strands, soff = rec
+        keep = [np.ascontiguousarray(names), np.ascontiguousarray(noff, dtype=np.uint64), np.ascontiguousarray(seq),
+                np.ascontiguousarray(qual), np.ascontiguousarray(off, dtype=np.uint64), np.ascontiguousarray(strands),
+                np.ascontiguousarray(soff, dtype=np.uint64)]
+        b = abi.FqTextBatch()
+        b.reads.n_reads = len(keep[4]) - 1; b.reads.first_index = first_index
+        b.reads.off, b.reads.seq, b.reads.qual = abi.ptr(keep[4]), abi.ptr(keep[2]), abi.ptr(keep[3])
+        b.name_off, b.names, b.strand_off, b.strands = abi.ptr(keep[1]), abi.ptr(keep[0]), abi.ptr(keep[6]), abi.ptr(keep[5])
+        return b, keep
+
+    def _text_call(self, fn, args_before, nbytes_hint, writers, recs):
+        bufs = [np.zeros(max(nbytes_hint, 16), dtype=np.uint8) for _ in range(abi.CH_COUNT)]
+        outs = (abi.FqTextOut * abi.CH_COUNT)()
+        for ch in range(abi.CH_COUNT):
+            outs[ch].data = abi.ptr(bufs[ch]); outs[ch].cap = bufs[ch].nbytes
+        passed = C.c_uint64(0)
+        rc = fn(self.h, *args_before, writers, *recs, outs, C.byref(passed))
+        self._check(rc, "fqk_process_*_text")
+        return ([bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], [int(outs[ch].records) for ch in range(abi.CH_COUNT)],
+                int(passed.value))
+
+    def process_se_text(self, rec, writers=0, first_index=0):
+        """-> (text block per channel, records per channel, readPassed, records array)."""
+        b, keep = self._text(rec, first_index)
+        out = np.zeros(b.reads.n_reads, dtype=abi.READ_RESULT_DTYPE)
+        hint = int(len(keep[0]) + 2 * len(keep[2]) + len(keep[5]) + 40 * b.reads.n_reads + 64)
+        blocks, nrec, passed = self._text_call(self.lib.fqk_process_se_text, (C.byref(b),), hint, writers, (abi.ptr(out),))
+        return blocks, nrec, passed, out
+
+    def process_pe_text(self, rec1, rec2, writers=0, first_index=0):
+        b1, k1 = self._text(rec1, first_index); b2, k2 = self._text(rec2, first_index)
+        n = b1.reads.n_reads
+        out = (np.zeros(n, dtype=abi.READ_RESULT_DTYPE), np.zeros(n, dtype=abi.READ_RESULT_DTYPE), np.zeros(n, dtype=abi.PAIR_RESULT_DTYPE))
+        hint = int(sum(len(k[0]) + 2 * len(k[2]) + len(k[5]) for k in (k1, k2)) + 80 * n + 64)
+        blocks, nrec, passed = self._text_call(self.lib.fqk_process_pe_text, (C.byref(b1), C.byref(b2)), hint, writers,
+                                               (abi.ptr(out[0]), abi.ptr(out[1]), abi.ptr(out[2])))
+        return blocks, nrec, passed, out
+
     def submit_se(self, batch, out):
         """Pipelined fqk_process_se: returns a ticket; `batch` and `out` must stay alive until wait(ticket)."""
         b = batch.c_struct()

@@ -264,6 +264,49 @@ int  fqk_process_pe_ascii(fqk_ctx* ctx, const fq_ascii_batch* r1, const fq_ascii
                           fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp);
 
 /*
+ * Text entry points: device-side output compaction and FASTQ record assembly.  The host hands
+ * over what FqReader parsed (names, sequences, third lines, qualities as flat character buffers) and gets back, per
+ * output channel, ONE contiguous block of FASTQ text in input order: exactly the strings the reference's worker
+ * bodies build with Read::toString / toStringWithTag (src/read.h:166-176), the routing ladders of
+ * src/seprocessor.cpp:340-349 and src/peprocessor.cpp:353-429 and OverlapAnalysis::merge (src/overlapanalysis.cpp:
+ * 74-104, name quirk included).  The writer threads only pass the blocks on; no per-read string is built on the host.
+ * `writers` says which optional writers exist (the reference tests its WriterThread pointers).  outs[ch].data is a
+ * caller-owned (preferably pinned) buffer of outs[ch].cap bytes, or NULL for a channel the caller does not want;
+ * on return outs[ch].len / .records hold the bytes and records of the channel.  A channel that does not fit makes the
+ * call fail with FQK_E_LIMIT (outs[ch].len then holds the size needed).  The records (out / out1 / out2 / outp) are
+ * still returned when the pointers are not NULL: the adapter text tallies are keyed by strings on the host.
+ */
+#define FQK_CH_OUT1      0
+#define FQK_CH_OUT2      1
+#define FQK_CH_MERGED    2
+#define FQK_CH_FAILED    3
+#define FQK_CH_UNPAIRED1 4
+#define FQK_CH_UNPAIRED2 5
+#define FQK_CH_SINGLE    6      /* interleaved pairs for stdout (Options::outputToSTDOUT) */
+#define FQK_CH_COUNT     7
+#define FQK_W_FAILED     1u     /* mFailedWriter != NULL        */
+#define FQK_W_UNPAIRED1  2u     /* mUnPairedLeftWriter != NULL  */
+#define FQK_W_STDOUT     4u     /* Options::outputToSTDOUT      */
+typedef struct fq_text_batch {
+    fq_ascii_batch  reads;         /* sequence and quality characters            */
+    const uint64_t* name_off;      /* [n_reads + 1]                              */
+    const char*     names;         /* first lines (with the '@'), no newline     */
+    const uint64_t* strand_off;    /* [n_reads + 1]                              */
+    const char*     strands;       /* third lines ("+..."), no newline           */
+} fq_text_batch;
+typedef struct fq_text_out {
+    char*    data;                 /* caller-owned buffer, NULL = channel unused */
+    uint64_t cap;
+    uint64_t len;                  /* out: bytes written (or needed)             */
+    uint64_t records;              /* out: FASTQ records in the block            */
+} fq_text_out;
+int  fqk_process_se_text(fqk_ctx* ctx, const fq_text_batch* in, uint32_t writers, fq_read_result* out,
+                         fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed);
+int  fqk_process_pe_text(fqk_ctx* ctx, const fq_text_batch* r1, const fq_text_batch* r2, uint32_t writers,
+                         fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp,
+                         fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed);
+
+/*
  * Pipelined form of fqk_process_se for hosts that keep two packs in flight: fqk_submit_se enqueues
  * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's
  * records are in `out`.  The upload of pack k+1 overlaps the kernels and the download of pack k.

@@ -1,0 +1,82 @@
+"""Device-side output compaction and FASTQ record assembly (fqk_process_*_text): the text blocks
+per output channel, concatenated over packs, must be byte-identical to the files the WHOLE reference program writes
+(`fqtool_ref -w 1`, md5 in tests/golden/e2e_expected.json made by tests/golden/make_e2e.py) for the same command lines:
+plain, failed (tagged), unpaired and merged outputs, base correction included.  No per-read string work on the host."""
+import gzip
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from fqtool_b200 import abi
+from fqtool_b200.options import from_cli
+from tests.golden import make_e2e
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EXPECTED = json.load(open(os.path.join(HERE, "golden", "e2e_expected.json")))
+FQ = [os.path.join(HERE, "golden", "fq", f"r{i}.fq.gz") for i in (1, 2)]
+FILES = {"out1.fq": abi.CH_OUT1, "out2.fq": abi.CH_OUT2, "merged.fq": abi.CH_MERGED, "failed.fq": abi.CH_FAILED,
+         "un1.fq": abi.CH_UNPAIRED1, "un2.fq": abi.CH_UNPAIRED2}
+
+
+def parse_fastq(path):
+    """What FqReader holds (src/fqreader.cpp:90-195): four lines per record, kept as flat buffers + offsets."""
+    lines = gzip.open(path, "rb").read().split(b"\n")
+    recs = [lines[i:i + 4] for i in range(0, len(lines) - 3, 4)]
+    return recs
+
+
+def flat(recs, lo, hi):
+    def cat(k):
+        parts = [r[k] for r in recs[lo:hi]]
+        off = np.zeros(len(parts) + 1, dtype=np.uint64)
+        off[1:] = np.cumsum([len(p) for p in parts])
+        return np.frombuffer(b"".join(parts), dtype=np.uint8), off
+    names, noff = cat(0); seq, off = cat(1); strands, soff = cat(2); qual, _ = cat(3)
+    return names, noff, seq, qual, off, strands, soff
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(EXPECTED))
+def test_text_blocks_match_reference_files(case):
+    from fqtool_b200.engine import Engine
+    paired, flags = make_e2e.CASES[case]
+    o = from_cli(flags.split() + (["-I", "r2"] if paired else []))
+    o.maxCycles = 320
+    eng = Engine(o.to_params())
+    r1 = parse_fastq(FQ[0]); r2 = parse_fastq(FQ[1]) if paired else None
+    outs = make_e2e.outputs(case, paired, "")
+    writers = (abi.W_FAILED if "--failed_out" in outs else 0) | (abi.W_UNPAIRED1 if "--unpaired_read1" in outs else 0)
+    acc = [b""] * abi.CH_COUNT
+    nrec_total = [0] * abi.CH_COUNT
+    for lo in range(0, len(r1), 700):
+        hi = min(len(r1), lo + 700)
+        if paired:
+            blocks, nrec, passed, _ = eng.process_pe_text(flat(r1, lo, hi), flat(r2, lo, hi), writers, lo)
+        else:
+            blocks, nrec, passed, _ = eng.process_se_text(flat(r1, lo, hi), writers, lo)
+        for ch in range(abi.CH_COUNT):
+            acc[ch] += blocks[ch]; nrec_total[ch] += nrec[ch]
+    eng.close()
+    for name, want in EXPECTED[case]["files"].items():
+        ch = FILES[name]
+        assert hashlib.md5(acc[ch]).hexdigest() == want, f"{case}: {name} differs from the reference binary's output"
+        assert acc[ch].count(b"\n") == 4 * nrec_total[ch]
+
+
+@pytest.mark.gpu
+def test_text_buffer_too_small_reports_needed_size():
+    import ctypes as C
+    from fqtool_b200.engine import Engine
+    o = from_cli("-q".split()); o.maxCycles = 160
+    eng = Engine(o.to_params())
+    r1 = parse_fastq(FQ[0])
+    b, keep = eng._text(flat(r1, 0, 500), 0)
+    outs = (abi.FqTextOut * abi.CH_COUNT)()
+    small = np.zeros(64, dtype=np.uint8)
+    outs[abi.CH_OUT1].data = abi.ptr(small); outs[abi.CH_OUT1].cap = 64
+    rc = eng.lib.fqk_process_se_text(eng.h, C.byref(b), 0, None, outs, None)
+    assert rc == -6 and outs[abi.CH_OUT1].len > 64 and outs[abi.CH_OUT1].records > 0
+    eng.close()
