@@ -462,7 +462,7 @@ def main():
                    f"{n_host} distinct pinned host batches of {BATCH_READS} reads (already in the fq_batch layout; host packing is outside)"}
 
     # ---- the same through the ASCII entry point (FASTQ characters in, packing on the GPU) ----
-    e2e_ascii = None
+    e2e_ascii = e2e_text = None
     if not c["paired"]:
         from fqtool_b200 import batch as fbatch
         seq, qual, off = fbatch.unpack(hbs[0][0])
@@ -480,7 +480,39 @@ def main():
         e2e_ascii = {"value": world * reps * hbs[0][0].n * c["L"] / dta / 1e9, "unit": "Gbases/s",
                      "h2d_bytes_per_call": int(2 * len(seq) + 10 * hbs[0][0].n), "calls": reps,
                      "note": "fqk_process_se_ascii: FASTQ characters over PCIe (2 B/base), 2-bit packing by k_pack_ascii on the GPU"}
-        del pseq, pqual, areads, seq, qual, off
+        # ---- and with the FASTQ records assembled on the device (text in, text out) ----
+        import ctypes as C
+        n1 = hbs[0][0].n
+        digits = (np.arange(n1, dtype=np.int64)[:, None] // (10 ** np.arange(9, -1, -1, dtype=np.int64))[None, :] % 10 + 48).astype(np.uint8)
+        head, tail = np.frombuffer(b"@SIM:1:FCX:1:", dtype=np.uint8), np.frombuffer(b" 1:N:0:ATCACG", dtype=np.uint8)
+        names = np.concatenate([np.broadcast_to(head, (n1, len(head))), digits, np.broadcast_to(tail, (n1, len(tail)))], axis=1).reshape(-1)
+        nlen = len(head) + 10 + len(tail)
+        pin = lambda a: (lambda t: (t.numpy().__setitem__(slice(None), a), t)[1])(torch.empty(a.shape, dtype=torch.uint8, pin_memory=True))
+        pnames = pin(names); pstr = pin(np.full(n1, ord("+"), dtype=np.uint8))
+        noff = np.arange(n1 + 1, dtype=np.uint64) * np.uint64(nlen); soff = np.arange(n1 + 1, dtype=np.uint64)
+        tb, keep = eng._text((pnames.numpy(), noff, pseq.numpy(), pqual.numpy(), off, pstr.numpy(), soff), 0)
+        cap = int(len(names) + 2 * len(seq) + n1 * 8)
+        tout = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
+        touts = (abi.FqTextOut * abi.CH_COUNT)()
+        touts[abi.CH_OUT1].data = tout.data_ptr(); touts[abi.CH_OUT1].cap = cap
+        passed = C.c_uint64(0)
+
+        def text_call():
+            rc = eng.lib.fqk_process_se_text(eng.h, C.byref(tb), 0, None, touts, C.byref(passed))
+            assert rc == 0, eng.lib.fqk_last_error(eng.h)
+        text_call()
+        eng.reset(); ctx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            text_call()
+        eng.finalize(); ctx.barrier()
+        dtt = ctx.max_over_ranks(time.perf_counter() - t0)
+        e2e_text = {"value": world * reps * n1 * c["L"] / dtt / 1e9, "unit": "Gbases/s", "calls": reps,
+                    "h2d_bytes_per_call": int(2 * len(seq) + len(names) + n1 * (1 + 8 + 8 + 8)),
+                    "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len), "records_out": int(touts[abi.CH_OUT1].records),
+                    "note": "fqk_process_se_text: FASTQ text in (names, bases, qualities), trimmed FASTQ text of the passing reads out; "
+                            "packing, trimming, statistics and record assembly on the GPU, no per-read work on the host"}
+        del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout
     del hbs, hout, batches
     job.close(); del job, eng
     ctx.free()
@@ -526,7 +558,7 @@ def main():
                            "read_length": c["L"], "batches_per_step": nb, "batch_reads": BATCH_READS,
                            "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit / 1e9),
                            "impl": a.impl},
-                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "gpu_launches": main_rec["gpu_launches"],
+                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "e2e_text": e2e_text, "gpu_launches": main_rec["gpu_launches"],
                 "roofline": main_rec["roofline"], "finalize_ms": main_rec["finalize_ms"], "cpu_baseline": cpu_baseline,
                 "configs": extra or None, "scaling_cfg5": scaling_cfg5, "merge_check": mcheck}
         emit(line)
