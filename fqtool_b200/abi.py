@@ -78,6 +78,10 @@ class FqTextBatch(C.Structure):
                 ("strand_off", C.c_void_p), ("strands", C.c_void_p)]
 
 
+class FqRawBlock(C.Structure):
+    _fields_ = [("text", C.c_void_p), ("bytes", C.c_uint64), ("first_index", C.c_uint64)]
+
+
 class FqTextOut(C.Structure):
     _fields_ = [("data", C.c_void_p), ("cap", C.c_uint64), ("len", C.c_uint64), ("records", C.c_uint64)]
 
@@ -117,6 +121,7 @@ EXPORTS = [
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
     "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits", "fqk_process_se_text", "fqk_process_pe_text",
+    "fqk_process_se_fastq", "fqk_process_pe_fastq",
 ]
 
 _lib = None
@@ -165,6 +170,10 @@ def load():
     lib.fqk_process_se_text.argtypes = [vp, P(FqTextBatch), u32, vp, P(FqTextOut), P(u64)]; lib.fqk_process_se_text.restype = i32
     lib.fqk_process_pe_text.argtypes = [vp, P(FqTextBatch), P(FqTextBatch), u32, vp, vp, vp, P(FqTextOut), P(u64)]
     lib.fqk_process_pe_text.restype = i32
+    lib.fqk_process_se_fastq.argtypes = [vp, P(FqRawBlock), u32, vp, u32, P(FqTextOut), P(u64), P(u32), P(u64)]
+    lib.fqk_process_se_fastq.restype = i32
+    lib.fqk_process_pe_fastq.argtypes = [vp, P(FqRawBlock), P(FqRawBlock), u32, vp, vp, vp, u32, P(FqTextOut), P(u64), P(u32), P(u64), P(u64)]
+    lib.fqk_process_pe_fastq.restype = i32
     lib.fqk_prepass_kmer_counts.argtypes = [i32, vp, i32, i32, i32, vp]; lib.fqk_prepass_kmer_counts.restype = i32
     lib.fqk_prepass_seed_hits.argtypes = [i32, vp, i32, i32, i32, u32, vp, vp, u32, vp]; lib.fqk_prepass_seed_hits.restype = i32
     lib.fqk_host_free.argtypes = [vp]; lib.fqk_host_free.restype = None

@@ -71,6 +71,9 @@ struct fqk_ctx {
     std::vector<uint32_t> hsrc[2], hdst[2]; std::vector<uint16_t> hlen[2];
     // text entry points (fqk_process_*_text): names and third lines per mate, sizes/offsets, per-channel text blocks
     DevBuf tnames[2], tnoff[2], tstr[2], tsoff[2], tsizes, tscratch, ttot, tout[FQK_CH_COUNT];
+    // raw FASTQ blocks (fqk_process_*_fastq): the text, newline counts/positions, quality offsets, line lengths
+    DevBuf traw[2], tnlc[2], tnl[2], aqsrc[2], tnlen[2], tslen[2];
+    bool raw_mode = false;                    // the staged mates come from raw blocks (TextMate then points into traw)
     std::vector<uint32_t> hnoff[2], hsoff[2];
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
     uint64_t* d_dups = nullptr; uint32_t* d_counts = nullptr; uint8_t* d_gc = nullptr; bool dup_final = false;
@@ -281,6 +284,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(int i = 0; i < 2; ++i){ c->aseq[i].release(); c->aqual[i].release(); c->asrc[i].release(); }
     for(int i = 0; i < 2; ++i){ c->tnames[i].release(); c->tnoff[i].release(); c->tstr[i].release(); c->tsoff[i].release(); }
     c->tsizes.release(); c->tscratch.release(); c->ttot.release();
+    for(int i = 0; i < 2; ++i){ c->traw[i].release(); c->tnlc[i].release(); c->tnl[i].release(); c->aqsrc[i].release(); c->tnlen[i].release(); c->tslen[i].release(); }
     for(int i = 0; i < FQK_CH_COUNT; ++i) c->tout[i].release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
     cudaFree(c->d_dups); cudaFree(c->d_counts); cudaFree(c->d_gc);
@@ -405,6 +409,7 @@ static int err_bits(uint32_t e, const char** msg){
     if(e & 1){ *msg = "a read (or merged read) is longer than max_cycles"; return FQK_E_LIMIT; }
     if(e & 2){ *msg = "batch is not dense/ordered/16-byte aligned (see fq_batch)"; return FQK_E_INVALID; }
     if(e & 4){ *msg = "base outside {A,C,G,T,N} or quality >= 128 in an ASCII batch"; return FQK_E_ALPHABET; }
+    if(e & 8){ *msg = "raw block is not four-line FASTQ ('@' name, bases, '+' line, qualities of the same length)"; return FQK_E_INVALID; }
     return 0;
 }
 static int check_err_flag(fqk_ctx* c){
@@ -581,10 +586,16 @@ static int stage_text(fqk_ctx* c, int m, const fq_text_batch* b){
 }
 static TextMate text_mate(fqk_ctx* c, int m){
     TextMate t;
-    t.seq = (const char*)c->aseq[m].p; t.qual = (const char*)c->aqual[m].p; t.src = (const uint32_t*)c->asrc[m].p;
-    t.len = (const uint16_t*)c->st[m].len.p;
-    t.names = (const char*)c->tnames[m].p; t.name_off = (const uint32_t*)c->tnoff[m].p;
-    t.strands = (const char*)c->tstr[m].p; t.strand_off = (const uint32_t*)c->tsoff[m].p;
+    t.src = (const uint32_t*)c->asrc[m].p; t.len = (const uint16_t*)c->st[m].len.p;
+    t.name_off = (const uint32_t*)c->tnoff[m].p; t.strand_off = (const uint32_t*)c->tsoff[m].p;
+    if(c->raw_mode){                                   // all four lines of a record live in the raw text
+        const char* raw = (const char*)c->traw[m].p;
+        t.seq = t.qual = t.names = t.strands = raw;
+        t.qsrc = (const uint32_t*)c->aqsrc[m].p; t.name_len = (const uint32_t*)c->tnlen[m].p; t.strand_len = (const uint32_t*)c->tslen[m].p;
+    }else{
+        t.seq = (const char*)c->aseq[m].p; t.qual = (const char*)c->aqual[m].p; t.qsrc = nullptr;
+        t.names = (const char*)c->tnames[m].p; t.strands = (const char*)c->tstr[m].p; t.name_len = t.strand_len = nullptr;
+    }
     return t;
 }
 // records on the device -> per-channel text blocks in the caller's buffers
@@ -599,8 +610,8 @@ static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq
     uint32_t* counters = (uint32_t*)(totals + FQK_CH_COUNT);
     CU(cudaMemsetAsync(c->ttot.p, 0, 256, c->stream));
     if(paired && c->D.P.correction_enabled && c->corr.p)
-        text_launch_apply_edits(c->stream, (const fq_correction*)c->corr.p, c->maxlen2 + 2, c->corr_cap, (char*)c->aseq[0].p, (char*)c->aqual[0].p,
-                                m1.src, (char*)c->aseq[1].p, (char*)c->aqual[1].p, m2.src);
+        text_launch_apply_edits(c->stream, (const fq_correction*)c->corr.p, c->maxlen2 + 2, c->corr_cap, (char*)m1.seq, (char*)m1.qual,
+                                m1.src, m1.qsrc, (char*)m2.seq, (char*)m2.qual, m2.src, m2.qsrc);
     text_launch_sizes(c->stream, paired, n, writers, m1, m2, r1, r2, rp, (uint32_t*)c->tsizes.p, counters);
     text_launch_scan(c->stream, n, (uint32_t*)c->tsizes.p, totals, (uint64_t*)c->tscratch.p);
     c->launches += paired && c->D.P.correction_enabled ? 5 : 4;
@@ -637,6 +648,7 @@ extern "C" int fqk_process_se_text(fqk_ctx* c, const fq_text_batch* in, uint32_t
     const size_t n = in->reads.n_reads;
     if(n == 0) return 0;
     CU(cudaSetDevice(c->device));
+    c->raw_mode = false;
     int rc = stage_ascii(c, 0, &in->reads); if(rc) return rc;
     rc = stage_text(c, 0, in); if(rc) return rc;
     if(c->res1.ensure(n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
@@ -656,6 +668,7 @@ extern "C" int fqk_process_pe_text(fqk_ctx* c, const fq_text_batch* r1, const fq
     const size_t n = r1->reads.n_reads;
     if(n == 0) return 0;
     CU(cudaSetDevice(c->device));
+    c->raw_mode = false;
     int rc = stage_ascii(c, 0, &r1->reads); if(rc) return rc;
     rc = stage_ascii(c, 1, &r2->reads); if(rc) return rc;
     rc = stage_text(c, 0, r1); if(rc) return rc;
@@ -668,6 +681,118 @@ extern "C" int fqk_process_pe_text(fqk_ctx* c, const fq_text_batch* r1, const fq
     if(o2) CU(cudaMemcpyAsync(o2, c->res2.p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
     if(op) CU(cudaMemcpyAsync(op, c->resp.p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
     rc = text_finish(c, true, (uint32_t)n, writers, outs, read_passed); if(rc) return rc;
+    return check_err_flag(c);
+}
+
+
+// ---------------------------------------------------------------- raw FASTQ blocks
+// step 1: the block to the device, newlines counted and scanned; *lines = complete lines in the block
+static int fastq_lines(fqk_ctx* c, int m, const fq_raw_block* b, uint32_t* lines){
+    if(b->bytes > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "raw FASTQ block of 4 GiB or more: use smaller blocks");
+    const uint32_t nc = (uint32_t)((b->bytes + NL_CHUNK - 1) / NL_CHUNK);
+    if(c->traw[m].ensure(b->bytes + 64) || c->tnlc[m].ensure((size_t)nc * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(nc) * 8) || c->ttot.ensure(256))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    if(b->bytes) CU(cudaMemcpyAsync(c->traw[m].p, b->text, b->bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync((char*)c->traw[m].p + b->bytes, 0, 32, c->stream));          // the pack kernel reads whole words
+    fastq_launch_count(c->stream, (const char*)c->traw[m].p, b->bytes, (uint32_t*)c->tnlc[m].p);
+    text_launch_scan(c->stream, nc, (uint32_t*)c->tnlc[m].p, (uint64_t*)c->ttot.p, (uint64_t*)c->tscratch.p, 1);
+    c->launches += 4;
+    uint64_t nl = 0;
+    CU(cudaMemcpyAsync(&nl, c->ttot.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *lines = (uint32_t)nl;
+    return 0;
+}
+// step 2: records 0..n-1 of the block indexed, destination offsets by a device prefix sum, bases packed; *consumed = bytes of those records
+static int fastq_stage(fqk_ctx* c, int m, const fq_raw_block* b, uint32_t lines, uint32_t n, uint64_t* consumed){
+    StagedBatch& s = c->st[m];
+    *consumed = 0;
+    if(n == 0){ s.dev = DevBatch(); s.dev.n = 0; return 0; }
+    if(c->tnl[m].ensure((size_t)lines * 4 + 16) || c->asrc[m].ensure((size_t)n * 4 + 16) || c->aqsrc[m].ensure((size_t)n * 4 + 16) ||
+       s.len.ensure((size_t)n * 2 + 16) || s.off.ensure((size_t)n * 4 + 16) || c->tnoff[m].ensure((size_t)n * 4 + 16) || c->tnlen[m].ensure((size_t)n * 4 + 16) ||
+       c->tsoff[m].ensure((size_t)n * 4 + 16) || c->tslen[m].ensure((size_t)n * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(n) * 8))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    const char* raw = (const char*)c->traw[m].p;
+    uint32_t* misc = (uint32_t*)((uint64_t*)c->ttot.p + 8);                          // [0] longest read
+    CU(cudaMemsetAsync(c->ttot.p, 0, 256, c->stream));
+    fastq_launch_positions(c->stream, raw, b->bytes, (const uint32_t*)c->tnlc[m].p, (uint32_t*)c->tnl[m].p);
+    fastq_launch_index(c->stream, raw, (const uint32_t*)c->tnl[m].p, n, (uint32_t*)c->asrc[m].p, (uint32_t*)c->aqsrc[m].p, (uint16_t*)s.len.p,
+                       (uint32_t*)c->tnoff[m].p, (uint32_t*)c->tnlen[m].p, (uint32_t*)c->tsoff[m].p, (uint32_t*)c->tslen[m].p,
+                       (uint32_t*)s.off.p, misc, c->err);
+    text_launch_scan(c->stream, n, (uint32_t*)s.off.p, (uint64_t*)c->ttot.p, (uint64_t*)c->tscratch.p, 1);   // padded lengths -> offsets
+    c->launches += 5;
+    struct { uint64_t total; uint64_t pad[7]; uint32_t maxlen; } h;
+    uint32_t last_nl = 0;
+    CU(cudaMemcpyAsync(&h, c->ttot.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(&last_nl, (uint32_t*)c->tnl[m].p + (4 * (size_t)n - 1), 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *consumed = (uint64_t)last_nl + 1;
+    if(h.total > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "batch larger than 2^32 padded bases");
+    const uint64_t total = (h.total + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
+    if(s.b2.ensure(total / 4 + 16) || s.q.ensure(total + 16)) return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    if(total > h.total){
+        CU(cudaMemsetAsync((uint8_t*)s.q.p + h.total, 0, total - h.total, c->stream));
+        CU(cudaMemsetAsync((uint8_t*)s.b2.p + h.total / 4, 0, (total - h.total) / 4, c->stream));
+    }
+    k_pack_ascii<<<grid_for(c, n, 16, 8), 256, 0, c->stream>>>(n, raw, raw, (const uint32_t*)c->asrc[m].p, (const uint32_t*)s.off.p,
+        (const uint16_t*)s.len.p, (uint8_t*)s.b2.p, (uint8_t*)s.q.p, c->err, (const uint32_t*)c->aqsrc[m].p);
+    c->launches++;
+    s.dev.n = n; s.dev.first_index = b->first_index; s.dev.total = total;
+    s.dev.offsets = (const uint32_t*)s.off.p; s.dev.lengths = (const uint16_t*)s.len.p;
+    s.dev.bases2 = (const uint8_t*)s.b2.p; s.dev.qual = (const uint8_t*)s.q.p; s.dev.max_len = h.maxlen;
+    return 0;
+}
+
+extern "C" int fqk_process_se_fastq(fqk_ctx* c, const fq_raw_block* in, uint32_t writers, fq_read_result* out, uint32_t out_cap,
+                                    fq_text_out* outs, uint64_t* read_passed, uint32_t* n_reads, uint64_t* consumed){
+    if(!c || !in || (!in->text && in->bytes) || !outs || !n_reads || !consumed) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    if(read_passed) *read_passed = 0;
+    *n_reads = 0; *consumed = 0;
+    CU(cudaSetDevice(c->device));
+    c->raw_mode = true;
+    uint32_t lines = 0;
+    int rc = fastq_lines(c, 0, in, &lines); if(rc) return rc;
+    const uint32_t n = lines / 4;
+    if(n == 0) return 0;
+    if(out && out_cap < n) return fail(c, FQK_E_LIMIT, "record array smaller than the number of reads in the block");
+    rc = fastq_stage(c, 0, in, lines, n, consumed); if(rc) return rc;
+    if(c->res1.ensure((size_t)n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_se(c, c->st[0].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
+    if(out) CU(cudaMemcpyAsync(out, c->res1.p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    rc = text_finish(c, false, n, writers, outs, read_passed); if(rc) return rc;
+    *n_reads = n;
+    return check_err_flag(c);
+}
+
+extern "C" int fqk_process_pe_fastq(fqk_ctx* c, const fq_raw_block* in1, const fq_raw_block* in2, uint32_t writers, fq_read_result* o1,
+                                    fq_read_result* o2, fq_pair_result* op, uint32_t out_cap, fq_text_out* outs, uint64_t* read_passed,
+                                    uint32_t* n_pairs, uint64_t* consumed1, uint64_t* consumed2){
+    if(!c || !in1 || !in2 || (!in1->text && in1->bytes) || (!in2->text && in2->bytes) || !outs || !n_pairs || !consumed1 || !consumed2) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    if(read_passed) *read_passed = 0;
+    *n_pairs = 0; *consumed1 = *consumed2 = 0;
+    CU(cudaSetDevice(c->device));
+    c->raw_mode = true;
+    uint32_t l1 = 0, l2 = 0;
+    int rc = fastq_lines(c, 0, in1, &l1); if(rc) return rc;
+    rc = fastq_lines(c, 1, in2, &l2); if(rc) return rc;
+    const uint32_t n = std::min(l1, l2) / 4;                               // pairs go by position: as many as both blocks hold
+    if(n == 0) return 0;
+    if((o1 || o2 || op) && out_cap < n) return fail(c, FQK_E_LIMIT, "record arrays smaller than the number of pairs in the blocks");
+    rc = fastq_stage(c, 0, in1, l1, n, consumed1); if(rc) return rc;
+    rc = fastq_stage(c, 1, in2, l2, n, consumed2); if(rc) return rc;
+    if(c->res1.ensure((size_t)n * sizeof(fq_read_result)) || c->res2.ensure((size_t)n * sizeof(fq_read_result)) ||
+       c->resp.ensure((size_t)n * sizeof(fq_pair_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_pe(c, c->st[0].dev, c->st[1].dev, (fq_read_result*)c->res1.p, (fq_read_result*)c->res2.p, (fq_pair_result*)c->resp.p);
+    if(rc) return rc;
+    if(o1) CU(cudaMemcpyAsync(o1, c->res1.p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    if(o2) CU(cudaMemcpyAsync(o2, c->res2.p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    if(op) CU(cudaMemcpyAsync(op, c->resp.p, (size_t)n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->stream));
+    rc = text_finish(c, true, n, writers, outs, read_passed); if(rc) return rc;
+    *n_pairs = n;
     return check_err_flag(c);
 }
 

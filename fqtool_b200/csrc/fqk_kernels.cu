@@ -500,24 +500,29 @@ __device__ __forceinline__ uint32_t eq_bytes(uint32_t v, uint32_t pat){         
 __global__ void __launch_bounds__(256) k_pack_ascii(uint32_t n, const char* __restrict__ seq, const char* __restrict__ qual,
                                                      const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
                                                      const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
-                                                     uint8_t* __restrict__ qout, uint32_t* __restrict__ err){
+                                                     uint8_t* __restrict__ qout, uint32_t* __restrict__ err,
+                                                     const uint32_t* __restrict__ qsrc_off){
+    // qsrc_off: where the quality characters of read r start when they do not sit at the same offset as its bases (raw
+    // FASTQ blocks: both lines live in one text buffer); nullptr = src_off
     const int lane = threadIdx.x & 15, warps = blockDim.x >> 4;                           // "warp" = half-warp here
     const uint32_t* s32 = reinterpret_cast<const uint32_t*>(seq);
     const uint32_t* q32 = reinterpret_cast<const uint32_t*>(qual);
     uint32_t bad = 0;
     for(uint32_t r = blockIdx.x * warps + (threadIdx.x >> 4); r < n; r += gridDim.x * warps){
         const uint32_t so = src_off[r], dof = dst_off[r], len = lengths[r];
+        const uint32_t qo = qsrc_off ? qsrc_off[r] : so;
         const uint32_t groups = ((len + 15) >> 4) << 2;
-        const uint32_t sh = 8u * (so & 3u);
+        const uint32_t sh = 8u * (so & 3u), qsh = 8u * (qo & 3u);
         for(uint32_t g = lane; g < groups; g += 16){
             const uint32_t i0 = 4u * g;
             uint32_t q = 0, code = 0;
             if(i0 < len){
-                const uint32_t w = (so + i0) >> 2;
-                const uint32_t a0 = s32[w], b0 = q32[w];
+                const uint32_t w = (so + i0) >> 2, qw = (qo + i0) >> 2;
+                const uint32_t a0 = s32[w], b0 = q32[qw];
                 uint32_t a1 = 0, b1 = 0;
-                if(sh){ a1 = s32[w + 1]; b1 = q32[w + 1]; }
-                const uint32_t sv = __funnelshift_r(a0, a1, sh), qv = __funnelshift_r(b0, b1, sh);
+                if(sh) a1 = s32[w + 1];
+                if(qsh) b1 = q32[qw + 1];
+                const uint32_t sv = __funnelshift_r(a0, a1, sh), qv = __funnelshift_r(b0, b1, qsh);
                 const uint32_t nv = len - i0;
                 const uint32_t vm = nv >= 4u ? 0xFFFFFFFFu : ((1u << (8u * nv)) - 1u);
                 const uint32_t hv = vm & 0x80808080u;

@@ -20,4 +20,4 @@ __global__ void k_dup_finish(uint64_t bins, const unsigned long long* tab128, co
 __global__ void k_pack_ascii(uint32_t n, const char* __restrict__ seq, const char* __restrict__ qual,
                              const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
                              const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
-                             uint8_t* __restrict__ qout, uint32_t* __restrict__ err);
+                             uint8_t* __restrict__ qout, uint32_t* __restrict__ err, const uint32_t* __restrict__ qsrc_off = nullptr);

@@ -80,14 +80,14 @@ __device__ __forceinline__ uint32_t merged_name_len(const char* name, uint32_t n
 __device__ __forceinline__ uint32_t piece_bytes(const Piece& p, const TextMate& m1, const TextMate& m2, uint32_t i,
                                                 const fq_read_result& x1, const fq_read_result& x2, const fq_pair_result& pr){
     if(p.kind == 2){
-        const uint32_t nl = m1.name_off[i + 1] - m1.name_off[i], sl = m1.strand_off[i + 1] - m1.strand_off[i];
+        const uint32_t nl = m1.nlen(i), sl = m1.slen(i);
         const uint32_t L = (uint32_t)pr.merge_len1 + pr.merge_len2;
         return merged_name_len(m1.names + m1.name_off[i], nl, pr.merge_len1, pr.merge_len2) + 1 + L + 1 + sl + 1 + L + 1;
     }
     const TextMate& m = p.kind ? m2 : m1;
     const fq_read_result& x = p.kind ? x2 : x1;
     uint32_t st, ln; view_of(x, m.len[i], st, ln);
-    const uint32_t nl = m.name_off[i + 1] - m.name_off[i], sl = m.strand_off[i + 1] - m.strand_off[i];
+    const uint32_t nl = m.nlen(i), sl = m.slen(i);
     return nl + (p.tag >= 0 ? 1 + tag_len(p.tag) : 0) + 1 + ln + 1 + sl + 1 + ln + 1;
 }
 
@@ -204,8 +204,8 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
                             const fq_read_result& x1, const fq_read_result& x2, const fq_pair_result& pr, int lane){
     if(p.kind == 2){
         // OverlapAnalysis::merge: read1[0, len1) + revcomp(read2 view)[ol, ol + len2), qualities reversed alike
-        const char* name = m1.names + m1.name_off[i]; const uint32_t nl = m1.name_off[i + 1] - m1.name_off[i];
-        const char* strand = m1.strands + m1.strand_off[i]; const uint32_t sl = m1.strand_off[i + 1] - m1.strand_off[i];
+        const char* name = m1.names + m1.name_off[i]; const uint32_t nl = m1.nlen(i);
+        const char* strand = m1.strands + m1.strand_off[i]; const uint32_t sl = m1.slen(i);
         const uint32_t len1 = pr.merge_len1, len2 = pr.merge_len2, ol = pr.ov2_len;
         const uint32_t sp = first_space(name, nl);
         if(sp < nl) put(dst, o, name, sp - 1, lane);
@@ -213,8 +213,8 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
         if(sp < nl) put(dst, o, name + sp, nl - sp, lane);
         put_ch(dst, o, '\n', lane);
         uint32_t s1, l1, s2, l2; view_of(x1, m1.len[i], s1, l1); view_of(x2, m2.len[i], s2, l2);
-        const char* a = m1.seq + m1.src[i] + s1; const char* aq = m1.qual + m1.src[i] + s1;
-        const char* b = m2.seq + m2.src[i] + s2; const char* bq = m2.qual + m2.src[i] + s2;
+        const char* a = m1.seq + m1.src[i] + s1; const char* aq = m1.qual + m1.qoff(i) + s1;
+        const char* b = m2.seq + m2.src[i] + s2; const char* bq = m2.qual + m2.qoff(i) + s2;
         put(dst, o, a, len1, lane);
         for(uint32_t t = lane; t < len2; t += 32) dst[o + t] = comp_base(b[l2 - 1 - ol - t]);
         o += len2;
@@ -229,12 +229,12 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
     const TextMate& m = p.kind ? m2 : m1;
     const fq_read_result& x = p.kind ? x2 : x1;
     uint32_t st, ln; view_of(x, m.len[i], st, ln);
-    put(dst, o, m.names + m.name_off[i], m.name_off[i + 1] - m.name_off[i], lane);
+    put(dst, o, m.names + m.name_off[i], m.nlen(i), lane);
     if(p.tag >= 0){ put_ch(dst, o, ' ', lane); put(dst, o, c_tags[p.tag], tag_len(p.tag), lane); }
     put_ch(dst, o, '\n', lane);
     put(dst, o, m.seq + m.src[i] + st, ln, lane); put_ch(dst, o, '\n', lane);
-    put(dst, o, m.strands + m.strand_off[i], m.strand_off[i + 1] - m.strand_off[i], lane); put_ch(dst, o, '\n', lane);
-    put(dst, o, m.qual + m.src[i] + st, ln, lane); put_ch(dst, o, '\n', lane);
+    put(dst, o, m.strands + m.strand_off[i], m.slen(i), lane); put_ch(dst, o, '\n', lane);
+    put(dst, o, m.qual + m.qoff(i) + st, ln, lane); put_ch(dst, o, '\n', lane);
 }
 
 __global__ void k_text_copy(bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* __restrict__ r1,
@@ -264,16 +264,68 @@ __global__ void k_text_copy(bool paired, uint32_t n, uint32_t writers, TextMate 
 
 // BaseCorrector::correctByOverlapAnalysis rewrote bases of the PACKED batch; the same edits on the staged characters
 __global__ void k_text_apply_edits(const fq_correction* __restrict__ edits, const uint32_t* __restrict__ n_edits, uint32_t cap,
-                                   char* seq1, char* qual1, const uint32_t* __restrict__ src1,
-                                   char* seq2, char* qual2, const uint32_t* __restrict__ src2){
+                                   char* seq1, char* qual1, const uint32_t* __restrict__ src1, const uint32_t* __restrict__ qsrc1,
+                                   char* seq2, char* qual2, const uint32_t* __restrict__ src2, const uint32_t* __restrict__ qsrc2){
     const uint32_t n = min(*n_edits, cap);
     for(uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x){
         const fq_correction c = edits[e];
         const bool m2 = (c.mate_base & 0x80) != 0;
-        const uint32_t at = (m2 ? src2 : src1)[c.pair] + c.pos;
-        (m2 ? seq2 : seq1)[at] = (char)(c.mate_base & 0x7F);
-        (m2 ? qual2 : qual1)[at] = (char)c.qual;
+        (m2 ? seq2 : seq1)[(m2 ? src2 : src1)[c.pair] + c.pos] = (char)(c.mate_base & 0x7F);
+        (m2 ? qual2 : qual1)[(m2 ? qsrc2 : qsrc1)[c.pair] + c.pos] = (char)c.qual;
     }
+}
+
+// ------------------------------------------------------------------ raw FASTQ blocks: the newline scan on the device
+// FqReader::getLine (src/fqreader.cpp:90-148) walks the decompressed text byte by byte.  Here: newlines are counted
+// per 2 KiB chunk, the counts are scanned, every chunk writes the positions of its newlines, and record r is lines
+// 4r .. 4r+3 (name, sequence, third line, quality; a trailing '\r' is dropped as clearLineBreaks does).  The reference
+// also skips stray lines that do not start with '@' (src/fqreader.cpp:167-170); a block that needs that is refused
+// (error bit 8): the GPU path takes well-formed four-line FASTQ only.
+__device__ __forceinline__ uint32_t nl_in8(const char* text, uint64_t bytes, uint64_t at, uint32_t& mask){
+    mask = 0;
+#pragma unroll
+    for(int k = 0; k < 8; ++k) if(at + k < bytes && text[at + k] == '\n') mask |= 1u << k;
+    return (uint32_t)__popc(mask);
+}
+__global__ void k_nl_count(const char* __restrict__ text, uint64_t bytes, uint32_t* __restrict__ counts){
+    const uint64_t at = (uint64_t)blockIdx.x * NL_CHUNK + threadIdx.x * 8u;
+    uint32_t m; const uint32_t c = nl_in8(text, bytes, at, m);
+    uint64_t tot;
+    block_excl_scan(c, &tot);
+    if(threadIdx.x == 0) counts[blockIdx.x] = (uint32_t)tot;
+}
+__global__ void k_nl_positions(const char* __restrict__ text, uint64_t bytes, const uint32_t* __restrict__ chunk_off, uint32_t* __restrict__ nlpos){
+    const uint64_t at = (uint64_t)blockIdx.x * NL_CHUNK + threadIdx.x * 8u;
+    uint32_t m; const uint32_t c = nl_in8(text, bytes, at, m);
+    uint32_t o = chunk_off[blockIdx.x] + (uint32_t)block_excl_scan(c, nullptr);
+    while(m){ const int k = __ffs((int)m) - 1; m &= m - 1; nlpos[o++] = (uint32_t)(at + k); }
+}
+__global__ void k_fastq_index(const char* __restrict__ text, const uint32_t* __restrict__ nlpos, uint32_t n, uint32_t* __restrict__ src_seq,
+                              uint32_t* __restrict__ src_qual, uint16_t* __restrict__ len, uint32_t* __restrict__ name_off,
+                              uint32_t* __restrict__ name_len, uint32_t* __restrict__ strand_off, uint32_t* __restrict__ strand_len,
+                              uint32_t* __restrict__ padlen, uint32_t* __restrict__ misc, uint32_t* __restrict__ err){
+    uint32_t mx = 0, bad = 0;
+    for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x){
+        uint32_t s[4], e[4];
+#pragma unroll
+        for(int k = 0; k < 4; ++k){
+            const uint32_t li = 4u * r + k;
+            s[k] = li ? nlpos[li - 1] + 1u : 0u;
+            e[k] = nlpos[li];
+            if(e[k] > s[k] && text[e[k] - 1] == '\r') --e[k];
+        }
+        const uint32_t l = e[1] - s[1];
+        if(e[0] == s[0] || text[s[0]] != '@' || e[2] == s[2] || text[s[2]] != '+' || e[3] - s[3] != l) bad |= 8u;
+        if(l > FQK_MAX_READ_LEN){ bad |= 1u; }
+        const uint32_t lc = min(l, (uint32_t)FQK_MAX_READ_LEN);
+        src_seq[r] = s[1]; src_qual[r] = s[3]; len[r] = (uint16_t)lc;
+        name_off[r] = s[0]; name_len[r] = e[0] - s[0]; strand_off[r] = s[2]; strand_len[r] = e[2] - s[2];
+        padlen[r] = (lc + FQK_PAD - 1u) / FQK_PAD * FQK_PAD;
+        mx = max(mx, lc);
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    bad = __reduce_or_sync(0xffffffffu, bad);
+    if((threadIdx.x & 31) == 0){ if(mx) atomicMax(&misc[0], mx); if(bad) atomicOr(err, bad); }
 }
 
 } // namespace
@@ -286,17 +338,34 @@ void text_launch_sizes(cudaStream_t st, bool paired, uint32_t n, uint32_t writer
     k_text_sizes<<<text_grid(n, 256), 256, 0, st>>>(paired, n, writers, m1, m2, r1, r2, rp, sizes, counters);
 }
 size_t text_scan_scratch_u64(uint32_t n){ return (size_t)FQK_CH_COUNT * (((size_t)n + SCAN_BLOCK - 1) / SCAN_BLOCK) + 8; }
-void text_launch_scan(cudaStream_t st, uint32_t n, uint32_t* sizes, uint64_t* totals, uint64_t* scratch){
+void text_launch_scan(cudaStream_t st, uint32_t n, uint32_t* sizes, uint64_t* totals, uint64_t* scratch, int nch){
     const uint32_t nb = (uint32_t)(((size_t)n + SCAN_BLOCK - 1) / SCAN_BLOCK);
-    k_scan_reduce<<<dim3(nb, FQK_CH_COUNT), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
-    k_scan_tops<<<FQK_CH_COUNT, SCAN_T, 0, st>>>(scratch, nb, totals);
-    k_scan_apply<<<dim3(nb, FQK_CH_COUNT), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
+    if(n == 0){ cudaMemsetAsync(totals, 0, (size_t)nch * 8, st); return; }
+    k_scan_reduce<<<dim3(nb, nch), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
+    k_scan_tops<<<nch, SCAN_T, 0, st>>>(scratch, nb, totals);
+    k_scan_apply<<<dim3(nb, nch), SCAN_T, 0, st>>>(n, sizes, scratch, nb);
 }
 void text_launch_copy(cudaStream_t st, bool paired, uint32_t n, uint32_t writers, TextMate m1, TextMate m2, const fq_read_result* r1,
                       const fq_read_result* r2, const fq_pair_result* rp, const uint32_t* offsets, TextOut out){
     k_text_copy<<<text_grid(n, 8), 256, 0, st>>>(paired, n, writers, m1, m2, r1, r2, rp, offsets, out);
 }
 void text_launch_apply_edits(cudaStream_t st, const fq_correction* edits, const uint32_t* n_edits, uint32_t cap,
-                             char* seq1, char* qual1, const uint32_t* src1, char* seq2, char* qual2, const uint32_t* src2){
-    k_text_apply_edits<<<148, 256, 0, st>>>(edits, n_edits, cap, seq1, qual1, src1, seq2, qual2, src2);
+                             char* seq1, char* qual1, const uint32_t* src1, const uint32_t* qsrc1,
+                             char* seq2, char* qual2, const uint32_t* src2, const uint32_t* qsrc2){
+    k_text_apply_edits<<<148, 256, 0, st>>>(edits, n_edits, cap, seq1, qual1, src1, qsrc1 ? qsrc1 : src1, seq2, qual2, src2, qsrc2 ? qsrc2 : src2);
+}
+
+void fastq_launch_count(cudaStream_t st, const char* text, uint64_t bytes, uint32_t* counts){
+    const uint32_t nc = (uint32_t)((bytes + NL_CHUNK - 1) / NL_CHUNK);
+    if(nc) k_nl_count<<<nc, NL_CHUNK / 8, 0, st>>>(text, bytes, counts);
+}
+void fastq_launch_positions(cudaStream_t st, const char* text, uint64_t bytes, const uint32_t* chunk_off, uint32_t* nlpos){
+    const uint32_t nc = (uint32_t)((bytes + NL_CHUNK - 1) / NL_CHUNK);
+    if(nc) k_nl_positions<<<nc, NL_CHUNK / 8, 0, st>>>(text, bytes, chunk_off, nlpos);
+}
+void fastq_launch_index(cudaStream_t st, const char* text, const uint32_t* nlpos, uint32_t n, uint32_t* src_seq, uint32_t* src_qual,
+                        uint16_t* len, uint32_t* name_off, uint32_t* name_len, uint32_t* strand_off, uint32_t* strand_len,
+                        uint32_t* padlen, uint32_t* misc, uint32_t* err){
+    if(n) k_fastq_index<<<text_grid(n, 256), 256, 0, st>>>(text, nlpos, n, src_seq, src_qual, len, name_off, name_len, strand_off, strand_len,
+                                                         padlen, misc, err);
 }

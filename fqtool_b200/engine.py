@@ -127,6 +127,34 @@ class Engine:
                                                (abi.ptr(out[0]), abi.ptr(out[1]), abi.ptr(out[2])))
         return blocks, nrec, passed, out
 
+    # ---- raw FASTQ blocks: decompressed text in, FASTQ text out (fqk_process_*_fastq) ----
+    def _fastq_outs(self, nbytes):
+        bufs = [np.zeros(max(nbytes, 16), dtype=np.uint8) for _ in range(abi.CH_COUNT)]
+        outs = (abi.FqTextOut * abi.CH_COUNT)()
+        for ch in range(abi.CH_COUNT):
+            outs[ch].data = abi.ptr(bufs[ch]); outs[ch].cap = bufs[ch].nbytes
+        return bufs, outs
+
+    def process_se_fastq(self, text, writers=0, first_index=0):
+        """text: bytes / uint8 array of a decompressed FASTQ block -> (blocks per channel, reads, bytes consumed, readPassed)."""
+        t = np.frombuffer(bytes(text), dtype=np.uint8) if not isinstance(text, np.ndarray) else text
+        b = abi.FqRawBlock(); b.text = abi.ptr(t) if len(t) else None; b.bytes = len(t); b.first_index = first_index
+        bufs, outs = self._fastq_outs(len(t) + 64 * (len(t) // 8 + 1))
+        passed, n, used = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0)
+        self._check(self.lib.fqk_process_se_fastq(self.h, C.byref(b), writers, None, 0, outs, C.byref(passed), C.byref(n), C.byref(used)),
+                    "fqk_process_se_fastq")
+        return [bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], n.value, used.value, int(passed.value)
+
+    def process_pe_fastq(self, text1, text2, writers=0, first_index=0):
+        t1 = np.frombuffer(bytes(text1), dtype=np.uint8); t2 = np.frombuffer(bytes(text2), dtype=np.uint8)
+        b1 = abi.FqRawBlock(); b1.text = abi.ptr(t1) if len(t1) else None; b1.bytes = len(t1); b1.first_index = first_index
+        b2 = abi.FqRawBlock(); b2.text = abi.ptr(t2) if len(t2) else None; b2.bytes = len(t2); b2.first_index = first_index
+        bufs, outs = self._fastq_outs(len(t1) + len(t2) + 64 * ((len(t1) + len(t2)) // 8 + 1))
+        passed, n, u1, u2 = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0), C.c_uint64(0)
+        self._check(self.lib.fqk_process_pe_fastq(self.h, C.byref(b1), C.byref(b2), writers, None, None, None, 0, outs, C.byref(passed),
+                                                  C.byref(n), C.byref(u1), C.byref(u2)), "fqk_process_pe_fastq")
+        return [bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], n.value, (u1.value, u2.value), int(passed.value)
+
     def submit_se(self, batch, out):
         """Pipelined fqk_process_se: returns a ticket; `batch` and `out` must stay alive until wait(ticket)."""
         b = batch.c_struct()

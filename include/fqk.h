@@ -307,6 +307,29 @@ int  fqk_process_pe_text(fqk_ctx* ctx, const fq_text_batch* r1, const fq_text_ba
                          fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed);
 
 /*
+ * Raw FASTQ entry points: the host hands over the DECOMPRESSED TEXT of a FASTQ block as it
+ * comes out of gzread and gets FASTQ text back; the newline scan of FqReader::getLine / FqReader::read
+ * (src/fqreader.cpp:90-195), the packing, the hot path and the record assembly all run on the device.  Record r is
+ * lines 4r .. 4r+3 of the block ('\r' before the newline is dropped); a trailing incomplete record is left alone and
+ * *consumed says how many bytes the processed records took, so the caller carries the rest into its next block.
+ * For pairs the two blocks are matched by position and min(records1, records2) pairs are processed.  Blocks that are
+ * not well-formed four-line FASTQ ('@' name, '+' third line, equal lengths) are refused with FQK_E_INVALID: the
+ * reference's skipping of stray lines (src/fqreader.cpp:167-170) is not reproduced.  out / out1 / out2 / outp may be
+ * NULL; when given they must hold out_cap >= records entries.
+ */
+typedef struct fq_raw_block {
+    const char* text;              /* decompressed FASTQ text (preferably pinned)  */
+    uint64_t    bytes;
+    uint64_t    first_index;       /* global index of the block's first read       */
+} fq_raw_block;
+int  fqk_process_se_fastq(fqk_ctx* ctx, const fq_raw_block* in, uint32_t writers, fq_read_result* out, uint32_t out_cap,
+                          fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed, uint32_t* n_reads, uint64_t* consumed);
+int  fqk_process_pe_fastq(fqk_ctx* ctx, const fq_raw_block* in1, const fq_raw_block* in2, uint32_t writers,
+                          fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp, uint32_t out_cap,
+                          fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed, uint32_t* n_pairs,
+                          uint64_t* consumed1, uint64_t* consumed2);
+
+/*
  * Pipelined form of fqk_process_se for hosts that keep two packs in flight: fqk_submit_se enqueues
  * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's
  * records are in `out`.  The upload of pack k+1 overlaps the kernels and the download of pack k.

@@ -80,3 +80,67 @@ def test_text_buffer_too_small_reports_needed_size():
     rc = eng.lib.fqk_process_se_text(eng.h, C.byref(b), 0, None, outs, None)
     assert rc == -6 and outs[abi.CH_OUT1].len > 64 and outs[abi.CH_OUT1].records > 0
     eng.close()
+
+
+# ---------------------------------------------------------------- raw FASTQ blocks
+def _stream_fastq(eng, paired, texts, writers, block):
+    """Feed decompressed text in blocks cut at ARBITRARY byte positions; the unconsumed tail is carried over."""
+    acc = [b""] * abi.CH_COUNT
+    pos = [0, 0]; first = 0
+    while True:
+        chunk = [t[p:p + block] for t, p in zip(texts, pos)]
+        if paired:
+            blocks, n, used, _ = eng.process_pe_fastq(chunk[0], chunk[1], writers, first)
+        else:
+            blocks, n, u, _ = eng.process_se_fastq(chunk[0], writers, first)
+            used = (u,)
+        for ch in range(abi.CH_COUNT):
+            acc[ch] += blocks[ch]
+        first += n
+        for k, u in enumerate(used):
+            pos[k] += u
+        if n == 0:
+            assert all(len(c) < block for c in chunk), "a block without one complete record: enlarge the block"
+            break
+    return acc, first
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(EXPECTED))
+def test_raw_fastq_blocks_match_reference_files(case):
+    """Decompressed FASTQ text in, FASTQ text out: newline scan, packing, hot path and record assembly on the device."""
+    from fqtool_b200.engine import Engine
+    paired, flags = make_e2e.CASES[case]
+    o = from_cli(flags.split() + (["-I", "r2"] if paired else []))
+    o.maxCycles = 320
+    eng = Engine(o.to_params())
+    texts = [gzip.open(f, "rb").read() for f in (FQ if paired else FQ[:1])]
+    outs = make_e2e.outputs(case, paired, "")
+    writers = (abi.W_FAILED if "--failed_out" in outs else 0) | (abi.W_UNPAIRED1 if "--unpaired_read1" in outs else 0)
+    acc, n = _stream_fastq(eng, paired, texts, writers, 250_007)
+    eng.close()
+    assert n == 2000
+    for name, want in EXPECTED[case]["files"].items():
+        assert hashlib.md5(acc[FILES[name]]).hexdigest() == want, f"{case}: {name} differs from the reference binary's output"
+
+
+@pytest.mark.gpu
+def test_raw_fastq_crlf_and_malformed():
+    from fqtool_b200.engine import Engine, FqkError
+    o = from_cli("-q --enable_cut_tail".split()); o.maxCycles = 160
+    text = gzip.open(FQ[0], "rb").read()
+    eng = Engine(o.to_params())
+    want, n, used, passed = eng.process_se_fastq(text)
+    assert n == 2000 and used == len(text) and passed == want[abi.CH_OUT1].count(b"\n") // 4
+    got, n2, used2, _ = eng.process_se_fastq(text.replace(b"\n", b"\r\n"))      # FqReader::getLine drops the '\r' too
+    assert n2 == 2000 and got[abi.CH_OUT1] == want[abi.CH_OUT1]
+    part, n3, used3, _ = eng.process_se_fastq(text[:100_000])                    # ends inside a record
+    assert 0 < n3 < 2000 and text[used3 - 1:used3] == b"\n" and want[abi.CH_OUT1].startswith(part[abi.CH_OUT1])
+    assert eng.process_se_fastq(b"")[1] == 0
+    eng.close()
+    lines = text.split(b"\n")
+    lines[6] = b"-"                                                              # third line of the second record
+    eng = Engine(o.to_params())
+    with pytest.raises(FqkError):
+        eng.process_se_fastq(b"\n".join(lines))
+    eng.close()
