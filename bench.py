@@ -462,7 +462,7 @@ def main():
                    f"{n_host} distinct pinned host batches of {BATCH_READS} reads (already in the fq_batch layout; host packing is outside)"}
 
     # ---- the same through the ASCII entry point (FASTQ characters in, packing on the GPU) ----
-    e2e_ascii = e2e_text = None
+    e2e_ascii = e2e_text = e2e_fastq = None
     if not c["paired"]:
         from fqtool_b200 import batch as fbatch
         seq, qual, off = fbatch.unpack(hbs[0][0])
@@ -512,7 +512,33 @@ def main():
                     "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len), "records_out": int(touts[abi.CH_OUT1].records),
                     "note": "fqk_process_se_text: FASTQ text in (names, bases, qualities), trimmed FASTQ text of the passing reads out; "
                             "packing, trimming, statistics and record assembly on the GPU, no per-read work on the host"}
-        del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout
+        # ---- and from the decompressed FASTQ TEXT itself (newline scan on the device too) ----
+        L1 = c["L"]
+        rec_bytes = nlen + 1 + L1 + 1 + 2 + L1 + 1
+        traw = torch.empty(n1 * rec_bytes, dtype=torch.uint8, pin_memory=True)
+        tv = traw.numpy().reshape(n1, rec_bytes)
+        tv[:, :nlen] = names.reshape(n1, nlen); tv[:, nlen] = 10
+        tv[:, nlen + 1:nlen + 1 + L1] = seq.reshape(n1, L1); tv[:, nlen + 1 + L1] = 10
+        tv[:, nlen + 2 + L1] = ord("+"); tv[:, nlen + 3 + L1] = 10
+        tv[:, nlen + 4 + L1:nlen + 4 + 2 * L1] = qual.reshape(n1, L1); tv[:, rec_bytes - 1] = 10
+        rb = abi.FqRawBlock(); rb.text = traw.data_ptr(); rb.bytes = traw.numel(); rb.first_index = 0
+        nr, used = C.c_uint32(0), C.c_uint64(0)
+
+        def fastq_call():
+            rc = eng.lib.fqk_process_se_fastq(eng.h, C.byref(rb), 0, None, 0, touts, C.byref(passed), C.byref(nr), C.byref(used))
+            assert rc == 0 and nr.value == n1 and used.value == traw.numel(), eng.lib.fqk_last_error(eng.h)
+        fastq_call()
+        eng.reset(); ctx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fastq_call()
+        eng.finalize(); ctx.barrier()
+        dtf = ctx.max_over_ranks(time.perf_counter() - t0)
+        e2e_fastq = {"value": world * reps * n1 * L1 / dtf / 1e9, "unit": "Gbases/s", "calls": reps,
+                     "h2d_bytes_per_call": int(traw.numel()), "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len),
+                     "note": "fqk_process_se_fastq: decompressed FASTQ text in, trimmed FASTQ text out; newline scan, packing, hot path "
+                             "and record assembly on the GPU (what FqReader, the worker body and Read::toString do in the reference)"}
+        del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout, traw, tv
     del hbs, hout, batches
     job.close(); del job, eng
     ctx.free()
@@ -558,7 +584,7 @@ def main():
                            "read_length": c["L"], "batches_per_step": nb, "batch_reads": BATCH_READS,
                            "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit / 1e9),
                            "impl": a.impl},
-                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "e2e_text": e2e_text, "gpu_launches": main_rec["gpu_launches"],
+                "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "e2e_text": e2e_text, "e2e_fastq": e2e_fastq, "gpu_launches": main_rec["gpu_launches"],
                 "roofline": main_rec["roofline"], "finalize_ms": main_rec["finalize_ms"], "cpu_baseline": cpu_baseline,
                 "configs": extra or None, "scaling_cfg5": scaling_cfg5, "merge_check": mcheck}
         emit(line)
