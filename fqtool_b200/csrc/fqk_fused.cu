@@ -455,7 +455,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             const uint16_t* sl = reinterpret_cast<const uint16_t*>(metap + (size_t)m * meta_bytes + mo);
             const uint32_t t0 = lo + (uint32_t)k * T;
             const int nt = (int)min((uint32_t)T, hi - t0);
-            mbar_wait(&metab[m], (uint32_t)(k / MS) & 1u);
+            mbar_wait_sleep(&metab[m], (uint32_t)(k / MS) & 1u, 20000);
             uint32_t* c = reinterpret_cast<uint32_t*>(S + o_cnt); c[0] = 0; c[1] = 0; c[2] = 0;
             const uint32_t a = so[0];
             uint64_t e = (uint64_t)so[nt - 1] + ((sl[nt - 1] + 15u) & ~15u);
@@ -484,8 +484,8 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
             uint32_t* cnt = reinterpret_cast<uint32_t*>(S + o_cnt);
             const uint32_t t0 = lo + (uint32_t)k * T;
             const int nt = (int)min((uint32_t)T, hi - t0);
-            mbar_wait(&metab[k % MS], (uint32_t)(k / MS) & 1u);
-            mbar_wait(&full[s], (uint32_t)(k / NS) & 1u);
+            mbar_wait_sleep(&metab[k % MS], (uint32_t)(k / MS) & 1u, 20000);
+            mbar_wait_sleep(&full[s], (uint32_t)(k / NS) & 1u, 20000);
             const uint32_t a0 = So[0];
             const uint32_t bshift = (a0 >> 2) & 15u;
             // read i of tile k goes to thread (i + k*T) mod WS_TRIM: when T is not a multiple of the trim threads the
@@ -558,7 +558,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
                 // stage of tile k+2 = stage of tile k-1: once the statistics warps released it, every thread of the block is
                 // done with tile k-1, whose metadata slot is the one tile k+3 lands in
                 const int k2 = k + 2, n2 = k2 / NS;
-                if(n2 >= 1) mbar_wait(&freeb[k2 % NS], (uint32_t)(n2 - 1) & 1u);
+                if(n2 >= 1) mbar_wait_sleep(&freeb[k2 % NS], (uint32_t)(n2 - 1) & 1u, 20000);
                 if(k + 3 < ntiles) issue_meta(k + 3);
                 issue_data(k2);
             }
@@ -578,7 +578,7 @@ k_fused_se_ws(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* _
         for(int k = 0; k < ntiles; ++k){
             const int s = k % NS;
             const uint32_t S32 = sp32 + (uint32_t)s * stage_bytes;
-            mbar_wait(&ready[s], (uint32_t)(k / NS) & 1u);
+            mbar_wait_sleep(&ready[s], (uint32_t)(k / NS) & 1u, 20000);
             if(active){
                 const uint32_t a0 = lds32(smem_u32(metap) + (uint32_t)(k % MS) * meta_bytes);
                 const uint32_t bshift = (a0 >> 2) & 15u;
