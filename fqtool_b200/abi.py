@@ -121,7 +121,7 @@ EXPORTS = [
     "fqk_set_kernel_timing", "fqk_kernel_times", "fqk_set_impl", "fqk_get_corrections", "fqk_reset", "fqk_finalize",
     "fqk_dup_table", "fqk_packed_bases", "fqk_pack_ascii", "fqk_host_alloc", "fqk_host_free",
     "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits", "fqk_process_se_text", "fqk_process_pe_text",
-    "fqk_process_se_fastq", "fqk_process_pe_fastq",
+    "fqk_process_se_fastq", "fqk_process_pe_fastq", "fqk_submit_se_ascii",
 ]
 
 _lib = None
@@ -151,6 +151,7 @@ def load():
     lib.fqk_process_pe_ascii.argtypes = [vp, P(FqAsciiBatch), P(FqAsciiBatch), vp, vp, vp]; lib.fqk_process_pe_ascii.restype = i32
     lib.fqk_submit_se.argtypes = [vp, P(FqBatch), vp, P(u64)]; lib.fqk_submit_se.restype = i32
     lib.fqk_wait.argtypes = [vp, u64]; lib.fqk_wait.restype = i32
+    lib.fqk_submit_se_ascii.argtypes = [vp, P(FqAsciiBatch), vp, P(u64)]; lib.fqk_submit_se_ascii.restype = i32
     lib.fqk_process_se_device.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se_device.restype = i32
     lib.fqk_process_pe_device.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp]
     lib.fqk_process_pe_device.restype = i32

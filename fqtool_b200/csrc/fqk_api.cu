@@ -73,6 +73,7 @@ struct fqk_ctx {
     DevBuf tnames[2], tnoff[2], tstr[2], tsoff[2], tsizes, tscratch, ttot, tout[FQK_CH_COUNT];
     // raw FASTQ blocks (fqk_process_*_fastq): the text, newline counts/positions, quality offsets, line lengths
     DevBuf traw[2], tnlc[2], tnl[2], aqsrc[2], tnlen[2], tslen[2];
+    DevBuf poff[2], pscr[2], ptot[2];         // pipelined ASCII ingest (fqk_submit_se_ascii): offsets, scan scratch, totals per slot
     bool raw_mode = false;                    // the staged mates come from raw blocks (TextMate then points into traw)
     std::vector<uint32_t> hnoff[2], hsoff[2];
     unsigned long long* tab128 = nullptr; unsigned long long* first64 = nullptr;   // dup table
@@ -284,6 +285,7 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(int i = 0; i < 2; ++i){ c->aseq[i].release(); c->aqual[i].release(); c->asrc[i].release(); }
     for(int i = 0; i < 2; ++i){ c->tnames[i].release(); c->tnoff[i].release(); c->tstr[i].release(); c->tsoff[i].release(); }
     c->tsizes.release(); c->tscratch.release(); c->ttot.release();
+    for(int i = 0; i < 2; ++i){ c->poff[i].release(); c->pscr[i].release(); c->ptot[i].release(); }
     for(int i = 0; i < 2; ++i){ c->traw[i].release(); c->tnlc[i].release(); c->tnl[i].release(); c->aqsrc[i].release(); c->tnlen[i].release(); c->tslen[i].release(); }
     for(int i = 0; i < FQK_CH_COUNT; ++i) c->tout[i].release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
@@ -796,23 +798,74 @@ extern "C" int fqk_process_pe_fastq(fqk_ctx* c, const fq_raw_block* in1, const f
     return check_err_flag(c);
 }
 
+static int pipe_init(fqk_ctx* c){
+    if(c->h2d) return 0;
+    CU(cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+    for(int i = 0; i < 2; ++i){
+        CU(cudaEventCreateWithFlags(&c->evH2D[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->evK[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->evD2H[i], cudaEventDisableTiming));
+    }
+    CU(cudaHostAlloc((void**)&c->perr_host, 2 * sizeof(uint32_t), cudaHostAllocDefault));
+    c->perr_host[0] = c->perr_host[1] = 0;
+    return 0;
+}
+
+// Pipelined form of fqk_process_se_ascii: two packs in flight, and NOTHING per read on the host -- the
+// per-read source offsets, lengths and destination offsets (a prefix sum of the padded lengths) are computed on the
+// device from the caller's offset array, so the call only enqueues copies and kernels.  Slot s of the pipeline uses the
+// staging buffers of "mate" s (a single-end context has no second mate).
+extern "C" int fqk_submit_se_ascii(fqk_ctx* c, const fq_ascii_batch* in, fq_read_result* out, uint64_t* ticket){
+    if(!c || !in || !in->off || !ticket || (!out && in->n_reads)) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    CU(cudaSetDevice(c->device));
+    int rc = pipe_init(c); if(rc) return rc;
+    const uint64_t t = c->submitted;
+    const int s = (int)(t & 1);
+    const uint32_t n = in->n_reads;
+    if(t >= 2){ CU(cudaEventSynchronize(c->evD2H[s])); note_pack_error(c, c->perr_host[s]); }
+    if(n == 0){ CU(cudaEventRecord(c->evD2H[s], c->d2h)); *ticket = t; c->submitted = t + 1; return 0; }
+    const uint64_t chars = in->off[n] - in->off[0];
+    const uint64_t cap = ((chars + 15ull * n + 64) + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;   // upper bound of the padded extent
+    if(chars > 0xFFFFFFF0ull || cap > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "ASCII batch larger than 2^32 (padded) characters");
+    StagedBatch& S = c->st[s];
+    if(c->aseq[s].ensure(chars + 16) || c->aqual[s].ensure(chars + 16) || c->asrc[s].ensure((size_t)n * 4 + 16) || c->poff[s].ensure((size_t)(n + 1) * 8) ||
+       c->pscr[s].ensure(text_scan_scratch_u64(n) * 8) || c->ptot[s].ensure(64) || S.off.ensure((size_t)n * 4 + 16) || S.len.ensure((size_t)n * 2 + 16) ||
+       S.b2.ensure(cap / 4 + 32) || S.q.ensure(cap + 80) || c->pres[s].ensure((size_t)n * sizeof(fq_read_result)))
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    CU(cudaStreamWaitEvent(c->h2d, c->evK[s], 0));                      // the slot's previous pack is through the kernels
+    CU(cudaMemcpyAsync(c->aseq[s].p, in->seq + in->off[0], chars, cudaMemcpyHostToDevice, c->h2d));
+    CU(cudaMemcpyAsync(c->aqual[s].p, in->qual + in->off[0], chars, cudaMemcpyHostToDevice, c->h2d));
+    CU(cudaMemcpyAsync(c->poff[s].p, in->off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, c->h2d));
+    ascii_launch_index(c->h2d, n, (const uint64_t*)c->poff[s].p, (uint32_t*)c->asrc[s].p, (uint16_t*)S.len.p, (uint32_t*)S.off.p, c->err);
+    text_launch_scan(c->h2d, n, (uint32_t*)S.off.p, (uint64_t*)c->ptot[s].p, (uint64_t*)c->pscr[s].p, 1);
+    ascii_launch_zero_tail(c->h2d, (const uint64_t*)c->ptot[s].p, (uint8_t*)S.q.p, (uint8_t*)S.b2.p);
+    k_pack_ascii<<<grid_for(c, n, 16, 8), 256, 0, c->h2d>>>(n, (const char*)c->aseq[s].p, (const char*)c->aqual[s].p, (const uint32_t*)c->asrc[s].p,
+        (const uint32_t*)S.off.p, (const uint16_t*)S.len.p, (uint8_t*)S.b2.p, (uint8_t*)S.q.p, c->err);
+    c->launches += 6;
+    S.dev.n = n; S.dev.first_index = in->first_index; S.dev.total = cap; S.dev.max_len = 0;
+    S.dev.offsets = (const uint32_t*)S.off.p; S.dev.lengths = (const uint16_t*)S.len.p;
+    S.dev.bases2 = (const uint8_t*)S.b2.p; S.dev.qual = (const uint8_t*)S.q.p;
+    CU(cudaEventRecord(c->evH2D[s], c->h2d));
+    CU(cudaStreamWaitEvent(c->stream, c->evH2D[s], 0));
+    rc = launch_se(c, S.dev, (fq_read_result*)c->pres[s].p); if(rc) return rc;
+    CU(cudaEventRecord(c->evK[s], c->stream));
+    CU(cudaStreamWaitEvent(c->d2h, c->evK[s], 0));
+    CU(cudaMemcpyAsync(out, c->pres[s].p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaEventRecord(c->evD2H[s], c->d2h));
+    *ticket = t; c->submitted = t + 1;
+    return 0;
+}
+
 // Pipelined form of fqk_process_se: the upload of pack k+1 overlaps the kernels and the download of pack k
 // (PCIe is full duplex).  At most two packs are in flight; buffers of a pack must stay valid until fqk_wait.
 extern "C" int fqk_submit_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out, uint64_t* ticket){
     if(!c || !in || !ticket || (!out && in->n_reads)) return FQK_E_INVALID;
     if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
     CU(cudaSetDevice(c->device));
-    if(!c->h2d){
-        CU(cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking));
-        CU(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
-        for(int i = 0; i < 2; ++i){
-            CU(cudaEventCreateWithFlags(&c->evH2D[i], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&c->evK[i], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&c->evD2H[i], cudaEventDisableTiming));
-        }
-        CU(cudaHostAlloc((void**)&c->perr_host, 2 * sizeof(uint32_t), cudaHostAllocDefault));
-        c->perr_host[0] = c->perr_host[1] = 0;
-    }
+    int rcp = pipe_init(c); if(rcp) return rcp;
     const uint64_t t = c->submitted;                                    // the ticket is handed out only when the pack is enqueued
     const int s = (int)(t & 1);
     const size_t n = in->n_reads;

@@ -328,6 +328,23 @@ __global__ void k_fastq_index(const char* __restrict__ text, const uint32_t* __r
     if((threadIdx.x & 31) == 0){ if(mx) atomicMax(&misc[0], mx); if(bad) atomicOr(err, bad); }
 }
 
+__global__ void k_ascii_index(uint32_t n, const uint64_t* __restrict__ off, uint32_t* __restrict__ src, uint16_t* __restrict__ len,
+                              uint32_t* __restrict__ padlen, uint32_t* __restrict__ err){
+    const uint64_t o0 = off[0];
+    for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x){
+        const uint64_t a = off[r], l = off[r + 1] - a;
+        if(l > FQK_MAX_READ_LEN) atomicOr(err, 1u);
+        const uint32_t lc = (uint32_t)(l > FQK_MAX_READ_LEN ? FQK_MAX_READ_LEN : l);
+        src[r] = (uint32_t)(a - o0); len[r] = (uint16_t)lc;
+        padlen[r] = (lc + FQK_PAD - 1u) / FQK_PAD * FQK_PAD;
+    }
+}
+__global__ void k_zero_tail(const uint64_t* __restrict__ total, uint8_t* __restrict__ qual, uint8_t* __restrict__ bases2){
+    const uint64_t t = *total;                                  // a multiple of 16
+    if(threadIdx.x < 64) qual[t + threadIdx.x] = 0;
+    if(threadIdx.x < 16) bases2[t / 4 + threadIdx.x] = 0;
+}
+
 } // namespace
 
 // ------------------------------------------------------------------ launchers
@@ -368,4 +385,11 @@ void fastq_launch_index(cudaStream_t st, const char* text, const uint32_t* nlpos
                         uint32_t* padlen, uint32_t* misc, uint32_t* err){
     if(n) k_fastq_index<<<text_grid(n, 256), 256, 0, st>>>(text, nlpos, n, src_seq, src_qual, len, name_off, name_len, strand_off, strand_len,
                                                          padlen, misc, err);
+}
+
+void ascii_launch_index(cudaStream_t st, uint32_t n, const uint64_t* off, uint32_t* src, uint16_t* len, uint32_t* padlen, uint32_t* err){
+    if(n) k_ascii_index<<<text_grid(n, 256), 256, 0, st>>>(n, off, src, len, padlen, err);
+}
+void ascii_launch_zero_tail(cudaStream_t st, const uint64_t* total, uint8_t* qual, uint8_t* bases2){
+    k_zero_tail<<<1, 64, 0, st>>>(total, qual, bases2);
 }

@@ -48,3 +48,9 @@ void fastq_launch_positions(cudaStream_t st, const char* text, uint64_t bytes, c
 void fastq_launch_index(cudaStream_t st, const char* text, const uint32_t* nlpos, uint32_t n, uint32_t* src_seq, uint32_t* src_qual,
                         uint16_t* len, uint32_t* name_off, uint32_t* name_len, uint32_t* strand_off, uint32_t* strand_len,
                         uint32_t* padlen, uint32_t* misc, uint32_t* err);
+
+// ---- ASCII batches indexed on the device (pipelined ingest): src / len / padded length from the caller's offsets ----
+// off: device copy of fq_ascii_batch.off[n+1]; err |= 1 for a read longer than FQK_MAX_READ_LEN
+void ascii_launch_index(cudaStream_t st, uint32_t n, const uint64_t* off, uint32_t* src, uint16_t* len, uint32_t* padlen, uint32_t* err);
+// zero the 64 bytes (16 base bytes) after the last padded read: *total = end of the packed data
+void ascii_launch_zero_tail(cudaStream_t st, const uint64_t* total, uint8_t* qual, uint8_t* bases2);

@@ -162,6 +162,13 @@ class Engine:
         self._check(self.lib.fqk_submit_se(self.h, C.byref(b), abi.ptr(out), C.byref(t)), "fqk_submit_se")
         return t.value
 
+    def submit_se_ascii(self, reads, out, first_index=0):
+        """Pipelined fqk_process_se_ascii; returns (ticket, keep): `keep` and `out` must stay alive until wait(ticket)."""
+        b, keep = self._ascii(reads, first_index)
+        t = C.c_uint64(0)
+        self._check(self.lib.fqk_submit_se_ascii(self.h, C.byref(b), abi.ptr(out), C.byref(t)), "fqk_submit_se_ascii")
+        return t.value, keep
+
     def wait(self, ticket):
         self._check(self.lib.fqk_wait(self.h, ticket), "fqk_wait")
 

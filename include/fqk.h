@@ -339,6 +339,9 @@ int  fqk_process_pe_fastq(fqk_ctx* ctx, const fq_raw_block* in1, const fq_raw_bl
  * later fqk_wait (also for tickets already recycled) and fqk_finalize return it until fqk_reset.
  */
 int  fqk_submit_se(fqk_ctx* ctx, const fq_batch* in, fq_read_result* out, uint64_t* ticket);
+/* the same for FASTQ characters (fq_ascii_batch): per-read offsets, lengths and the packed layout are all derived on the
+ * device, the call only enqueues copies and kernels; in->off / seq / qual must stay valid until fqk_wait */
+int  fqk_submit_se_ascii(fqk_ctx* ctx, const fq_ascii_batch* in, fq_read_result* out, uint64_t* ticket);
 int  fqk_wait(fqk_ctx* ctx, uint64_t ticket);
 
 /*

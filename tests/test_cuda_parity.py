@@ -93,13 +93,14 @@ def test_pipelined_submit_wait_matches_sync():
 
 @pytest.mark.parametrize("name", ["cfg2", "cfg4", "cfg3", "pe_correct_merge"])
 def test_ascii_entry_points_match_packed_path(name):
-    """fqk_process_*_ascii (device-side packing) == host-packed path; foreign alphabet is an error."""
+    """fqk_process_*_ascii (device-side packing) against the ORACLE (and hence the host-packed path); foreign alphabet is
+    an error."""
     from fqtool_b200 import batch
     from fqtool_b200.engine import Engine, FqkError
     opt = configs.options(name)
     paired = name in configs.PE
     r1 = synth.ragged(5000, seed=91); r2 = synth.ragged(5000, seed=92) if paired else None
-    want = util.run_cuda(opt, r1, r2)
+    want = util.run_oracle(opt, r1, r2)
     e = Engine(opt.to_params())
     recs = e.process_pe_ascii(r1, r2) if paired else (e.process_se_ascii(r1),)
     got = (tuple(recs), e.finalize(), e.dup_table() if opt.duplicate.enabled else None)
@@ -108,4 +109,37 @@ def test_ascii_entry_points_match_packed_path(name):
         bad = batch.from_strings(["ACGTNACGTRACGT"], ["IIIIIIIIIIIIII"])
         with pytest.raises(FqkError):
             e.process_se_ascii(bad)
+    e.close()
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg4", "se_all_cuts"])
+def test_pipelined_ascii_submit_matches_oracle(name):
+    """fqk_submit_se_ascii / fqk_wait: two packs in flight, per-read offsets / lengths / packed layout derived on the device
+    (k_ascii_index + prefix sum); records, accumulators and the duplication table against the oracle."""
+    from fqtool_b200 import abi, batch
+    from fqtool_b200.engine import Engine, FqkError
+    opt = configs.options(name)
+    reads = synth.ragged(9000, seed=78)
+    want = util.run_oracle(opt, reads)
+    e = Engine(opt.to_params())
+    bounds = np.linspace(0, 9000, 8).astype(int)
+    packs = [batch.slice_reads(reads, lo, hi) for lo, hi in zip(bounds[:-1], bounds[1:])]
+    outs = [np.zeros(len(p[2]) - 1, dtype=abi.READ_RESULT_DTYPE) for p in packs]
+    pending, keep = None, []
+    for p, o, lo in zip(packs, outs, bounds[:-1]):
+        t, k = e.submit_se_ascii(p, o, int(lo))
+        keep.append(k)
+        if pending is not None:
+            e.wait(pending)
+        pending = t
+    e.wait(pending)
+    got = ((np.concatenate(outs),), e.finalize(), e.dup_table() if opt.duplicate.enabled else None)
+    util.assert_same(got, want[:3])
+    e.close()
+    # an over-long read is reported by the wait (the index is built on the device)
+    e = Engine(configs.options("cfg2", max_cycles=64).to_params())
+    o = np.zeros(10, dtype=abi.READ_RESULT_DTYPE)
+    t, k = e.submit_se_ascii(synth.se_hiseq(10, 100, seed=1), o)
+    with pytest.raises(FqkError):
+        e.wait(t)
     e.close()
