@@ -331,7 +331,22 @@ static DevBatch to_dev(const fq_batch* b){
 static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     if(B.n == 0) return 0;
     Timer all(c, FQK_T_ALL);
-    if(c->impl != 1 && fused_supported_se(c->D, B)){
+    // k-mers as a pass of their own (k_kmer_se) after a fused kernel that runs WITHOUT them: k_se_v3 has no k-mer code and
+    // is twice as fast as k_fused_se_ws, whose k-mer counting costs another 2.3 ms per 4 M reads (tools/prof_cfg4_parts.py)
+    static const bool kmer_fused = getenv("FQK_KMER_FUSED") != nullptr;       // A/B switch: k-mers inside k_fused_se_ws as in round 1
+    DevParams Dn = c->D; Dn.P.kmer_len = 0;
+    const bool ksplit = c->impl == 0 && c->D.P.kmer_len >= 4 && c->D.P.kmer_len <= 13 && !kmer_fused && fused_supported_se(Dn, B);
+    if(ksplit){
+        { Timer t(c, FQK_T_FUSED);
+          int nl = fused_launch_se(Dn, B, out, c->flat, c->sms, c->stream, c->impl);
+          if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");
+          c->launches += nl; }
+        Timer t(c, FQK_T_STATS);
+        const int K = c->D.P.kmer_len;
+        const int use_smem = K <= 6;
+        k_kmer_se<<<c->sms * (use_smem ? 4 : 8), 256, use_smem ? (size_t)2 * 4 * ((size_t)1 << (2 * K)) : 0, c->stream>>>(c->D, B, out, c->flat, use_smem);
+        c->launches++;
+    }else if(c->impl != 1 && fused_supported_se(c->D, B)){
         Timer t(c, FQK_T_FUSED);
         int nl = fused_launch_se(c->D, B, out, c->flat, c->sms, c->stream, c->impl);
         if(nl < 0) return fail(c, FQK_E_CUDA, "fused SE launch failed");

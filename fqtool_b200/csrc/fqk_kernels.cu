@@ -541,3 +541,90 @@ __global__ void __launch_bounds__(256) k_pack_ascii(uint32_t n, const char* __re
     }
     if(bad) atomicOr(err, 4u);
 }
+
+// ---------------------------------------------------------------- k-mer counting as its own pass (single-end)
+// Stats::statRead counts, for every position i >= k-1 of a read, the k-mer ending at i iff its k bases are all in ATCG
+// (Evaluator::seq2int, src/evaluator.cpp:3-49; src/stats.cpp:266-274): once for the raw read (pre) and once for the kept
+// part of a passing read (post), in the coordinates of the kept part.  As a pass of its own it reads 0.25 B/base of
+// packed bases, the N flags (bit 7 of the quality bytes) and the records; the fused kernels then run without k-mers
+// (cfg4: k_fused_se_ws with k-mers 4.9 ms, k_se_v3 without 2.5 ms per 4 M reads).
+// A warp takes a read: its packed words and N masks go to shared memory, then a lane owns 4 positions and the 16 bases
+// ending at its last position are one 32-bit window (funnel shift).  Two
+// privatised histograms per block for k <= 6: both (window inside the kept part of a passing read), pre only -- a window that
+// counts for both Stats objects costs one shared reduction; for k > 6 global atomics on the flat buffer.  (Two
+// histograms suffice: a window of the kept part is always a window of the raw read.)
+__device__ __forceinline__ uint32_t nflags16_g(const uint8_t* q){               // N flags (bit 7) of 16 quality bytes as a 16-bit mask
+    const uint4 v = *reinterpret_cast<const uint4*>(q);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t m = 0;
+#pragma unroll
+    for(int k = 0; k < 4; ++k) m |= ((((w[k] >> 7) & 0x01010101u) * 0x00204081u) >> 21 & 0xFu) << (4 * k);
+    return m;
+}
+__global__ void __launch_bounds__(256) k_kmer_se(const __grid_constant__ DevParams D, DevBatch B, const fq_read_result* __restrict__ recs,
+                                                  uint64_t* __restrict__ flat, int use_smem){
+    extern __shared__ uint32_t sh_hist[];                                        // [2][4^k] when use_smem: both, pre only
+    const int K = D.P.kmer_len;
+    const uint32_t bins = 1u << (2 * K), kmask = bins - 1u;
+    if(use_smem){ for(uint32_t i = threadIdx.x; i < 2 * bins; i += blockDim.x) sh_hist[i] = 0; __syncthreads(); }
+    uint64_t* pre = flat + D.L.stats_off[0] + D.L.s_kmer;
+    uint64_t* post = flat + D.L.stats_off[2] + D.L.s_kmer;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    // per warp: the packed words and N masks of the read in hand, word w at index w + 1 (index 0 = "word -1" = nothing)
+    __shared__ uint32_t s_c[8][34], s_n[8][34];
+    const uint32_t wmask = (1u << K) - 1u;
+    for(uint32_t r = warp; r < B.n; r += nwarps){
+        const uint32_t off = B.offsets[r], len = B.lengths[r];
+        const fq_read_result x = recs[r];
+        const bool pass = !(x.flags & FQK_F_DROPPED) && x.result == FQK_PASS_FILTER;
+        const uint32_t vs = x.start, ve = (uint32_t)x.start + x.len;            // kept part [vs, ve)
+        const uint32_t nw = (len + 15u) >> 4;
+        for(uint32_t w0 = 0; w0 < nw; w0 += 32){                                // 512 positions per round
+            __syncwarp();
+            {   // stage: lane l loads word w0 + l (the word before the round, for windows that reach back, goes to index 0)
+                const uint32_t w = w0 + lane;
+                uint32_t cw = 0, nm = 0;
+                if(w < nw){ cw = *reinterpret_cast<const uint32_t*>(B.bases2 + (off >> 2) + 4u * w); nm = nflags16_g(B.qual + off + 16u * w); }
+                s_c[wib][lane + 1] = cw; s_n[wib][lane + 1] = nm;
+                if(lane == 0){
+                    uint32_t pw = 0, pn = 0;
+                    if(w0 > 0){ pw = *reinterpret_cast<const uint32_t*>(B.bases2 + (off >> 2) + 4u * (w0 - 1)); pn = nflags16_g(B.qual + off + 16u * (w0 - 1)); }
+                    s_c[wib][0] = pw; s_n[wib][0] = pn; s_c[wib][33] = 0; s_n[wib][33] = 0;
+                }
+            }
+            __syncwarp();
+            // count: a lane owns 4 positions; the 16 bases ending at its last position are one 32-bit window
+#pragma unroll 1
+            for(uint32_t g0 = 0; g0 < 128; g0 += 32){
+                const uint32_t g = g0 + lane;                                   // group of 4 positions inside the round
+                const uint32_t i0 = 16u * w0 + 4u * g;                          // raw position of its first base
+                if(i0 >= len) break;                                            // (uniform: later groups lie further right)
+                const int s0 = (int)(4u * g) + 3 - 15 + 16;                     // window start, in bases from index 0 of s_c (word -1)
+                const uint32_t wi = (uint32_t)s0 >> 4, sh = (uint32_t)s0 & 15u;
+                const uint32_t win = __funnelshift_r(s_c[wib][wi], s_c[wib][wi + 1], 2u * sh);       // bases s0 .. s0+15
+                const uint32_t nwin = ((s_n[wib][wi] | (s_n[wib][wi + 1] << 16)) >> sh) & 0xFFFFu;   // their N flags
+#pragma unroll
+                for(int j = 0; j < 4; ++j){
+                    const uint32_t i = i0 + (uint32_t)j;                        // the window ends at raw position i = index 12 + j
+                    if(i >= len || i + 1u < (uint32_t)K) continue;
+                    const int lo = 12 + j - (K - 1);
+                    if((nwin >> lo) & wmask) continue;                          // an N inside: seq2int returns -1
+                    uint32_t key = __brev((win >> (2 * lo)) & kmask) >> (32 - 2 * K);   // first base on top (seq2int)
+                    key = ((key >> 1) & 0x55555555u) | ((key & 0x55555555u) << 1);
+                    const bool inpost = pass && i + 1u >= vs + (uint32_t)K && i < ve;   // the window lies inside the kept part
+                    if(use_smem) atomicAdd(&sh_hist[(inpost ? 0u : bins) + key], 1u);
+                    else { add_u64(pre + key, 1); if(inpost) add_u64(post + key, 1); }
+                }
+            }
+        }
+    }
+    if(use_smem){
+        __syncthreads();
+        for(uint32_t i = threadIdx.x; i < bins; i += blockDim.x){
+            const uint32_t both = sh_hist[i], po = sh_hist[bins + i];
+            if(both + po) add_u64(pre + i, both + po);
+            if(both) add_u64(post + i, both);
+        }
+    }
+}

@@ -21,3 +21,5 @@ __global__ void k_pack_ascii(uint32_t n, const char* __restrict__ seq, const cha
                              const uint32_t* __restrict__ src_off, const uint32_t* __restrict__ dst_off,
                              const uint16_t* __restrict__ lengths, uint8_t* __restrict__ bases2,
                              uint8_t* __restrict__ qout, uint32_t* __restrict__ err, const uint32_t* __restrict__ qsrc_off = nullptr);
+__global__ void k_kmer_se(const __grid_constant__ DevParams D, DevBatch B, const fq_read_result* __restrict__ recs,
+                          uint64_t* __restrict__ flat, int use_smem);
