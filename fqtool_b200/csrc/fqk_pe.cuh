@@ -257,28 +257,77 @@ __device__ inline bool dev_trim_by_sequence_packed(ReadView& v, const uint32_t* 
     int start = 0;
     if(alen >= 16) start = -4; else if(alen >= 12) start = -3; else if(alen >= 8) start = -2;
     PackedSeq r;
-    pack_view(v, r);
     int pos; bool found = false;
-    // Quick reject for pos >= 0 while a whole first word of the adapter is compared: the window of the read is one funnel
-    // shift of two words kept in registers, codes only.  N bases carry code 0 in both packed strings, so the code-only
-    // count never exceeds the true count: a position the reference accepts is never dropped here, and the survivors go
-    // through the exact test below.  (k_se_v3 generic trim role, adapter only, 4 M reads of 100 bp: 2.44 -> 2.18 ms.)
-    const int a16 = min(alen, 16);
-    const uint32_t A0 = adc[0], m16 = valid_mask(a16);
-    uint32_t w0 = r.c[0], w1 = r.c[1];
-    for(pos = start; pos < rlen - 4; ++pos){
-        const int cmplen = min(rlen - pos, alen);
-        const int allowed = cmplen / 8;
-        if(pos >= 0 && cmplen >= a16){
-            if(pos && !(pos & 15)){ w0 = w1; w1 = r.c[(pos >> 4) + 1]; }
-            const uint32_t t = __funnelshift_r(w0, w1, 2u * ((uint32_t)pos & 15u)) ^ A0;
-            if(__popc((t | (t >> 1)) & m16) > allowed) continue;
-        }
-        const int ao = max(0, -pos), ro = max(0, pos), n = cmplen - ao;
+    // Quick reject on the first word of the comparison, codes only, straight from the read's packed words (two words in
+    // registers, one funnel shift per position): N bases carry code 0 in the batch and in the packed adapter, so the
+    // code-only count never exceeds the true count -- a position the reference accepts is never dropped here -- and the
+    // survivors go through the exact test below.  The view is packed (N masks, local memory) only when a position
+    // survives, which most reads never see.  (Generic trim role of k_se_v3, adapter only, 4 M reads of 100 bp: 2.44 ms
+    // with a packed compare per position, 2.18 ms with the reject on the packed view; profiles/r02q_*.)
+    const bool aligned = (reinterpret_cast<uintptr_t>(v.b2) & 3u) == 0;
+    const uint32_t* bw = reinterpret_cast<const uint32_t*>(v.b2);      // word i = bases 16i .. 16i+15 of the raw read
+    bool packed = false;
+    int cur = -1; uint32_t w0 = 0, w1 = 0;
+    // the read's 16 bases from raw position p0, codes only
+    auto window = [&](int p0) -> uint32_t {
+        if((p0 >> 4) != cur){ cur = p0 >> 4; w0 = bw[cur]; w1 = bw[cur + 1]; }
+        return __funnelshift_r(w0, w1, 2u * ((uint32_t)p0 & 15u));
+    };
+    // the exact test of one position (the reference's inner loop, on packed words)
+    auto exact = [&](int p, int cmplen, int allowed) -> bool {
+        if(!packed){ pack_view(v, r); packed = true; }
+        const int ao = max(0, -p), ro = max(0, p), n = cmplen - ao;
         int d = mism_words(adc, adn, ao, r.c, r.n, ro, 0, min(n, 16));
-        if(d > allowed) continue;
+        if(d > allowed) return false;
         if(n > 16) d += mism_words(adc, adn, ao, r.c, r.n, ro, 16, n);
-        if(d <= allowed){ found = true; break; }
+        return d <= allowed;
+    };
+    // any position, with the quick reject when the words can be read directly
+    auto general = [&](int p) -> bool {
+        const int cmplen = min(rlen - p, alen), allowed = cmplen / 8;
+        const int ao = max(0, -p), ro = max(0, p), n = cmplen - ao;
+        if(aligned && n > 0){
+            const uint32_t aw = ao ? __funnelshift_r(adc[0], adc[1], 2u * (uint32_t)ao) : adc[0];      // ao <= 4
+            const uint32_t t = window(v.start + ro) ^ aw;
+            if(__popc((t | (t >> 1)) & valid_mask(min(n, 16))) > allowed) return false;
+        }
+        return exact(p, cmplen, allowed);
+    };
+    pos = start;
+    for(; pos < 0 && pos < rlen - 4 && !found; ++pos) found = general(pos);
+    if(found) --pos;
+    if(!found && aligned && alen >= 16){
+        // the bulk: the whole adapter fits (cmplen == alen): constant budget and mask.  Sixteen positions per step: three
+        // words give the 32 bases from the step's first position, every window is one funnel shift by a constant.
+        const int allowed = alen / 8, last = min(rlen - alen, rlen - 5);
+        const uint32_t A0 = adc[0];
+        if(pos <= last){
+            const int q0 = v.start + pos;
+            const uint32_t sh = 2u * ((uint32_t)q0 & 15u);
+            int wi = q0 >> 4;
+            uint32_t wa = bw[wi], wb = bw[wi + 1];
+            for(; pos <= last && !found; pos += 16, ++wi){
+                const uint32_t wc = bw[wi + 2];
+                const uint32_t B0 = __funnelshift_r(wa, wb, sh), B1 = __funnelshift_r(wb, wc, sh);     // bases pos .. pos+31 of the view
+                wa = wb; wb = wc;
+                uint32_t cm = 0;
+#pragma unroll
+                for(int k = 0; k < 16; ++k){
+                    const uint32_t t = (k ? __funnelshift_r(B0, B1, 2 * k) : B0) ^ A0;
+                    cm |= (__popc((t | (t >> 1)) & 0x55555555u) <= allowed) ? (1u << k) : 0u;
+                }
+                const int nv = last - pos + 1;
+                if(nv < 16) cm &= (1u << nv) - 1u;
+                while(cm){
+                    const int k = __ffs((int)cm) - 1; cm &= cm - 1u;
+                    if(exact(pos + k, alen, allowed)){ found = true; pos += k - 16; break; }           // (the loop adds 16 back)
+                }
+            }
+            if(!found) pos = last + 1;
+        }
+    }
+    if(!found){
+        for(; pos < rlen - 4; ++pos) if(general(pos)){ found = true; break; }
     }
     if(!found) return false;
     int textlen;

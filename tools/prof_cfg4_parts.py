@@ -13,15 +13,19 @@ variants = {"full": f"-a --adapter_of_read1 {A} -x -d --dup_ana_key_len 12 --kme
             "polyX only": "-x",
             "kmer only": "--kmer --kmer_length 6",
             "plain": ""}
-n = 4_000_000
+n = int(os.environ.get("PARTS_N", "4000000"))
+only = os.environ.get("PARTS_ONLY")
+reps = int(os.environ.get("PARTS_REPS", "6"))
 dev = torch.device("cuda", 0)
 for name, cli in variants.items():
+    if only and name != only:
+        continue
     o = from_cli(cli.split()); o.maxCycles = 128
     eng = Engine(o.to_params(), device=0)
     b1, _ = workload.generate("cfg4", n, 0, dev, eng.stream)
     o1 = torch.empty(n * 16, dtype=torch.uint8, device=dev)
     s1 = b1.c_struct(); eng.sync(); eng.set_kernel_timing(True)
-    for _ in range(6):
+    for _ in range(reps):
         eng.process_se_device(s1, o1.data_ptr())
     eng.sync(); ms, cnt = eng.kernel_times()
     print(f"{name:18s} ms per launch [all, trim, stats, dup, fused]:", [round(m / max(c, 1), 3) for m, c in zip(ms, cnt)])
