@@ -182,7 +182,7 @@ def kernel_name(cfg, params, impl):
     c = workload.CONFIGS[cfg]
     if c["paired"]:
         return "k_pe_v4" if impl == "b200" else "k_trim_pe+k_stats_pe"
-    return "k_se_v3" if (not params.kmer_len and impl == "b200") else "k_fused_se_ws"
+    return "k_se_v3" if (impl == "b200" and params.kmer_len <= 13) else "k_fused_se_ws"   # k-mers run as their own pass (k_kmer_se)
 
 
 class Job:
@@ -254,7 +254,8 @@ class Job:
         total_bases = total_units * self.c["L"] * (2 if self.c["paired"] else 1)
         # roofline of the dominant kernel: live CUDA-event durations on the launching stream
         fused = kernel_name(self.cfg, self.params, ctx.a.impl)
-        names = {abi.T_TRIM: "k_trim", abi.T_STATS: "k_stats", abi.T_DUP: "k_dup", abi.T_FUSED: fused}
+        stats_name = "k_kmer_se" if (not self.c["paired"] and self.params.kmer_len and ctx.a.impl == "b200") else "k_stats"
+        names = {abi.T_TRIM: "k_trim", abi.T_STATS: stats_name, abi.T_DUP: "k_dup", abi.T_FUSED: fused}
         dom = max(names, key=lambda s: kms[s])
         per_launch_ms = kms[dom] / max(kn[dom], 1)
         per_launch_units = min(BATCH_READS, self.units)
