@@ -641,8 +641,9 @@ static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq
         outs[ch].len = h.tot[ch]; outs[ch].records = h.cnt[ch];
         to.p[ch] = nullptr;
         if(!h.tot[ch]) continue;
+        if(!outs[ch].data) continue;                                      // channel not wanted: sizes and counts only
         if(h.tot[ch] > 0xFFFFFFF0ull) rc = fail(c, FQK_E_LIMIT, "a text channel of a pack exceeds 4 GiB: use smaller packs");
-        else if(!outs[ch].data || outs[ch].cap < h.tot[ch]) rc = fail(c, FQK_E_LIMIT, "text output buffer too small (fq_text_out.len holds the size needed)");
+        else if(outs[ch].cap < h.tot[ch]) rc = fail(c, FQK_E_LIMIT, "text output buffer too small (fq_text_out.len holds the size needed)");
         else if(c->tout[ch].ensure(h.tot[ch] + 16)) rc = fail(c, FQK_E_NOMEM, "text block allocation failed");
         to.p[ch] = (char*)c->tout[ch].p;
     }
@@ -651,7 +652,7 @@ static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq
     text_launch_copy(c->stream, paired, n, writers, m1, m2, r1, r2, rp, (const uint32_t*)c->tsizes.p, to);
     c->launches++;
     for(int ch = 0; ch < FQK_CH_COUNT; ++ch)
-        if(h.tot[ch]) CU(cudaMemcpyAsync(outs[ch].data, c->tout[ch].p, h.tot[ch], cudaMemcpyDeviceToHost, c->stream));
+        if(h.tot[ch] && outs[ch].data) CU(cudaMemcpyAsync(outs[ch].data, c->tout[ch].p, h.tot[ch], cudaMemcpyDeviceToHost, c->stream));
     CU(cudaGetLastError());
     return 0;
 }

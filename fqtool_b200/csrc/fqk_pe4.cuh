@@ -664,10 +664,16 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
         if(both && isize != P.insert_size_max) reds_add(X.ins32 + 4u * (uint32_t)isize, 1u);
     }
     bool modified = false;                                   // reads changed since the first analyze()
+    bool known2 = false;                                     // ... in a way that makes the second analyze()'s answer known
     if(both && P.adapter_trim_enabled){
         // AdapterTrimmer::trimByOverlapAnalysis, src/adaptertrimmer.cpp:14-27
         if(ov.diff <= 5 && ov.overlapped && ov.offset < 0 && ov.len > a.len / 3){
             const int t1 = a.len - ov.len, t2 = b.len - ov.len;
+            // Both reads are cut to the overlap.  When the overlap ran to the end of read 2's reverse complement
+            // (ov.len == len2 + offset) the cut reads are reverse complements over their whole length: the second analyze()
+            // tries offset 0 first (ov.len > overlapRequire holds because loop B only visits offsets > overlapRequire - len2),
+            // compares exactly the base pairs the accepted alignment compared, and returns (offset 0, ov.len, same diff).
+            known2 = ov.len == b.len + ov.offset;
             a.len = ov.len; b.len = ov.len;
             rec1.flags |= FQK_F_ADAPTER_OV; rec1.adapter_pos = (int16_t)ov.len; rec1.adapter_len = (uint16_t)t1;
             rec2.flags |= FQK_F_ADAPTER_OV; rec2.adapter_pos = (int16_t)ov.len; rec2.adapter_len = (uint16_t)t2;
@@ -704,6 +710,10 @@ __device__ inline void v4_chunk(const V4X& X, const int j, const int lane, Tally
     V4_PROF(prof, 3);
     // second analyze(), :354: same answer as the first when neither read changed
     OvRes ov2 = ov;
+    if(known2 && a.len == ov.len && b.len == ov.len){        // nothing touched the reads after the overlap trim
+        ov2.overlapped = 1; ov2.offset = 0; ov2.len = ov.len; ov2.diff = ov.diff;
+        modified = false;
+    }
     if(!(X.dbg & 8)) v4_overlap_chunk(a, b, P.merge_enabled && both && modified, P.overlap_diff_limit, P.overlap_require, lane, ov2);
     V4_GSYNC(X);
     V4_PROF(prof, 4);

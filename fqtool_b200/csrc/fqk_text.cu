@@ -254,7 +254,7 @@ __global__ void k_text_copy(bool paired, uint32_t n, uint32_t writers, TextMate 
             uint32_t u = 0;
 #pragma unroll
             for(int c = 0; c < FQK_CH_COUNT; ++c) if(ch == c) u = used[c];
-            write_piece(pc[k], out.p[ch], offsets[(size_t)ch * n + i] + u, m1, m2, i, x1, x2, pr, lane);
+            if(out.p[ch]) write_piece(pc[k], out.p[ch], offsets[(size_t)ch * n + i] + u, m1, m2, i, x1, x2, pr, lane);   // nullptr: channel not wanted
             const uint32_t b = piece_bytes(pc[k], m1, m2, i, x1, x2, pr);
 #pragma unroll
             for(int c = 0; c < FQK_CH_COUNT; ++c) if(ch == c) used[c] += b;

@@ -121,6 +121,28 @@ struct Mate {
     }
 };
 
+// names and third lines of one mate as flat buffers (fq_text_batch), for the text entry points
+struct MateText {
+    std::string names, strands; std::vector<uint64_t> noff, soff;
+    size_t textBytes = 0;          // upper bound of the FASTQ text of the pack (untrimmed records)
+    template<class GetRead> void load(size_t n, GetRead get, const fq_ascii_batch& reads, fq_text_batch& b){
+        names.clear(); strands.clear(); noff.assign(n + 1, 0); soff.assign(n + 1, 0);
+        for(size_t i = 0; i < n; ++i){
+            Read* r = get(i);
+            noff[i] = names.size(); names += r->name;
+            soff[i] = strands.size(); strands += r->strand;
+        }
+        noff[n] = names.size(); soff[n] = strands.size();
+        textBytes = names.size() + strands.size() + 2 * (size_t)reads.off[n] + 4 * n;
+        b.reads = reads; b.name_off = noff.data(); b.names = names.data(); b.strand_off = soff.data(); b.strands = strands.data();
+    }
+};
+// FQK_SEAM_TEXT=0 switches the worker bodies back to one std::string per read on the host (A/B and tests)
+inline bool useText(){ static const bool on = !(std::getenv("FQK_SEAM_TEXT") && std::atoi(std::getenv("FQK_SEAM_TEXT")) == 0); return on; }
+// a text channel the caller wants: a heap block that is handed to the WriterThread as it is (WriterThread frees it)
+inline void wantChannel(fq_text_out* outs, int ch, size_t cap){ outs[ch].data = new char[cap ? cap : 1]; outs[ch].cap = cap; }
+inline void dropChannels(fq_text_out* outs){ for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ delete[] outs[ch].data; outs[ch].data = nullptr; } }
+
 struct Seam {
     std::mutex mtx;                 // one GPU context per process; worker threads take turns (pack order = call order)
     fqk_ctx* ctx = nullptr;
@@ -128,6 +150,7 @@ struct Seam {
     fq_stats_layout L;
     uint64_t firstIndex = 0;        // global index of the next read (Duplicate's first-read-wins rule needs input order)
     Mate m[2];
+    MateText t[2];
     std::vector<fq_pair_result> pairs;
     std::vector<fq_correction> edits;
 

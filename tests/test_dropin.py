@@ -57,25 +57,31 @@ def test_dropin_binary_links_against_libfqk():
     assert "libfqk.so" in r.stdout and "not found" not in r.stdout
 
 
-def _run(exe, case, d, pack):
+def _run(exe, case, d, pack, seam_text=None):
     paired, flags = CASES[case]
     os.makedirs(d, exist_ok=True)
+    env = dict(os.environ)
+    if seam_text is not None:
+        env["FQK_SEAM_TEXT"] = str(seam_text)
     make_e2e.CASES.setdefault(case, CASES[case])
     cmd = make_e2e.command(exe, case, FQ1, FQ2, d) + ["-w", "1", "-J", os.path.join(d, "report.json"),
                                                        "-H", os.path.join(d, "report.html"), "--max_item_in_pack", str(pack)]
-    r = subprocess.run(cmd, capture_output=True, text=True, cwd=d)
+    r = subprocess.run(cmd, capture_output=True, text=True, cwd=d, env=env)
     assert r.returncode == 0, f"{' '.join(cmd)}\n{r.stdout}\n{r.stderr}"
     return r
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("seam_text", [1, 0], ids=["device_text", "host_strings"])
 @pytest.mark.parametrize("case", sorted(CASES))
-def test_dropin_matches_reference_program(case, tmp_path):
+def test_dropin_matches_reference_program(case, seam_text, tmp_path):
+    """seam_text 1: the worker bodies get the output TEXT from the device (fqk_process_*_text, the default);
+    0: they build one std::string per read on the host from the records (fqk_process_*_ascii)."""
     if not _have():
         pytest.skip("drop-in binaries not built (reference sources absent)")
     dr, dg = str(tmp_path / "ref"), str(tmp_path / "fqk")
     _run(REF, case, dr, 700)
-    _run(FQK, case, dg, 700)
+    _run(FQK, case, dg, 700, seam_text)
     names = sorted(f for f in os.listdir(dr) if f.endswith(".fq"))
     assert names, "the reference wrote no output"
     for f in names:
