@@ -344,7 +344,7 @@ static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
         Timer t(c, FQK_T_STATS);
         const int K = c->D.P.kmer_len;
         const int use_smem = K <= 6;
-        k_kmer_se<<<c->sms * (use_smem ? 4 : 8), 256, use_smem ? (size_t)2 * 4 * ((size_t)1 << (2 * K)) : 0, c->stream>>>(c->D, B, out, c->flat, use_smem);
+        k_kmer_se<<<c->sms * 4, 512, use_smem ? (size_t)2 * 4 * ((size_t)1 << (2 * K)) : 0, c->stream>>>(c->D, B, out, c->flat, use_smem);
         c->launches++;
     }else if(c->impl != 1 && fused_supported_se(c->D, B)){
         Timer t(c, FQK_T_FUSED);

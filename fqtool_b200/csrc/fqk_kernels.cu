@@ -561,7 +561,7 @@ __device__ __forceinline__ uint32_t nflags16_g(const uint8_t* q){               
     for(int k = 0; k < 4; ++k) m |= ((((w[k] >> 7) & 0x01010101u) * 0x00204081u) >> 21 & 0xFu) << (4 * k);
     return m;
 }
-__global__ void __launch_bounds__(256) k_kmer_se(const __grid_constant__ DevParams D, DevBatch B, const fq_read_result* __restrict__ recs,
+__global__ void __launch_bounds__(512) k_kmer_se(const __grid_constant__ DevParams D, DevBatch B, const fq_read_result* __restrict__ recs,
                                                   uint64_t* __restrict__ flat, int use_smem){
     extern __shared__ uint32_t sh_hist[];                                        // [2][4^k] when use_smem: both, pre only
     const int K = D.P.kmer_len;
@@ -572,13 +572,19 @@ __global__ void __launch_bounds__(256) k_kmer_se(const __grid_constant__ DevPara
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     // per warp: the packed words and N masks of the read in hand, word w at index w + 1 (index 0 = "word -1" = nothing)
-    __shared__ uint32_t s_c[8][34], s_n[8][34];
+    __shared__ uint32_t s_c[16][34], s_n[16][34];
     const uint32_t wmask = (1u << K) - 1u;
+    // the metadata of the warp's next read is fetched while it works on the current one (the loads at the top of the loop
+    // were half of the stall samples, profiles/r02v_*)
+    uint32_t noff = 0, nlen = 0; uint2 nrec = make_uint2(0u, 0u);
+    if(warp < B.n){ noff = B.offsets[warp]; nlen = B.lengths[warp]; nrec = *reinterpret_cast<const uint2*>(recs + warp); }
     for(uint32_t r = warp; r < B.n; r += nwarps){
-        const uint32_t off = B.offsets[r], len = B.lengths[r];
-        const fq_read_result x = recs[r];
-        const bool pass = !(x.flags & FQK_F_DROPPED) && x.result == FQK_PASS_FILTER;
-        const uint32_t vs = x.start, ve = (uint32_t)x.start + x.len;            // kept part [vs, ve)
+        const uint32_t off = noff, len = nlen;
+        const uint2 xr = nrec;                                                  // start | len << 16, result | flags << 8 | ...
+        if(r + nwarps < B.n){ noff = B.offsets[r + nwarps]; nlen = B.lengths[r + nwarps]; nrec = *reinterpret_cast<const uint2*>(recs + r + nwarps); }
+        const uint32_t xstart = xr.x & 0xFFFFu, xlen = xr.x >> 16, xresult = xr.y & 0xFFu, xflags = (xr.y >> 8) & 0xFFu;
+        const bool pass = !(xflags & FQK_F_DROPPED) && xresult == FQK_PASS_FILTER;
+        const uint32_t vs = xstart, ve = xstart + xlen;                         // kept part [vs, ve)
         const uint32_t nw = (len + 15u) >> 4;
         for(uint32_t w0 = 0; w0 < nw; w0 += 32){                                // 512 positions per round
             __syncwarp();
