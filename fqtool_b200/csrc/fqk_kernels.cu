@@ -427,6 +427,32 @@ __device__ inline uint32_t gc_count(const ReadView& v){
     for(int i = 0; i < v.len; ++i){ const int c = v.cls(i); g += (c == 2 || c == 3); }
     return g;
 }
+// The same on whole words when the read's buffers are aligned (the batch layout guarantees it for dense batches):
+// C and G are the codes with bit 1 set, N and the padding carry code 0, so the GC count of a raw read is a popcount per
+// packed word; the k-mer codes are a 64-bit window of the packed bases with the 2-bit groups reversed (seq2int puts the
+// first base on top); an N inside [p, p+n) is bit 7 of one of its quality bytes.
+__device__ __forceinline__ uint32_t gc_count_words(const ReadView& v){
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(v.b2);
+    const int nw = (v.len + 15) >> 4;
+    uint32_t g = 0;
+    for(int i = 0; i < nw; ++i) g += (uint32_t)__popc(w[i] & 0xAAAAAAAAu);
+    return g;
+}
+__device__ __forceinline__ bool dup_code_words(const ReadView& v, int p, int n, uint64_t& out){      // n <= 32, p + n <= len
+    for(int i = p & ~3; i < p + n; i += 4){                              // quality words covering [p, p+n)
+        uint32_t qw = *reinterpret_cast<const uint32_t*>(v.q + i) & 0x80808080u;
+        if(i < p) qw &= 0xFFFFFFFFu << (8 * (p - i));
+        if(i + 4 > p + n) qw &= 0xFFFFFFFFu >> (8 * (i + 4 - p - n));
+        if(qw) return false;
+    }
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(v.b2);
+    const int wi = p >> 4; const uint32_t sh = 2u * ((uint32_t)p & 15u);
+    const uint32_t w0 = w[wi], w1 = w[wi + 1], w2 = sh ? w[wi + 2] : 0u;      // (words past the read exist: next read or the batch's tail pad)
+    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);          // bases p .. p+31
+    const uint64_t v64 = ((uint64_t)rev2(lo) << 32) | rev2(hi);                               // base p on top
+    out = n >= 32 ? v64 : (v64 >> (2 * (32 - n)));
+    return true;
+}
 
 __device__ inline void dup_insert(unsigned long long* tab128, unsigned long long* first64,
                                   uint32_t key, uint64_t kmer, uint64_t gidx, uint32_t gcbyte){
@@ -449,21 +475,36 @@ __device__ inline void dup_insert(unsigned long long* tab128, unsigned long long
 __global__ void __launch_bounds__(256) k_dup(const __grid_constant__ DevParams D, DevBatch B1, DevBatch B2, int paired,
                                               unsigned long long* tab128, unsigned long long* first64){
     const int kl = D.P.dup_keylen;
+    // word-wise form when every buffer is 4-byte aligned (reads start at multiples of 16 bases)
+    const bool fast = ((reinterpret_cast<uintptr_t>(B1.qual) | reinterpret_cast<uintptr_t>(B1.bases2) |
+                        (paired ? reinterpret_cast<uintptr_t>(B2.qual) | reinterpret_cast<uintptr_t>(B2.bases2) : 0)) & 3) == 0;
     for(uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B1.n; r += gridDim.x * blockDim.x){
         ReadView a = make_view(B1, r);
         uint64_t key64, kmer; uint32_t gc; int tot;
         if(!paired){
             if(a.len < 32) continue;                                        // :65-67
-            if(!dup_code(a, 0, kl, key64)) continue;
-            if(!dup_code(a, max(0, a.len - 37), 32, kmer)) continue;        // :70,79
-            gc = gc_count(a) & 0xFF;                                        // uint8_t counter wraps, :83-89
+            if(fast){
+                if(!dup_code_words(a, 0, kl, key64)) continue;
+                if(!dup_code_words(a, max(0, a.len - 37), 32, kmer)) continue;
+                gc = gc_count_words(a) & 0xFF;
+            }else{
+                if(!dup_code(a, 0, kl, key64)) continue;
+                if(!dup_code(a, max(0, a.len - 37), 32, kmer)) continue;    // :70,79
+                gc = gc_count(a) & 0xFF;                                    // uint8_t counter wraps, :83-89
+            }
             tot = a.len;
         }else{
             ReadView b = make_view(B2, r);
             if(a.len < 32 || b.len < 32) continue;                          // :96-98
-            if(!dup_code(a, 0, kl, key64)) continue;
-            if(!dup_code(b, 0, 32, kmer)) continue;                         // :108
-            gc = (gc_count(a) + gc_count(b)) & 0xFF;
+            if(fast){
+                if(!dup_code_words(a, 0, kl, key64)) continue;
+                if(!dup_code_words(b, 0, 32, kmer)) continue;
+                gc = (gc_count_words(a) + gc_count_words(b)) & 0xFF;
+            }else{
+                if(!dup_code(a, 0, kl, key64)) continue;
+                if(!dup_code(b, 0, 32, kmer)) continue;                     // :108
+                gc = (gc_count(a) + gc_count(b)) & 0xFF;
+            }
             tot = a.len + b.len;
         }
         const uint32_t gcbyte = (uint32_t)(uint8_t)round(255.0 * (double)gc / (double)tot);   // :91,127
