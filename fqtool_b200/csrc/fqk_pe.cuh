@@ -297,9 +297,10 @@ __device__ inline bool dev_trim_by_sequence_packed(ReadView& v, const uint32_t* 
     for(; pos < 0 && pos < rlen - 4 && !found; ++pos) found = general(pos);
     if(found) --pos;
     if(!found && aligned && alen >= 16){
-        // the bulk: the whole adapter fits (cmplen == alen): constant budget and mask.  Sixteen positions per step: three
-        // words give the 32 bases from the step's first position, every window is one funnel shift by a constant.
-        const int allowed = alen / 8, last = min(rlen - alen, rlen - 5);
+        // the bulk: every position whose comparison covers a whole first word (cmplen >= 16).  Sixteen positions per step:
+        // three words give the 32 bases from the step's first position, every window is one funnel shift by a constant;
+        // the budget cmplen / 8 shrinks over the last alen positions.
+        const int last = rlen - 16;
         const uint32_t A0 = adc[0];
         if(pos <= last){
             const int q0 = v.start + pos;
@@ -310,17 +311,19 @@ __device__ inline bool dev_trim_by_sequence_packed(ReadView& v, const uint32_t* 
                 const uint32_t wc = bw[wi + 2];
                 const uint32_t B0 = __funnelshift_r(wa, wb, sh), B1 = __funnelshift_r(wb, wc, sh);     // bases pos .. pos+31 of the view
                 wa = wb; wb = wc;
+                const int room = rlen - pos;                                                          // cmplen of position pos + k = min(room - k, alen)
                 uint32_t cm = 0;
 #pragma unroll
                 for(int k = 0; k < 16; ++k){
                     const uint32_t t = (k ? __funnelshift_r(B0, B1, 2 * k) : B0) ^ A0;
-                    cm |= (__popc((t | (t >> 1)) & 0x55555555u) <= allowed) ? (1u << k) : 0u;
+                    cm |= (__popc((t | (t >> 1)) & 0x55555555u) <= (min(room - k, alen) >> 3)) ? (1u << k) : 0u;
                 }
                 const int nv = last - pos + 1;
                 if(nv < 16) cm &= (1u << nv) - 1u;
                 while(cm){
                     const int k = __ffs((int)cm) - 1; cm &= cm - 1u;
-                    if(exact(pos + k, alen, allowed)){ found = true; pos += k - 16; break; }           // (the loop adds 16 back)
+                    const int cl = min(room - k, alen);
+                    if(exact(pos + k, cl, cl >> 3)){ found = true; pos += k - 16; break; }             // (the loop adds 16 back)
                 }
             }
             if(!found) pos = last + 1;
