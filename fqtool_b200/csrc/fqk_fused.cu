@@ -726,10 +726,10 @@ size_t g_smem_optin = 0;
 #include "fqk_pe4.cuh"
 
 // largest tile (multiple of 32 reads, whole quads per statistics group preferred) whose NS stages fit
-int v3_tile(int W){
+int v3_tile(int W, int nstat = V3_STATS){
     const size_t budget = g_smem_optin > 4096 ? g_smem_optin - 1024 : 0;
-    if(W > V3_STATS) return 0;
-    const int G = V3_STATS / W;
+    if(W > nstat) return 0;
+    const int G = nstat / W;
     int fallback = 0;
     for(int T = 256; T >= 32; T -= 32){
         const V3L l = v3_layout(W, T);
@@ -759,6 +759,7 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_fused_se_ws<2, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_se_v3<false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<false>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
@@ -790,7 +791,11 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
                     int variant){
     const int W = (int)(D.L.max_cycles + 3) / 4;
     if(variant == 0 && !D.P.kmer_len && v3_tile(W) > 0){
-        const int T = v3_tile(W);
+        // generic option sets (adapter by sequence, polyG / polyX, ...): the trim role is the long one (one lane per read,
+        // dependent scalar chains), so it gets 11 working warps and the statistics 4 (FQK_V3_WIDE=0 keeps 7 + 8)
+        static const bool wide_on = !(getenv("FQK_V3_WIDE") && atoi(getenv("FQK_V3_WIDE")) == 0);
+        const bool wide = wide_on && !v3_fast_options(D.P) && v3_tile(W, 128) > 0;
+        const int T = wide ? v3_tile(W, 128) : v3_tile(W);
         int rpb = (int)((B.n + sms - 1) / sms);
         rpb = std::min(rpb, 1 << 24);                          // 32-bit per-block sums of quality characters
         rpb = (rpb + T - 1) / T * T;
@@ -798,6 +803,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         const size_t sm = v3_layout(W, T).total + 128;
         static const int dbg = getenv("FQK_V3_DEBUG") ? atoi(getenv("FQK_V3_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
         if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
+        else if(wide) k_se_v3<false, 128><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         else k_se_v3<false><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }

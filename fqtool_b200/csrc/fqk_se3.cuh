@@ -262,10 +262,13 @@ __device__ __noinline__ void z_word_atomic(uint32_t qraw, uint32_t b, int nv, ui
 // exception entry (8 bytes): x = (tile offset)/16 | raw length << 17,  y = kept start | kept length << 13 | kind << 26
 // kind 1: the read is not in the output (D = whole read); kind 2: passing read, trimmed (D = what was cut off when the
 // front is intact, else D = whole read and Z = kept part at its shifted cycle)
-template <bool FAST>
+// NSTAT: statistics threads (256, or 128 for option sets whose trim role is the long one: 4 statistics warps, 11 trim
+// warps + the producer)
+template <bool FAST, int NSTAT = V3_STATS>
 __global__ void __launch_bounds__(V3_THREADS, 1)
 k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restrict__ out,
         uint64_t* __restrict__ flat, int W, int T, int reads_per_block, int dbg){
+    constexpr int VS = NSTAT, VT = V3_THREADS - NSTAT, VW = VT / 32 - 1;       // statistics threads, trim threads, working trim warps
     extern __shared__ __align__(128) uint8_t smraw[];
     const fq_params& P = D.P;
     const V3L L = v3_layout(W, T);
@@ -288,7 +291,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     counters_zero(bc);
     if(threadIdx.x == 0){
         for(int s = 0; s < V3_NS; ++s){
-            mbar_init(&full[s], 1); mbar_init(&ready[s], (uint32_t)CH); mbar_init(&freeb[s], V3_STATS / 32);
+            mbar_init(&full[s], 1); mbar_init(&ready[s], (uint32_t)CH); mbar_init(&freeb[s], VS / 32);
             *reinterpret_cast<uint32_t*>(sp + (size_t)s * L.stage_bytes + L.o_cnt + 12) = 0xFFFFFFFFu;   // tile tag: nothing staged yet
         }
         blkmax[0] = 0;
@@ -312,12 +315,12 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
     PROF_T(t_block);
 
     // role of a thread: the statistics warps take the high warp ids (V3_STATS_HIGH) or the low ones
-    const bool is_trim = V3_STATS_HIGH ? (threadIdx.x < V3_TRIM) : (threadIdx.x >= V3_STATS);
-    const int rtid = V3_STATS_HIGH ? (is_trim ? threadIdx.x : threadIdx.x - V3_TRIM) : (is_trim ? threadIdx.x - V3_STATS : threadIdx.x);
+    const bool is_trim = V3_STATS_HIGH ? (threadIdx.x < VT) : (threadIdx.x >= VS);
+    const int rtid = V3_STATS_HIGH ? (is_trim ? threadIdx.x : threadIdx.x - VT) : (is_trim ? threadIdx.x - VS : threadIdx.x);
     if(is_trim){
         asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
         const int tw = rtid >> 5;
-        if(tw == V3_WORKERS){
+        if(tw == VW){
             // ============================== copy producer ==============================
             uint32_t a = 0, last = 0, ll = 0;
             if(ntiles > 0){ const uint32_t nt = min((uint32_t)T, hi - lo); a = B.offsets[lo]; last = B.offsets[lo + nt - 1]; ll = B.lengths[lo + nt - 1]; }
@@ -331,7 +334,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                     a = B.offsets[t1]; last = B.offsets[t1 + nt1 - 1]; ll = B.lengths[t1 + nt1 - 1];
                 }
                 PROF_T(t_pw);
-                if(n >= 1) nb_sync(1 + V3_NS + s, V3_STATS + 32);
+                if(n >= 1) nb_sync(1 + V3_NS + s, VS + 32);
                 PROF_ADD(6, t_pw);
                 PROF_T(t_pi);
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
@@ -372,7 +375,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             const uint32_t pre32 = smem_u32(smPre), post32 = smem_u32(smPost);
             const uint32_t lh = 4u * NSETS * (uint32_t)C * 4u;         // byte offset of the length histogram
             const int nchunks = ntiles * CH;
-            for(int c = tw; c < nchunks; c += V3_WORKERS){
+            for(int c = tw; c < nchunks; c += VW){
                 const int k = c / CH, j = c - k * CH, s = k % V3_NS;
                 uint8_t* S = sp + (size_t)s * L.stage_bytes;
                 const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
@@ -481,14 +484,14 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                 __syncwarp();
                 PROF_ADD(1, t_tc);
                 __threadfence_block();
-                nb_arrive(1 + s, CH * 32 + V3_STATS);
+                nb_arrive(1 + s, CH * 32 + VS);
             }
             counters_add_tally(bc, tl);
         }
     }else{
         // ============================ statistics warps ============================
         asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
-        const int G = V3_STATS / Wr;
+        const int G = VS / Wr;
         const int g = rtid / Wr, w = rtid - g * Wr;
         const bool active = g < G;
         QuadAcc qa;
@@ -500,7 +503,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             const int s = k % V3_NS;
             const uint32_t S32 = sp32 + (uint32_t)s * L.stage_bytes;
             PROF_T(t_sw);
-            nb_sync(1 + s, CH * 32 + V3_STATS);
+            nb_sync(1 + s, CH * 32 + VS);
             PROF_ADD(3, t_sw);
             PROF_T(t_sp);
             if(active && !(dbg & 2)){
@@ -596,7 +599,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
             }
             __syncwarp();
             PROF_ADD(5, t_sp);
-            if(k + V3_NS < ntiles) nb_arrive(1 + V3_NS + s, V3_STATS + 32);      // the producer waits only for stages it refills
+            if(k + V3_NS < ntiles) nb_arrive(1 + V3_NS + s, VS + 32);      // the producer waits only for stages it refills
         }
         if(active){
             quad_drain(qa, smPre, smPost, C, w);
