@@ -505,7 +505,11 @@ def main():
         pin = lambda a: (lambda t: (t.numpy().__setitem__(slice(None), a), t)[1])(torch.empty(a.shape, dtype=torch.uint8, pin_memory=True))
         pnames = pin(names); pstr = pin(np.full(n1, ord("+"), dtype=np.uint8))
         noff = np.arange(n1 + 1, dtype=np.uint64) * np.uint64(nlen); soff = np.arange(n1 + 1, dtype=np.uint64)
-        tb, keep = eng._text((pnames.numpy(), noff, pseq.numpy(), pqual.numpy(), off, pstr.numpy(), soff), 0)
+        # every array of the pack pinned: a pageable source makes cudaMemcpyAsync wait for the stream, which serialises the pipeline
+        pin64 = lambda a: (lambda t: (t.numpy().__setitem__(slice(None), a.astype(np.int64)), t)[1])(torch.empty(len(a), dtype=torch.int64, pin_memory=True))
+        pnoff, psoff = pin64(noff), pin64(soff)
+        tb, keep = eng._text((pnames.numpy(), pnoff.numpy().view(np.uint64), pseq.numpy(), pqual.numpy(), poff.numpy().view(np.uint64),
+                              pstr.numpy(), psoff.numpy().view(np.uint64)), 0)
         cap = int(len(names) + 2 * len(seq) + n1 * 8)
         tout = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
         touts = (abi.FqTextOut * abi.CH_COUNT)()
@@ -516,17 +520,36 @@ def main():
             rc = eng.lib.fqk_process_se_text(eng.h, C.byref(tb), 0, None, touts, C.byref(passed))
             assert rc == 0, eng.lib.fqk_last_error(eng.h)
         text_call()
+        # two packs in flight: fqk_submit_se_text / fqk_wait_text, the upload of pack k+1 over the assembly + download of pack k
+        tout2 = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
+        touts2 = (abi.FqTextOut * abi.CH_COUNT)()
+        touts2[abi.CH_OUT1].data = tout2.data_ptr(); touts2[abi.CH_OUT1].cap = cap
+        slots = (touts, touts2)
+
+        def text_pipe(reps):
+            pend = None
+            for i in range(reps + 1):
+                tk = None
+                if i < reps:
+                    tk = C.c_uint64(0)
+                    rc = eng.lib.fqk_submit_se_text(eng.h, C.byref(tb), 0, None, slots[i & 1], C.byref(tk))
+                    assert rc == 0, eng.lib.fqk_last_error(eng.h)
+                if pend is not None:
+                    rc = eng.lib.fqk_wait_text(eng.h, pend.value, C.byref(passed))
+                    assert rc == 0, eng.lib.fqk_last_error(eng.h)
+                pend = tk
+        text_pipe(2)
         eng.reset(); ctx.barrier()
         t0 = time.perf_counter()
-        for _ in range(reps):
-            text_call()
+        text_pipe(reps)
         eng.finalize(); ctx.barrier()
         dtt = ctx.max_over_ranks(time.perf_counter() - t0)
         e2e_text = {"value": world * reps * n1 * c["L"] / dtt / 1e9, "unit": "Gbases/s", "calls": reps,
                     "h2d_bytes_per_call": int(2 * len(seq) + len(names) + n1 * (1 + 8 + 8 + 8)),
                     "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len), "records_out": int(touts[abi.CH_OUT1].records),
-                    "note": "fqk_process_se_text: FASTQ text in (names, bases, qualities), trimmed FASTQ text of the passing reads out; "
-                            "packing, trimming, statistics and record assembly on the GPU, no per-read work on the host"}
+                    "note": "fqk_submit_se_text / fqk_wait_text, two packs in flight: FASTQ text in (names, bases, qualities), trimmed FASTQ "
+                            "text of the passing reads out; packing, trimming, statistics and record assembly on the GPU, no per-read "
+                            "work on the host"}
         # ---- and from the decompressed FASTQ TEXT itself (newline scan on the device too) ----
         L1 = c["L"]
         rec_bytes = nlen + 1 + L1 + 1 + 2 + L1 + 1
@@ -553,7 +576,7 @@ def main():
                      "h2d_bytes_per_call": int(traw.numel()), "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len),
                      "note": "fqk_process_se_fastq: decompressed FASTQ text in, trimmed FASTQ text out; newline scan, packing, hot path "
                              "and record assembly on the GPU (what FqReader, the worker body and Read::toString do in the reference)"}
-        del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout, traw, tv
+        del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout, tout2, traw, tv
     del hbs, hout, batches
     job.close(); del job, eng
     ctx.free()

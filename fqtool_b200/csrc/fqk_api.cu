@@ -73,6 +73,13 @@ struct fqk_ctx {
     DevBuf tnames[2], tnoff[2], tstr[2], tsoff[2], tsizes, tscratch, ttot, tout[FQK_CH_COUNT];
     // raw FASTQ blocks (fqk_process_*_fastq): the text, newline counts/positions, quality offsets, line lengths
     DevBuf traw[2], tnlc[2], tnl[2], aqsrc[2], tnlen[2], tslen[2];
+    // pipelined text path (fqk_submit_se_text / fqk_wait_text): per slot the 64-bit name / third-line offsets, sizes, totals, blocks
+    DevBuf pno[2], pso[2], psz[2], ptt[2], pout[2][FQK_CH_COUNT];
+    cudaEvent_t evTot[2] = {nullptr, nullptr};
+    cudaStream_t tdl[2] = {nullptr, nullptr}; // one download stream per slot: the small downloads of pack k+1 (which wait for its
+                                              // kernels) must not sit in front of the text download of pack k
+    uint64_t* ptoth = nullptr;                // pinned: [2][16] totals + counters of a slot
+    struct TextSlot { uint32_t n = 0, writers = 0; fq_text_out* outs = nullptr; bool open = false; } tslot[2];
     DevBuf poff[2], pscr[2], ptot[2];         // pipelined ASCII ingest (fqk_submit_se_ascii): offsets, scan scratch, totals per slot
     bool raw_mode = false;                    // the staged mates come from raw blocks (TextMate then points into traw)
     std::vector<uint32_t> hnoff[2], hsoff[2];
@@ -286,6 +293,13 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(int i = 0; i < 2; ++i){ c->tnames[i].release(); c->tnoff[i].release(); c->tstr[i].release(); c->tsoff[i].release(); }
     c->tsizes.release(); c->tscratch.release(); c->ttot.release();
     for(int i = 0; i < 2; ++i){ c->poff[i].release(); c->pscr[i].release(); c->ptot[i].release(); }
+    for(int i = 0; i < 2; ++i){
+        c->pno[i].release(); c->pso[i].release(); c->psz[i].release(); c->ptt[i].release();
+        for(int ch = 0; ch < FQK_CH_COUNT; ++ch) c->pout[i][ch].release();
+        if(c->evTot[i]) cudaEventDestroy(c->evTot[i]);
+        if(c->tdl[i]) cudaStreamDestroy(c->tdl[i]);
+    }
+    if(c->ptoth) cudaFreeHost(c->ptoth);
     for(int i = 0; i < 2; ++i){ c->traw[i].release(); c->tnlc[i].release(); c->tnl[i].release(); c->aqsrc[i].release(); c->tnlen[i].release(); c->tslen[i].release(); }
     for(int i = 0; i < FQK_CH_COUNT; ++i) c->tout[i].release();
     cudaFree(c->flat); cudaFree(c->err); cudaFree(c->maxlen2); cudaFree(c->tab128); cudaFree(c->first64);
@@ -873,6 +887,138 @@ extern "C" int fqk_submit_se_ascii(fqk_ctx* c, const fq_ascii_batch* in, fq_read
     CU(cudaEventRecord(c->evD2H[s], c->d2h));
     *ticket = t; c->submitted = t + 1;
     return 0;
+}
+
+
+// Pipelined form of fqk_process_se_text: submit enqueues the upload, the per-read index, the packing, the hot path and the
+// sizes / prefix sums of the text; wait reads the totals, launches the copy kernel and downloads the blocks.  With two
+// packs in flight (submit k+1, then wait k) the upload of pack k+1 overlaps the assembly and the download of pack k.
+extern "C" int fqk_submit_se_text(fqk_ctx* c, const fq_text_batch* in, uint32_t writers, fq_read_result* out, fq_text_out* outs,
+                                  uint64_t* ticket){
+    if(!c || !in || !in->reads.off || !in->name_off || !in->strand_off || !outs || !ticket) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    CU(cudaSetDevice(c->device));
+    int rc = pipe_init(c); if(rc) return rc;
+    if(!c->ptoth){
+        CU(cudaHostAlloc((void**)&c->ptoth, 2 * 16 * sizeof(uint64_t), cudaHostAllocDefault));
+        for(int i = 0; i < 2; ++i){
+            CU(cudaEventCreateWithFlags(&c->evTot[i], cudaEventDisableTiming));
+            CU(cudaStreamCreateWithFlags(&c->tdl[i], cudaStreamNonBlocking));
+        }
+    }
+    const uint64_t t = c->submitted;
+    const int s = (int)(t & 1);
+    const uint32_t n = in->reads.n_reads;
+    if(c->tslot[s].open) return fail(c, FQK_E_INVALID, "fqk_wait_text of the pack two submissions back is missing");
+    if(t >= 2){ CU(cudaEventSynchronize(c->evD2H[s])); note_pack_error(c, c->perr_host[s]); }
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    c->tslot[s].n = n; c->tslot[s].writers = writers; c->tslot[s].outs = outs; c->tslot[s].open = true;
+    *ticket = t; c->submitted = t + 1;
+    if(n == 0){ CU(cudaEventRecord(c->evTot[s], c->tdl[s])); return 0; }
+    const uint64_t chars = in->reads.off[n] - in->reads.off[0];
+    const uint64_t nb = in->name_off[n] - in->name_off[0], sb = in->strand_off[n] - in->strand_off[0];
+    const uint64_t cap = ((chars + 15ull * n + 64) + FQK_BATCH_PAD - 1) / FQK_BATCH_PAD * FQK_BATCH_PAD;
+    if(chars > 0xFFFFFFF0ull || cap > 0xFFFFFFF0ull || nb > 0xFFFFFFF0ull || sb > 0xFFFFFFF0ull){
+        c->tslot[s].open = false; c->submitted = t;
+        return fail(c, FQK_E_LIMIT, "text batch larger than 2^32 characters");
+    }
+    StagedBatch& S = c->st[s];
+    if(c->aseq[s].ensure(chars + 16) || c->aqual[s].ensure(chars + 16) || c->asrc[s].ensure((size_t)n * 4 + 16) || c->poff[s].ensure((size_t)(n + 1) * 8) ||
+       c->pscr[s].ensure(text_scan_scratch_u64(n) * 8) || c->ptot[s].ensure(64) || S.off.ensure((size_t)n * 4 + 16) || S.len.ensure((size_t)n * 2 + 16) ||
+       S.b2.ensure(cap / 4 + 32) || S.q.ensure(cap + 80) || c->pres[s].ensure((size_t)n * sizeof(fq_read_result)) ||
+       c->tnames[s].ensure(nb + 16) || c->tstr[s].ensure(sb + 16) || c->pno[s].ensure((size_t)(n + 1) * 8) || c->pso[s].ensure((size_t)(n + 1) * 8) ||
+       c->tnoff[s].ensure((size_t)(n + 1) * 4) || c->tsoff[s].ensure((size_t)(n + 1) * 4) || c->psz[s].ensure((size_t)FQK_CH_COUNT * n * 4 + 16) ||
+       c->ptt[s].ensure(256)){
+        c->tslot[s].open = false; c->submitted = t;
+        return fail(c, FQK_E_NOMEM, "device staging allocation failed");
+    }
+    cudaStream_t h = c->h2d;
+    CU(cudaStreamWaitEvent(h, c->evK[s], 0));
+    CU(cudaMemcpyAsync(c->aseq[s].p, in->reads.seq + in->reads.off[0], chars, cudaMemcpyHostToDevice, h));
+    CU(cudaMemcpyAsync(c->aqual[s].p, in->reads.qual + in->reads.off[0], chars, cudaMemcpyHostToDevice, h));
+    CU(cudaMemcpyAsync(c->poff[s].p, in->reads.off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, h));
+    if(nb) CU(cudaMemcpyAsync(c->tnames[s].p, in->names + in->name_off[0], nb, cudaMemcpyHostToDevice, h));
+    if(sb) CU(cudaMemcpyAsync(c->tstr[s].p, in->strands + in->strand_off[0], sb, cudaMemcpyHostToDevice, h));
+    CU(cudaMemcpyAsync(c->pno[s].p, in->name_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, h));
+    CU(cudaMemcpyAsync(c->pso[s].p, in->strand_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, h));
+    ascii_launch_index(h, n, (const uint64_t*)c->poff[s].p, (uint32_t*)c->asrc[s].p, (uint16_t*)S.len.p, (uint32_t*)S.off.p, c->err);
+    text_launch_scan(h, n, (uint32_t*)S.off.p, (uint64_t*)c->ptot[s].p, (uint64_t*)c->pscr[s].p, 1);
+    ascii_launch_zero_tail(h, (const uint64_t*)c->ptot[s].p, (uint8_t*)S.q.p, (uint8_t*)S.b2.p);
+    k_pack_ascii<<<grid_for(c, n, 16, 8), 256, 0, h>>>(n, (const char*)c->aseq[s].p, (const char*)c->aqual[s].p, (const uint32_t*)c->asrc[s].p,
+        (const uint32_t*)S.off.p, (const uint16_t*)S.len.p, (uint8_t*)S.b2.p, (uint8_t*)S.q.p, c->err);
+    text_launch_narrow(h, n + 1, (const uint64_t*)c->pno[s].p, (uint32_t*)c->tnoff[s].p);
+    text_launch_narrow(h, n + 1, (const uint64_t*)c->pso[s].p, (uint32_t*)c->tsoff[s].p);
+    c->launches += 8;
+    S.dev.n = n; S.dev.first_index = in->reads.first_index; S.dev.total = cap; S.dev.max_len = 0;
+    S.dev.offsets = (const uint32_t*)S.off.p; S.dev.lengths = (const uint16_t*)S.len.p;
+    S.dev.bases2 = (const uint8_t*)S.b2.p; S.dev.qual = (const uint8_t*)S.q.p;
+    CU(cudaEventRecord(c->evH2D[s], h));
+    CU(cudaStreamWaitEvent(c->stream, c->evH2D[s], 0));
+    rc = launch_se(c, S.dev, (fq_read_result*)c->pres[s].p); if(rc) return rc;
+    // sizes and prefix sums of the text on the kernel stream; the scan scratch of the slot is free again by then
+    TextMate m; 
+    m.seq = (const char*)c->aseq[s].p; m.qual = (const char*)c->aqual[s].p; m.src = (const uint32_t*)c->asrc[s].p; m.qsrc = nullptr;
+    m.len = (const uint16_t*)S.len.p; m.names = (const char*)c->tnames[s].p; m.name_off = (const uint32_t*)c->tnoff[s].p;
+    m.strands = (const char*)c->tstr[s].p; m.strand_off = (const uint32_t*)c->tsoff[s].p; m.name_len = m.strand_len = nullptr;
+    uint64_t* totals = (uint64_t*)c->ptt[s].p; uint32_t* counters = (uint32_t*)(totals + FQK_CH_COUNT);
+    CU(cudaMemsetAsync(c->ptt[s].p, 0, 256, c->stream));
+    if(c->pscr[s].ensure(text_scan_scratch_u64(n) * 8)) return fail(c, FQK_E_NOMEM, "text scratch allocation failed");
+    text_launch_sizes(c->stream, false, n, writers, m, m, (const fq_read_result*)c->pres[s].p, nullptr, nullptr, (uint32_t*)c->psz[s].p, counters);
+    text_launch_scan(c->stream, n, (uint32_t*)c->psz[s].p, totals, (uint64_t*)c->pscr[s].p);
+    c->launches += 4;
+    CU(cudaEventRecord(c->evK[s], c->stream));
+    cudaStream_t dl = c->tdl[s];
+    CU(cudaStreamWaitEvent(dl, c->evK[s], 0));
+    if(out) CU(cudaMemcpyAsync(out, c->pres[s].p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, dl));
+    CU(cudaMemcpyAsync(c->ptoth + 16 * s, c->ptt[s].p, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, dl));
+    CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, dl));
+    CU(cudaEventRecord(c->evTot[s], dl));
+    return 0;
+}
+
+extern "C" int fqk_wait_text(fqk_ctx* c, uint64_t ticket, uint64_t* read_passed){
+    if(!c || ticket >= c->submitted) return FQK_E_INVALID;
+    const int s = (int)(ticket & 1);
+    if(!c->tslot[s].open || ticket + 2 < c->submitted) return fail(c, FQK_E_INVALID, "no text pack with this ticket is in flight");
+    CU(cudaSetDevice(c->device));
+    fqk_ctx::TextSlot& ts = c->tslot[s];
+    ts.open = false;
+    if(read_passed) *read_passed = 0;
+    CU(cudaEventSynchronize(c->evTot[s]));
+    if(ts.n == 0){ CU(cudaEventRecord(c->evD2H[s], c->tdl[s])); return c->sticky ? fail(c, c->sticky, c->sticky_msg) : 0; }
+    note_pack_error(c, c->perr_host[s]);
+    const uint64_t* tot = c->ptoth + 16 * s;
+    const uint32_t* cnt = reinterpret_cast<const uint32_t*>(tot + FQK_CH_COUNT);
+    int rc = 0;
+    TextOut to;
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){
+        ts.outs[ch].len = tot[ch]; ts.outs[ch].records = cnt[ch];
+        to.p[ch] = nullptr;
+        if(!tot[ch] || !ts.outs[ch].data) continue;
+        if(tot[ch] > 0xFFFFFFF0ull) rc = fail(c, FQK_E_LIMIT, "a text channel of a pack exceeds 4 GiB: use smaller packs");
+        else if(ts.outs[ch].cap < tot[ch]) rc = fail(c, FQK_E_LIMIT, "text output buffer too small (fq_text_out.len holds the size needed)");
+        else if(c->pout[s][ch].ensure(tot[ch] + 16)) rc = fail(c, FQK_E_NOMEM, "text block allocation failed");
+        to.p[ch] = (char*)c->pout[s][ch].p;
+    }
+    if(read_passed) *read_passed = cnt[FQK_CH_COUNT];
+    if(!rc && !c->sticky){
+        StagedBatch& S = c->st[s];
+        TextMate m;
+        m.seq = (const char*)c->aseq[s].p; m.qual = (const char*)c->aqual[s].p; m.src = (const uint32_t*)c->asrc[s].p; m.qsrc = nullptr;
+        m.len = (const uint16_t*)S.len.p; m.names = (const char*)c->tnames[s].p; m.name_off = (const uint32_t*)c->tnoff[s].p;
+        m.strands = (const char*)c->tstr[s].p; m.strand_off = (const uint32_t*)c->tsoff[s].p; m.name_len = m.strand_len = nullptr;
+        // the copy kernel and the download run on the download stream: the kernel stream may already hold the next pack
+        text_launch_copy(c->tdl[s], false, ts.n, ts.writers, m, m, (const fq_read_result*)c->pres[s].p, nullptr, nullptr, (const uint32_t*)c->psz[s].p, to);
+        c->launches++;
+        for(int ch = 0; ch < FQK_CH_COUNT; ++ch)
+            if(to.p[ch]) CU(cudaMemcpyAsync(ts.outs[ch].data, to.p[ch], tot[ch], cudaMemcpyDeviceToHost, c->tdl[s]));
+    }
+    // the slot's staging buffers are read by the copy kernel: the next upload into this slot waits for it
+    CU(cudaEventRecord(c->evD2H[s], c->tdl[s]));
+    CU(cudaEventRecord(c->evK[s], c->tdl[s]));
+    CU(cudaEventSynchronize(c->evD2H[s]));
+    if(rc) return rc;
+    return c->sticky ? fail(c, c->sticky, c->sticky_msg) : 0;
 }
 
 // Pipelined form of fqk_process_se: the upload of pack k+1 overlaps the kernels and the download of pack k

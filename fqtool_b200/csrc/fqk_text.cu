@@ -345,6 +345,11 @@ __global__ void k_zero_tail(const uint64_t* __restrict__ total, uint8_t* __restr
     if(threadIdx.x < 16) bases2[t / 4 + threadIdx.x] = 0;
 }
 
+__global__ void k_narrow(uint32_t n, const uint64_t* __restrict__ in, uint32_t* __restrict__ out){
+    const uint64_t b = in[0];
+    for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = (uint32_t)(in[i] - b);
+}
+
 } // namespace
 
 // ------------------------------------------------------------------ launchers
@@ -392,4 +397,7 @@ void ascii_launch_index(cudaStream_t st, uint32_t n, const uint64_t* off, uint32
 }
 void ascii_launch_zero_tail(cudaStream_t st, const uint64_t* total, uint8_t* qual, uint8_t* bases2){
     k_zero_tail<<<1, 64, 0, st>>>(total, qual, bases2);
+}
+void text_launch_narrow(cudaStream_t st, uint32_t n, const uint64_t* in, uint32_t* out){
+    if(n) k_narrow<<<text_grid(n, 256), 256, 0, st>>>(n, in, out);
 }

@@ -54,3 +54,5 @@ void fastq_launch_index(cudaStream_t st, const char* text, const uint32_t* nlpos
 void ascii_launch_index(cudaStream_t st, uint32_t n, const uint64_t* off, uint32_t* src, uint16_t* len, uint32_t* padlen, uint32_t* err);
 // zero the 64 bytes (16 base bytes) after the last padded read: *total = end of the packed data
 void ascii_launch_zero_tail(cudaStream_t st, const uint64_t* total, uint8_t* qual, uint8_t* bases2);
+// out[i] = (uint32_t)(in[i] - in[0]), i < n (offset arrays of a text batch narrowed on the device: pipelined text path)
+void text_launch_narrow(cudaStream_t st, uint32_t n, const uint64_t* in, uint32_t* out);

@@ -127,6 +127,23 @@ class Engine:
                                                (abi.ptr(out[0]), abi.ptr(out[1]), abi.ptr(out[2])))
         return blocks, nrec, passed, out
 
+    def submit_se_text(self, rec, writers=0, first_index=0):
+        """Pipelined fqk_process_se_text; returns a handle for wait_text (it keeps every buffer of the pack alive)."""
+        b, keep = self._text(rec, first_index)
+        hint = int(len(keep[0]) + 2 * len(keep[2]) + len(keep[5]) + 40 * b.reads.n_reads + 64)
+        bufs, outs = self._fastq_outs(hint)
+        out = np.zeros(b.reads.n_reads, dtype=abi.READ_RESULT_DTYPE)
+        t = C.c_uint64(0)
+        self._check(self.lib.fqk_submit_se_text(self.h, C.byref(b), writers, abi.ptr(out), outs, C.byref(t)), "fqk_submit_se_text")
+        return {"ticket": t.value, "keep": (b, keep), "bufs": bufs, "outs": outs, "records": out}
+
+    def wait_text(self, handle):
+        passed = C.c_uint64(0)
+        self._check(self.lib.fqk_wait_text(self.h, handle["ticket"], C.byref(passed)), "fqk_wait_text")
+        outs, bufs = handle["outs"], handle["bufs"]
+        return ([bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], [int(outs[ch].records) for ch in range(abi.CH_COUNT)],
+                int(passed.value), handle["records"])
+
     # ---- raw FASTQ blocks: decompressed text in, FASTQ text out (fqk_process_*_fastq) ----
     def _fastq_outs(self, nbytes):
         bufs = [np.zeros(max(nbytes, 16), dtype=np.uint8) for _ in range(abi.CH_COUNT)]

@@ -306,6 +306,15 @@ int  fqk_process_pe_text(fqk_ctx* ctx, const fq_text_batch* r1, const fq_text_ba
                          fq_read_result* out1, fq_read_result* out2, fq_pair_result* outp,
                          fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed);
 
+/* Pipelined form of fqk_process_se_text: fqk_submit_se_text enqueues the upload, the packing, the hot path and the sizes
+ * of the text blocks; fqk_wait_text assembles and downloads them and fills outs[].len / .records (the array given to
+ * submit, which must stay valid, like every buffer of the pack, until the wait returns).  Keep two packs in flight
+ * (submit k+1, then wait k): the upload of pack k+1 overlaps the assembly and download of pack k.  Every submitted
+ * pack must be waited for, in order, before the pack after the next one is submitted. */
+int  fqk_submit_se_text(fqk_ctx* ctx, const fq_text_batch* in, uint32_t writers, fq_read_result* out,
+                        fq_text_out outs[FQK_CH_COUNT], uint64_t* ticket);
+int  fqk_wait_text(fqk_ctx* ctx, uint64_t ticket, uint64_t* read_passed);
+
 /*
  * Raw FASTQ entry points: the host hands over the DECOMPRESSED TEXT of a FASTQ block as it
  * comes out of gzread and gets FASTQ text back; the newline scan of FqReader::getLine / FqReader::read

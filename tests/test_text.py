@@ -144,3 +144,36 @@ def test_raw_fastq_crlf_and_malformed():
     with pytest.raises(FqkError):
         eng.process_se_fastq(b"\n".join(lines))
     eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["cfg2_r1", "cfg4_r1", "se_failed"])
+def test_pipelined_text_matches_reference_files(case):
+    """fqk_submit_se_text / fqk_wait_text with two packs in flight: same files as the reference program, same accumulators
+    as the synchronous call."""
+    from fqtool_b200.engine import Engine
+    paired, flags = make_e2e.CASES[case]
+    o = from_cli(flags.split()); o.maxCycles = 320
+    r1 = parse_fastq(FQ[0])
+    outs = make_e2e.outputs(case, paired, "")
+    writers = abi.W_FAILED if "--failed_out" in outs else 0
+    eng = Engine(o.to_params())
+    acc = [b""] * abi.CH_COUNT
+    pending = None
+    for lo in list(range(0, len(r1), 450)) + [None]:
+        h = eng.submit_se_text(flat(r1, lo, min(len(r1), lo + 450)), writers, lo) if lo is not None else None
+        if pending is not None:
+            blocks, nrec, passed, recs = eng.wait_text(pending)
+            assert passed == nrec[abi.CH_OUT1]
+            for ch in range(abi.CH_COUNT):
+                acc[ch] += blocks[ch]
+        pending = h
+    flat_pipe = eng.finalize()
+    eng.close()
+    for name, want in EXPECTED[case]["files"].items():
+        assert hashlib.md5(acc[FILES[name]]).hexdigest() == want, f"{case}: {name} differs from the reference binary's output"
+    eng = Engine(o.to_params())
+    for lo in range(0, len(r1), 450):
+        eng.process_se_text(flat(r1, lo, min(len(r1), lo + 450)), writers, lo)
+    assert np.array_equal(eng.finalize(), flat_pipe)
+    eng.close()
