@@ -566,15 +566,28 @@ def main():
             rc = eng.lib.fqk_process_se_fastq(eng.h, C.byref(rb), 0, None, 0, touts, C.byref(passed), C.byref(nr), C.byref(used))
             assert rc == 0 and nr.value == n1 and used.value == traw.numel(), eng.lib.fqk_last_error(eng.h)
         fastq_call()
+
+        def fastq_pipe(reps):                    # two blocks in flight: fqk_submit_se_fastq / fqk_wait_fastq
+            pend = None
+            for i in range(reps + 1):
+                tk = None
+                if i < reps:
+                    tk = C.c_uint64(0)
+                    rc = eng.lib.fqk_submit_se_fastq(eng.h, C.byref(rb), C.byref(tk))
+                    assert rc == 0, eng.lib.fqk_last_error(eng.h)
+                if pend is not None:
+                    rc = eng.lib.fqk_wait_fastq(eng.h, pend.value, 0, None, 0, slots[i & 1], C.byref(passed), C.byref(nr), C.byref(used))
+                    assert rc == 0 and nr.value == n1 and used.value == traw.numel(), eng.lib.fqk_last_error(eng.h)
+                pend = tk
+        fastq_pipe(2)
         eng.reset(); ctx.barrier()
         t0 = time.perf_counter()
-        for _ in range(reps):
-            fastq_call()
+        fastq_pipe(reps)
         eng.finalize(); ctx.barrier()
         dtf = ctx.max_over_ranks(time.perf_counter() - t0)
         e2e_fastq = {"value": world * reps * n1 * L1 / dtf / 1e9, "unit": "Gbases/s", "calls": reps,
                      "h2d_bytes_per_call": int(traw.numel()), "d2h_bytes_per_call": int(touts[abi.CH_OUT1].len),
-                     "note": "fqk_process_se_fastq: decompressed FASTQ text in, trimmed FASTQ text out; newline scan, packing, hot path "
+                     "note": "fqk_submit_se_fastq / fqk_wait_fastq, two blocks in flight: decompressed FASTQ text in, trimmed FASTQ text out; newline scan, packing, hot path "
                              "and record assembly on the GPU (what FqReader, the worker body and Read::toString do in the reference)"}
         del pseq, pqual, areads, seq, qual, off, pnames, pstr, tout, tout2, traw, tv
     del hbs, hout, batches

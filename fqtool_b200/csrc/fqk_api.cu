@@ -80,6 +80,7 @@ struct fqk_ctx {
                                               // kernels) must not sit in front of the text download of pack k
     uint64_t* ptoth = nullptr;                // pinned: [2][16] totals + counters of a slot
     struct TextSlot { uint32_t n = 0, writers = 0; fq_text_out* outs = nullptr; bool open = false; } tslot[2];
+    struct RawSlot { fq_raw_block blk; bool open = false; } rslot[2];      // fqk_submit_se_fastq / fqk_wait_fastq
     DevBuf poff[2], pscr[2], ptot[2];         // pipelined ASCII ingest (fqk_submit_se_ascii): offsets, scan scratch, totals per slot
     bool raw_mode = false;                    // the staged mates come from raw blocks (TextMate then points into traw)
     std::vector<uint32_t> hnoff[2], hsoff[2];
@@ -630,8 +631,8 @@ static TextMate text_mate(fqk_ctx* c, int m){
     return t;
 }
 // records on the device -> per-channel text blocks in the caller's buffers
-static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq_text_out* outs, uint64_t* read_passed){
-    const TextMate m1 = text_mate(c, 0), m2 = paired ? text_mate(c, 1) : m1;
+static int text_finish(fqk_ctx* c, bool paired, uint32_t n, uint32_t writers, fq_text_out* outs, uint64_t* read_passed, int slot = 0){
+    const TextMate m1 = text_mate(c, slot), m2 = paired ? text_mate(c, 1) : m1;      // slot: staging set of a single-end pack
     const fq_read_result* r1 = (const fq_read_result*)c->res1.p;
     const fq_read_result* r2 = paired ? (const fq_read_result*)c->res2.p : nullptr;
     const fq_pair_result* rp = paired ? (const fq_pair_result*)c->resp.p : nullptr;
@@ -719,16 +720,21 @@ extern "C" int fqk_process_pe_text(fqk_ctx* c, const fq_text_batch* r1, const fq
 
 // ---------------------------------------------------------------- raw FASTQ blocks
 // step 1: the block to the device, newlines counted and scanned; *lines = complete lines in the block
-static int fastq_lines(fqk_ctx* c, int m, const fq_raw_block* b, uint32_t* lines){
+// the asynchronous half: upload, newline counts, their prefix sum (tot[0] = newlines of the block)
+static int fastq_upload(fqk_ctx* c, int m, const fq_raw_block* b, cudaStream_t st, DevBuf& scratch, DevBuf& tot){
     if(b->bytes > 0xFFFFFFF0ull) return fail(c, FQK_E_LIMIT, "raw FASTQ block of 4 GiB or more: use smaller blocks");
     const uint32_t nc = (uint32_t)((b->bytes + NL_CHUNK - 1) / NL_CHUNK);
-    if(c->traw[m].ensure(b->bytes + 64) || c->tnlc[m].ensure((size_t)nc * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(nc) * 8) || c->ttot.ensure(256))
+    if(c->traw[m].ensure(b->bytes + 64) || c->tnlc[m].ensure((size_t)nc * 4 + 16) || scratch.ensure(text_scan_scratch_u64(nc) * 8) || tot.ensure(256))
         return fail(c, FQK_E_NOMEM, "device staging allocation failed");
-    if(b->bytes) CU(cudaMemcpyAsync(c->traw[m].p, b->text, b->bytes, cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemsetAsync((char*)c->traw[m].p + b->bytes, 0, 32, c->stream));          // the pack kernel reads whole words
-    fastq_launch_count(c->stream, (const char*)c->traw[m].p, b->bytes, (uint32_t*)c->tnlc[m].p);
-    text_launch_scan(c->stream, nc, (uint32_t*)c->tnlc[m].p, (uint64_t*)c->ttot.p, (uint64_t*)c->tscratch.p, 1);
+    if(b->bytes) CU(cudaMemcpyAsync(c->traw[m].p, b->text, b->bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync((char*)c->traw[m].p + b->bytes, 0, 32, st));                 // the pack kernel reads whole words
+    fastq_launch_count(st, (const char*)c->traw[m].p, b->bytes, (uint32_t*)c->tnlc[m].p);
+    text_launch_scan(st, nc, (uint32_t*)c->tnlc[m].p, (uint64_t*)tot.p, (uint64_t*)scratch.p, 1);
     c->launches += 4;
+    return 0;
+}
+static int fastq_lines(fqk_ctx* c, int m, const fq_raw_block* b, uint32_t* lines){
+    int rc = fastq_upload(c, m, b, c->stream, c->tscratch, c->ttot); if(rc) return rc;
     uint64_t nl = 0;
     CU(cudaMemcpyAsync(&nl, c->ttot.p, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -742,7 +748,8 @@ static int fastq_stage(fqk_ctx* c, int m, const fq_raw_block* b, uint32_t lines,
     if(n == 0){ s.dev = DevBatch(); s.dev.n = 0; return 0; }
     if(c->tnl[m].ensure((size_t)lines * 4 + 16) || c->asrc[m].ensure((size_t)n * 4 + 16) || c->aqsrc[m].ensure((size_t)n * 4 + 16) ||
        s.len.ensure((size_t)n * 2 + 16) || s.off.ensure((size_t)n * 4 + 16) || c->tnoff[m].ensure((size_t)n * 4 + 16) || c->tnlen[m].ensure((size_t)n * 4 + 16) ||
-       c->tsoff[m].ensure((size_t)n * 4 + 16) || c->tslen[m].ensure((size_t)n * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(n) * 8))
+       c->tsoff[m].ensure((size_t)n * 4 + 16) || c->tslen[m].ensure((size_t)n * 4 + 16) || c->tscratch.ensure(text_scan_scratch_u64(n) * 8) ||
+       c->ttot.ensure(256))
         return fail(c, FQK_E_NOMEM, "device staging allocation failed");
     const char* raw = (const char*)c->traw[m].p;
     uint32_t* misc = (uint32_t*)((uint64_t*)c->ttot.p + 8);                          // [0] longest read
@@ -1019,6 +1026,60 @@ extern "C" int fqk_wait_text(fqk_ctx* c, uint64_t ticket, uint64_t* read_passed)
     CU(cudaEventSynchronize(c->evD2H[s]));
     if(rc) return rc;
     return c->sticky ? fail(c, c->sticky, c->sticky_msg) : 0;
+}
+
+
+// Pipelined form of fqk_process_se_fastq.  submit: the block goes up and its newlines are counted (asynchronous, on the
+// upload stream); wait: everything that needs the number of records on the host (index, packing, hot path, assembly,
+// download).  With two blocks in flight (submit k+1, then wait k) the upload of block k+1 overlaps the kernels and the
+// download of block k.
+extern "C" int fqk_submit_se_fastq(fqk_ctx* c, const fq_raw_block* in, uint64_t* ticket){
+    if(!c || !in || (!in->text && in->bytes) || !ticket) return FQK_E_INVALID;
+    if(c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for paired-end data");
+    CU(cudaSetDevice(c->device));
+    int rc = pipe_init(c); if(rc) return rc;
+    if(!c->ptoth){
+        CU(cudaHostAlloc((void**)&c->ptoth, 2 * 16 * sizeof(uint64_t), cudaHostAllocDefault));
+        for(int i = 0; i < 2; ++i){
+            CU(cudaEventCreateWithFlags(&c->evTot[i], cudaEventDisableTiming));
+            CU(cudaStreamCreateWithFlags(&c->tdl[i], cudaStreamNonBlocking));
+        }
+    }
+    const uint64_t t = c->submitted;
+    const int s = (int)(t & 1);
+    if(c->rslot[s].open) return fail(c, FQK_E_INVALID, "fqk_wait_fastq of the block two submissions back is missing");
+    rc = fastq_upload(c, s, in, c->h2d, c->pscr[s], c->ptot[s]); if(rc) return rc;
+    CU(cudaMemcpyAsync(c->ptoth + 16 * s, c->ptot[s].p, 8, cudaMemcpyDeviceToHost, c->h2d));
+    CU(cudaEventRecord(c->evH2D[s], c->h2d));
+    c->rslot[s].blk = *in; c->rslot[s].open = true;
+    *ticket = t; c->submitted = t + 1;
+    return 0;
+}
+
+extern "C" int fqk_wait_fastq(fqk_ctx* c, uint64_t ticket, uint32_t writers, fq_read_result* out, uint32_t out_cap, fq_text_out* outs,
+                              uint64_t* read_passed, uint32_t* n_reads, uint64_t* consumed){
+    if(!c || ticket >= c->submitted || !outs || !n_reads || !consumed) return FQK_E_INVALID;
+    const int s = (int)(ticket & 1);
+    if(!c->rslot[s].open || ticket + 2 < c->submitted) return fail(c, FQK_E_INVALID, "no FASTQ block with this ticket is in flight");
+    CU(cudaSetDevice(c->device));
+    c->rslot[s].open = false;
+    for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ outs[ch].len = 0; outs[ch].records = 0; }
+    if(read_passed) *read_passed = 0;
+    *n_reads = 0; *consumed = 0;
+    CU(cudaEventSynchronize(c->evH2D[s]));                              // the block is on the device, its newlines are counted
+    CU(cudaStreamWaitEvent(c->stream, c->evH2D[s], 0));
+    const uint32_t lines = (uint32_t)c->ptoth[16 * s];
+    const uint32_t n = lines / 4;
+    if(n == 0) return 0;
+    if(out && out_cap < n) return fail(c, FQK_E_LIMIT, "record array smaller than the number of reads in the block");
+    c->raw_mode = true;
+    int rc = fastq_stage(c, s, &c->rslot[s].blk, lines, n, consumed); if(rc) return rc;
+    if(c->res1.ensure((size_t)n * sizeof(fq_read_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    rc = launch_se(c, c->st[s].dev, (fq_read_result*)c->res1.p); if(rc) return rc;
+    if(out) CU(cudaMemcpyAsync(out, c->res1.p, (size_t)n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->stream));
+    rc = text_finish(c, false, n, writers, outs, read_passed, s); if(rc) return rc;
+    *n_reads = n;
+    return check_err_flag(c);
 }
 
 // Pipelined form of fqk_process_se: the upload of pack k+1 overlaps the kernels and the download of pack k

@@ -172,6 +172,22 @@ class Engine:
                                                   C.byref(n), C.byref(u1), C.byref(u2)), "fqk_process_pe_fastq")
         return [bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], n.value, (u1.value, u2.value), int(passed.value)
 
+    def submit_se_fastq(self, text, first_index=0):
+        """Pipelined fqk_process_se_fastq, first half (upload + newline count); returns a handle for wait_fastq."""
+        t = np.frombuffer(bytes(text), dtype=np.uint8) if not isinstance(text, np.ndarray) else text
+        b = abi.FqRawBlock(); b.text = abi.ptr(t) if len(t) else None; b.bytes = len(t); b.first_index = first_index
+        tk = C.c_uint64(0)
+        self._check(self.lib.fqk_submit_se_fastq(self.h, C.byref(b), C.byref(tk)), "fqk_submit_se_fastq")
+        return {"ticket": tk.value, "keep": (t, b)}
+
+    def wait_fastq(self, handle, writers=0):
+        nbytes = len(handle["keep"][0])
+        bufs, outs = self._fastq_outs(nbytes + 64 * (nbytes // 8 + 1))
+        passed, n, used = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0)
+        self._check(self.lib.fqk_wait_fastq(self.h, handle["ticket"], writers, None, 0, outs, C.byref(passed), C.byref(n), C.byref(used)),
+                    "fqk_wait_fastq")
+        return [bytes(bufs[ch][:outs[ch].len]) for ch in range(abi.CH_COUNT)], n.value, used.value, int(passed.value)
+
     def submit_se(self, batch, out):
         """Pipelined fqk_process_se: returns a ticket; `batch` and `out` must stay alive until wait(ticket)."""
         b = batch.c_struct()

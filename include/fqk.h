@@ -338,6 +338,15 @@ int  fqk_process_pe_fastq(fqk_ctx* ctx, const fq_raw_block* in1, const fq_raw_bl
                           fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed, uint32_t* n_pairs,
                           uint64_t* consumed1, uint64_t* consumed2);
 
+/* Pipelined form of fqk_process_se_fastq: fqk_submit_se_fastq uploads the block and counts its newlines (asynchronous);
+ * fqk_wait_fastq does the rest and returns what fqk_process_se_fastq returns.  With two blocks in flight (submit k+1,
+ * then wait k) the upload of block k+1 overlaps the kernels and the download of block k.  The block's text must stay
+ * valid until its wait returns; blocks are independent (the caller cuts them at record boundaries, e.g. with the
+ * *consumed of a previous call on a probe, or by scanning back to a line that starts with '@' after a quality line). */
+int  fqk_submit_se_fastq(fqk_ctx* ctx, const fq_raw_block* in, uint64_t* ticket);
+int  fqk_wait_fastq(fqk_ctx* ctx, uint64_t ticket, uint32_t writers, fq_read_result* out, uint32_t out_cap,
+                    fq_text_out outs[FQK_CH_COUNT], uint64_t* read_passed, uint32_t* n_reads, uint64_t* consumed);
+
 /*
  * Pipelined form of fqk_process_se for hosts that keep two packs in flight: fqk_submit_se enqueues
  * upload, kernels and download of a pack and returns a ticket; fqk_wait blocks until that pack's

@@ -177,3 +177,36 @@ def test_pipelined_text_matches_reference_files(case):
         eng.process_se_text(flat(r1, lo, min(len(r1), lo + 450)), writers, lo)
     assert np.array_equal(eng.finalize(), flat_pipe)
     eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["cfg2_r1", "se_failed"])
+def test_pipelined_fastq_blocks_match_reference_files(case):
+    """fqk_submit_se_fastq / fqk_wait_fastq, two blocks in flight; blocks cut at record boundaries by the caller."""
+    from fqtool_b200.engine import Engine
+    paired, flags = make_e2e.CASES[case]
+    o = from_cli(flags.split()); o.maxCycles = 320
+    text = gzip.open(FQ[0], "rb").read()
+    lines = text.split(b"\n")[:-1]                                      # the text ends with a newline
+    blocks_in = [b"\n".join(lines[i:i + 4 * 300]) + b"\n" for i in range(0, len(lines), 4 * 300)]
+    assert b"".join(blocks_in) == text
+    outs = make_e2e.outputs(case, paired, "")
+    writers = abi.W_FAILED if "--failed_out" in outs else 0
+    eng = Engine(o.to_params())
+    acc = [b""] * abi.CH_COUNT
+    pending, first, total = None, 0, 0
+    for blk in blocks_in + [None]:
+        h = eng.submit_se_fastq(blk, first) if blk is not None else None
+        if blk is not None:
+            first += 300
+        if pending is not None:
+            blocks, n, used, passed = eng.wait_fastq(pending, writers)
+            assert used == len(pending["keep"][0]) and n > 0
+            total += n
+            for ch in range(abi.CH_COUNT):
+                acc[ch] += blocks[ch]
+        pending = h
+    eng.close()
+    assert total == 2000
+    for name, want in EXPECTED[case]["files"].items():
+        assert hashlib.md5(acc[FILES[name]]).hexdigest() == want, f"{case}: {name} differs from the reference binary's output"
