@@ -760,6 +760,7 @@ void fused_configure(const cudaDeviceProp& prop){
     cudaFuncSetAttribute(k_se_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_se_v3<false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
+    cudaFuncSetAttribute(k_se_v3<true, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<true>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
     cudaFuncSetAttribute(k_pe_v4<V4Spec<false>, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem_optin);
@@ -794,7 +795,8 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         // generic option sets (adapter by sequence, polyG / polyX, ...): the trim role is the long one (one lane per read,
         // dependent scalar chains), so it gets 11 working warps and the statistics 4 (FQK_V3_WIDE=0 keeps 7 + 8)
         static const bool wide_on = !(getenv("FQK_V3_WIDE") && atoi(getenv("FQK_V3_WIDE")) == 0);
-        const bool wide = wide_on && !v3_fast_options(D.P) && v3_tile(W, 128) > 0;
+        static const int wide_fast = getenv("FQK_V3_WIDE_FAST") ? atoi(getenv("FQK_V3_WIDE_FAST")) : 0;   // experiment: 4 + 11 warps for the fast option sets too
+        const bool wide = wide_on && (!v3_fast_options(D.P) || wide_fast) && v3_tile(W, 128) > 0;
         const int T = wide ? v3_tile(W, 128) : v3_tile(W);
         int rpb = (int)((B.n + sms - 1) / sms);
         rpb = std::min(rpb, 1 << 24);                          // 32-bit per-block sums of quality characters
@@ -802,7 +804,8 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const size_t sm = v3_layout(W, T).total + 128;
         static const int dbg = getenv("FQK_V3_DEBUG") ? atoi(getenv("FQK_V3_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
-        if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
+        if(v3_fast_options(D.P) && wide) k_se_v3<true, 128><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
+        else if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         else if(wide) k_se_v3<false, 128><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         else k_se_v3<false><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
