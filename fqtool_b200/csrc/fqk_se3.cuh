@@ -437,7 +437,7 @@ k_se_v3(const __grid_constant__ DevParams D, DevBatch B, fq_read_result* __restr
                         pass = !(rec.flags & FQK_F_DROPPED) && rec.result == FQK_PASS_FILTER;
                     }
                     if(FAST){
-                        coop = coop && pass;
+                        coop = coop && pass && !(dbg & 16);                 // (FQK_V3_DEBUG 16: every cut-off tail through the exception list)
                         const uint32_t sbase = S32 + L.o_b + bshift;
                         const uint32_t row = 4u * (uint32_t)C, krow = (uint32_t)NSETS * row;
                         for(unsigned mc = __ballot_sync(0xffffffffu, coop); mc; mc &= mc - 1){
