@@ -5,6 +5,13 @@
  * cites the reference file:line (relative to /root/reference/) it follows.
  * Reads are handled as views (pointer + length) into the caller's ASCII
  * buffers: all of the reference's trims are prefix/suffix cuts.
+ *
+ * PARITY PINNED: this port is checked against the reference itself, built here from its own sources
+ * (oracle/_ref/libfqref.so, oracle/_ref/fqtool_ref): tests/test_oracle_vs_ref.py (records, accumulators, duplication
+ * tables on 22 option sets), tests/test_known_answers.py (whole-binary known answers), tests/test_golden.py (fixtures
+ * generated from the reference build), tests/test_prepass.py (the pre-pass loops with the reference's Evaluator::seq2int
+ * and getAdapterWithSeed).  Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline leg may use it; the product
+ * (fqtool_b200/, include/, integration/) never does.
  */
 #include "fq_oracle.h"
 #include <stdlib.h>
