@@ -185,8 +185,28 @@ __global__ void k_scan_apply(uint32_t n, uint32_t* __restrict__ sizes, const uin
 }
 
 // ------------------------------------------------------------------ copy
-__device__ __forceinline__ void put(char* dst, uint32_t& o, const char* src, uint32_t n, int lane){     // warp copy, advances o
+__device__ __forceinline__ void put_bytes(char* dst, uint32_t& o, const char* src, uint32_t n, int lane){     // warp copy, advances o
     for(uint32_t k = lane; k < n; k += 32) dst[o + k] = src[k];
+    o += n;
+}
+// The same for the long pieces (names, bases, qualities) with aligned 32-bit stores: bytes up to the destination's next
+// word boundary, then whole words assembled from two aligned source words by a funnel shift, then the last bytes.  The
+// source buffers carry at least 16 spare bytes, so the word that straddles the end of a piece can be read.
+__device__ __forceinline__ void put(char* dst, uint32_t& o, const char* src, uint32_t n, int lane){
+    char* d = dst + o;
+    const uint32_t head = min((4u - (uint32_t)(reinterpret_cast<uintptr_t>(d) & 3u)) & 3u, n);
+    if((uint32_t)lane < head) d[lane] = src[lane];
+    const uint32_t nwords = (n - head) >> 2;
+    const char* s = src + head;
+    const uint32_t sa = (uint32_t)(reinterpret_cast<uintptr_t>(s) & 3u);
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(s - sa);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(d + head);
+    for(uint32_t k = lane; k < nwords; k += 32){
+        const uint32_t w0 = sw[k], w1 = sa ? sw[k + 1] : 0u;
+        dw[k] = __funnelshift_r(w0, w1, 8u * sa);
+    }
+    const uint32_t done = head + 4u * nwords;
+    if((uint32_t)lane < n - done) d[done + lane] = src[done + lane];
     o += n;
 }
 __device__ __forceinline__ void put_ch(char* dst, uint32_t& o, char c, int lane){ if(lane == 0) dst[o] = c; o += 1; }
@@ -209,7 +229,7 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
         const uint32_t len1 = pr.merge_len1, len2 = pr.merge_len2, ol = pr.ov2_len;
         const uint32_t sp = first_space(name, nl);
         if(sp < nl) put(dst, o, name, sp - 1, lane);
-        put(dst, o, "_merged_", 8, lane); put_dec(dst, o, len1, lane); put_ch(dst, o, '_', lane); put_dec(dst, o, len2, lane);
+        put_bytes(dst, o, "_merged_", 8, lane); put_dec(dst, o, len1, lane); put_ch(dst, o, '_', lane); put_dec(dst, o, len2, lane);
         if(sp < nl) put(dst, o, name + sp, nl - sp, lane);
         put_ch(dst, o, '\n', lane);
         uint32_t s1, l1, s2, l2; view_of(x1, m1.len[i], s1, l1); view_of(x2, m2.len[i], s2, l2);
@@ -230,7 +250,7 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
     const fq_read_result& x = p.kind ? x2 : x1;
     uint32_t st, ln; view_of(x, m.len[i], st, ln);
     put(dst, o, m.names + m.name_off[i], m.nlen(i), lane);
-    if(p.tag >= 0){ put_ch(dst, o, ' ', lane); put(dst, o, c_tags[p.tag], tag_len(p.tag), lane); }
+    if(p.tag >= 0){ put_ch(dst, o, ' ', lane); put_bytes(dst, o, c_tags[p.tag], tag_len(p.tag), lane); }
     put_ch(dst, o, '\n', lane);
     put(dst, o, m.seq + m.src[i] + st, ln, lane); put_ch(dst, o, '\n', lane);
     put(dst, o, m.strands + m.strand_off[i], m.slen(i), lane); put_ch(dst, o, '\n', lane);
