@@ -8,7 +8,7 @@
 // contiguous block of FASTQ text in input order:
 //   k_text_sizes   a thread per read (pair): the routing ladder -> bytes per channel
 //   k_scan_*       exclusive prefix sums per channel (three small kernels, 2048 items per block)
-//   k_text_copy    a warp per read (pair): the same ladder -> the pieces, copied with lane-strided byte moves
+//   k_text_copy    a warp per read (pair): the same ladder -> the pieces, copied with aligned word stores (funnel-shifted source words)
 // so that the host's writer threads only hand blocks to gzwrite; no per-read string is built on the host.
 #include "fqk_text.h"
 
