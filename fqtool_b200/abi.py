@@ -123,6 +123,7 @@ EXPORTS = [
     "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits", "fqk_process_se_text", "fqk_process_pe_text",
     "fqk_process_se_fastq", "fqk_process_pe_fastq", "fqk_submit_se_ascii",
     "fqk_submit_se_text", "fqk_wait_text", "fqk_submit_se_fastq", "fqk_wait_fastq",
+    "fqk_prepass_kmer_counts_static",
 ]
 
 _lib = None
@@ -181,6 +182,8 @@ def load():
     lib.fqk_submit_se_fastq.argtypes = [vp, P(FqRawBlock), P(u64)]; lib.fqk_submit_se_fastq.restype = i32
     lib.fqk_wait_fastq.argtypes = [vp, u64, u32, vp, u32, P(FqTextOut), P(u64), P(u32), P(u64)]; lib.fqk_wait_fastq.restype = i32
     lib.fqk_prepass_kmer_counts.argtypes = [i32, vp, i32, i32, i32, vp]; lib.fqk_prepass_kmer_counts.restype = i32
+    lib.fqk_prepass_kmer_counts_static.argtypes = [i32, u32, vp, vp, i32, i32, i32, vp, vp]
+    lib.fqk_prepass_kmer_counts_static.restype = i32
     lib.fqk_prepass_seed_hits.argtypes = [i32, vp, i32, i32, i32, u32, vp, vp, u32, vp]; lib.fqk_prepass_seed_hits.restype = i32
     lib.fqk_host_free.argtypes = [vp]; lib.fqk_host_free.restype = None
     _lib = lib

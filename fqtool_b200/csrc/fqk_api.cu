@@ -111,6 +111,9 @@ struct fqk_ctx {
 
 static thread_local std::string g_create_error;
 
+// error text for the context-free entry points of other translation units (read back with fqk_last_error(NULL))
+void fqk_set_thread_error(const char* msg){ g_create_error = msg ? msg : ""; }
+
 static int fail(fqk_ctx* c, int code, const std::string& msg){
     if(c) c->error = msg; else g_create_error = msg;
     return code;

@@ -9,8 +9,12 @@
 // NucleotideTree walk over the few reads that carry the seed (string work on a handful of reads).
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
+#include <string>
 #include <cuda_runtime.h>
 #include "../../include/fqk.h"
+
+void fqk_set_thread_error(const char* msg);                               // fqk_api.cu: text behind fqk_last_error(NULL)
 
 namespace {
 
@@ -129,5 +133,97 @@ extern "C" int fqk_prepass_seed_hits(int device, const fq_ascii_batch* reads, in
         if(cudaMemcpy(read_idx, dr.p, (size_t)m * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return FQK_E_CUDA;
         if(cudaMemcpy(pos, dp.p, (size_t)m * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return FQK_E_CUDA;
     }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// fqk_prepass_kmer_counts_static: the k-mer count of the pre-pass for callers that must not allocate.
+//
+// fqk_prepass_kmer_counts above takes its 32-bit histogram (the table the lanes add into) from cudaMalloc and gives it
+// back with cudaFree on every call.  Two kinds of caller cannot afford that:
+//   * a thread that runs the pre-pass while other threads of the same process have packs in flight on this GPU through
+//     fqk_submit_* : cudaMalloc and cudaFree wait for and block every stream of the device, so each call would stall the
+//     upload / kernel / download overlap of all the workers;
+//   * a process that has handed the whole of HBM to its own pool (or to long-lived fqk contexts) and has nothing left
+//     for the driver to hand out, so cudaMalloc fails there.
+// For them the histogram lives in the library image itself: a file-scope device array that every GPU which loads
+// libfqk.so holds from load until exit (4 MiB per GPU, whether or not this entry point is ever called).  4 MiB is
+// 4^10 32-bit bins, i.e. key lengths up to FQK_PREPASS_STATIC_MAX_KEYLEN = 10, the length the reference's
+// Evaluator uses; longer keys are refused (FQK_E_LIMIT), use fqk_prepass_kmer_counts for them.
+// Inputs and the output are the caller's own DEVICE buffers, so nothing is allocated here: no cudaMalloc / cudaFree,
+// no host staging buffer, no library routine that allocates.
+//
+// The array's name is only usable as an address inside device code; on the host it is a stand-in symbol, and a kernel
+// handed `g_prepass_static_hist` from host code would fault (or scribble on host memory where the GPU can reach it).
+// So the first call on each device asks the runtime for the real address, with that device current
+// (cudaGetSymbolAddress), and remembers it per device.  That first call does this one-time set-up; make it before any
+// stream capture begins on that device.
+//
+// All calls on one GPU share the one array and it keeps whatever the previous call left: each call clears the bins it
+// is going to use (stream-ordered, before its kernel).  Two calls that overlap on the GPU (different streams, or two
+// threads on the same device) race on the bins and both results are garbage: serialise them (same stream, or a
+// synchronise between them).
+namespace {
+
+constexpr int      kStaticMaxKeylen = FQK_PREPASS_STATIC_MAX_KEYLEN;
+constexpr uint32_t kStaticBins      = 1u << (2 * kStaticMaxKeylen);       // 4^10 = 1 Mi bins = 4 MiB
+constexpr int      kStaticMaxDevices = 64;
+
+static __device__ __align__(256) uint32_t g_prepass_static_hist[kStaticBins];
+
+uint32_t*  g_static_hist_addr[kStaticMaxDevices] = {nullptr};             // device address of the array, per device
+std::mutex g_static_hist_mtx;
+
+// 32-bit bins of the scratch histogram -> the caller's 64-bit counts (the layout fqk_prepass_kmer_counts returns)
+__global__ void k_prepass_widen(const uint32_t* __restrict__ hist, uint64_t* __restrict__ counts, uint32_t bins){
+    for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < bins; i += gridDim.x * blockDim.x) counts[i] = hist[i];
+}
+
+int static_fail(int code, const std::string& msg){ fqk_set_thread_error(msg.c_str()); return code; }
+
+// address of the scratch array on `device` (which must be the current device); looked up once per device
+int static_hist_address(int device, uint32_t** out){
+    std::lock_guard<std::mutex> lk(g_static_hist_mtx);
+    if(!g_static_hist_addr[device]){
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_prepass_static_hist);
+        if(e != cudaSuccess || !p)
+            return static_fail(FQK_E_CUDA, std::string("fqk_prepass_kmer_counts_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_static_hist_addr[device] = (uint32_t*)p;
+    }
+    *out = g_static_hist_addr[device];
+    return 0;
+}
+
+} // namespace
+
+extern "C" int fqk_prepass_kmer_counts_static(int device, uint32_t n_reads, const char* seq_dev, const uint64_t* off_dev, int keylen,
+                                              int first_pos, int shift_tail, uint64_t* counts_dev, void* stream){
+    if(keylen > kStaticMaxKeylen)
+        return static_fail(FQK_E_LIMIT, "fqk_prepass_kmer_counts_static: keylen " + std::to_string(keylen) + " needs 4^keylen bins, the built-in scratch "
+                           "array holds 4^" + std::to_string(kStaticMaxKeylen) + " (keylen <= " + std::to_string(kStaticMaxKeylen) +
+                           "); use fqk_prepass_kmer_counts for longer keys");
+    if(keylen < 1 || first_pos < 0 || shift_tail < 0 || !counts_dev || !off_dev || (n_reads && !seq_dev))
+        return static_fail(FQK_E_INVALID, "fqk_prepass_kmer_counts_static: bad argument (keylen 1..10, first_pos/shift_tail >= 0, device pointers set)");
+    int ndev = 0;
+    if(cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return static_fail(FQK_E_CUDA, "fqk_prepass_kmer_counts_static: no such CUDA device (there is no CPU fallback)");
+    if(device >= kStaticMaxDevices)
+        return static_fail(FQK_E_LIMIT, "fqk_prepass_kmer_counts_static: device ordinal beyond " + std::to_string(kStaticMaxDevices - 1));
+    cudaError_t e = cudaSetDevice(device);
+    if(e != cudaSuccess) return static_fail(FQK_E_CUDA, std::string("fqk_prepass_kmer_counts_static: cudaSetDevice: ") + cudaGetErrorString(e));
+    uint32_t* hist = nullptr;
+    int rc = static_hist_address(device, &hist); if(rc) return rc;
+    const cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t bins = 1u << (2 * keylen);
+    // the array still holds the previous call's bins: clear the ones this call counts into
+    e = cudaMemsetAsync(hist, 0, (size_t)bins * 4, st);
+    if(e != cudaSuccess) return static_fail(FQK_E_CUDA, std::string("fqk_prepass_kmer_counts_static: cudaMemsetAsync: ") + cudaGetErrorString(e));
+    if(n_reads)
+        k_prepass_kmers<<<grid_for(n_reads), 256, 0, st>>>(n_reads, seq_dev, off_dev, keylen, first_pos, shift_tail, -1, hist, nullptr, nullptr, 0,
+                                                          nullptr);
+    k_prepass_widen<<<(int)((bins + 255) / 256 < 148 * 4 ? (bins + 255) / 256 : 148 * 4), 256, 0, st>>>(hist, counts_dev, bins);
+    e = cudaGetLastError();
+    if(e != cudaSuccess) return static_fail(FQK_E_CUDA, std::string("fqk_prepass_kmer_counts_static: launch: ") + cudaGetErrorString(e));
     return 0;
 }

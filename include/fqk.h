@@ -446,6 +446,33 @@ int  fqk_prepass_kmer_counts(int device, const fq_ascii_batch* reads, int keylen
 int  fqk_prepass_seed_hits(int device, const fq_ascii_batch* reads, int keylen, int first_pos, int shift_tail, uint32_t seed,
                            uint32_t* read_idx, uint32_t* pos, uint32_t cap, uint32_t* n);
 
+/*
+ * fqk_prepass_kmer_counts_static -- no counterpart in the reference (the reference counts on the CPU and has nothing to
+ * allocate on a GPU); it exists for callers of THIS library that must not allocate device memory.
+ *
+ * Same counts as fqk_prepass_kmer_counts, but the call allocates nothing: no cudaMalloc / cudaFree and no staging
+ * buffer.  fqk_prepass_kmer_counts takes its working histogram from cudaMalloc on every call; that is a problem for
+ *   - a thread that runs the pre-pass while other threads of the process have packs in flight on the same GPU
+ *     (fqk_submit_*): cudaMalloc / cudaFree hold up every stream of the device, so each call would stall all workers;
+ *   - a process whose HBM is already fully handed out (its own pool, long-lived contexts), where cudaMalloc fails.
+ * Here the histogram is an array built into libfqk.so: 4 MiB of device memory on EVERY GPU that loads the library,
+ * held until the process exits.  It has room for 4^10 bins, so keylen is limited to FQK_PREPASS_STATIC_MAX_KEYLEN
+ * (the reference's Evaluator uses 10); a longer key returns FQK_E_LIMIT and fqk_last_error(NULL) says why.
+ *
+ * Everything the caller passes is DEVICE memory it owns: seq_dev = the reads' characters, off_dev[n_reads + 1] = start
+ * of each read in seq_dev (off_dev[n_reads] = end of the last), counts_dev[4^keylen] = output (overwritten).
+ * `stream` is a cudaStream_t (NULL = the default stream); the work is queued on it and the call returns without
+ * waiting: counts_dev is complete once that stream has been synchronised.  `device` becomes the current device.
+ * The first call on each device also looks up the array's device address (one-time set-up): make that first call
+ * before any stream capture on that device.
+ * All calls on a GPU share the one array and it keeps the previous call's contents; every call clears the bins it uses
+ * first.  Calls that overlap on the GPU (two streams, two threads) race on it and both get wrong counts: keep them on
+ * one stream or synchronise between them.
+ */
+#define FQK_PREPASS_STATIC_MAX_KEYLEN 10
+int  fqk_prepass_kmer_counts_static(int device, uint32_t n_reads, const char* seq_dev, const uint64_t* off_dev, int keylen,
+                                    int first_pos, int shift_tail, uint64_t* counts_dev, void* stream);
+
 /* pinned host memory helpers for callers without a CUDA toolchain */
 void* fqk_host_alloc(size_t bytes);
 void  fqk_host_free(void* p);
