@@ -74,7 +74,8 @@ __device__ __forceinline__ uint32_t merged_name_len(const char* name, uint32_t n
     const uint32_t tagl = 8 + dec_digits(len1) + 1 + dec_digits(len2);
     const uint32_t sp = first_space(name, nl);
     if(sp >= nl) return tagl;
-    return (sp - 1) + tagl + (nl - sp);
+    // a name that BEGINS with a space: substr(0, pos - 1) is substr(0, npos), the whole name, so the name appears twice
+    return (sp ? sp - 1 : nl) + tagl + (nl - sp);
 }
 
 __device__ __forceinline__ uint32_t piece_bytes(const Piece& p, const TextMate& m1, const TextMate& m2, uint32_t i,
@@ -228,7 +229,7 @@ __device__ void write_piece(const Piece& p, char* dst, uint32_t o, const TextMat
         const char* strand = m1.strands + m1.strand_off[i]; const uint32_t sl = m1.slen(i);
         const uint32_t len1 = pr.merge_len1, len2 = pr.merge_len2, ol = pr.ov2_len;
         const uint32_t sp = first_space(name, nl);
-        if(sp < nl) put(dst, o, name, sp - 1, lane);
+        if(sp < nl) put(dst, o, name, sp ? sp - 1 : nl, lane);    // sp == 0: see merged_name_len
         put_bytes(dst, o, "_merged_", 8, lane); put_dec(dst, o, len1, lane); put_ch(dst, o, '_', lane); put_dec(dst, o, len2, lane);
         if(sp < nl) put(dst, o, name + sp, nl - sp, lane);
         put_ch(dst, o, '\n', lane);
@@ -336,10 +337,14 @@ __global__ void k_fastq_index(const char* __restrict__ text, const uint32_t* __r
         }
         const uint32_t l = e[1] - s[1];
         if(e[0] == s[0] || text[s[0]] != '@' || e[2] == s[2] || text[s[2]] != '+' || e[3] - s[3] != l) bad |= 8u;
+        const bool malformed = e[0] == s[0] || text[s[0]] != '@' || e[2] == s[2] || text[s[2]] != '+' || e[3] - s[3] != l;
         if(l > FQK_MAX_READ_LEN){ bad |= 1u; }
-        const uint32_t lc = min(l, (uint32_t)FQK_MAX_READ_LEN);
-        src_seq[r] = s[1]; src_qual[r] = s[3]; len[r] = (uint16_t)lc;
-        name_off[r] = s[0]; name_len[r] = e[0] - s[0]; strand_off[r] = s[2]; strand_len[r] = e[2] - s[2];
+        // a malformed record gets length 0 and no name / third line: the block is refused when the error word is read at
+        // the end, but the packer, the trim kernels and the text assembly still run over it first and must not follow a
+        // sequence length the quality line does not have (that would read past the uploaded block)
+        const uint32_t lc = malformed ? 0u : min(l, (uint32_t)FQK_MAX_READ_LEN);
+        src_seq[r] = s[1]; src_qual[r] = malformed ? s[1] : s[3]; len[r] = (uint16_t)lc;
+        name_off[r] = s[0]; name_len[r] = malformed ? 0u : e[0] - s[0]; strand_off[r] = s[2]; strand_len[r] = malformed ? 0u : e[2] - s[2];
         padlen[r] = (lc + FQK_PAD - 1u) / FQK_PAD * FQK_PAD;
         mx = max(mx, lc);
     }

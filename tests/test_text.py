@@ -210,3 +210,48 @@ def test_pipelined_fastq_blocks_match_reference_files(case):
     assert total == 2000
     for name, want in EXPECTED[case]["files"].items():
         assert hashlib.md5(acc[FILES[name]]).hexdigest() == want, f"{case}: {name} differs from the reference binary's output"
+
+
+@pytest.mark.gpu
+def test_raw_fastq_truncated_quality_line_is_refused_cleanly():
+    """A record whose quality line is shorter than its sequence (here: the last record of the block, so the sequence length
+    would lead the packer past the uploaded bytes) is refused like the reference's reader does (src/fqreader.cpp:183-190),
+    without a device fault: the same context and a new one keep working afterwards."""
+    from fqtool_b200.engine import Engine, FqkError
+    o = from_cli("-q --enable_cut_tail".split()); o.maxCycles = 160
+    text = gzip.open(FQ[0], "rb").read()
+    lines = text.split(b"\n")[:4 * 500]
+    good = b"\n".join(lines) + b"\n"
+    lines[-1] = lines[-1][:3]                                                    # 3 quality characters for 150 bases
+    bad = b"\n".join(lines) + b"\n"
+    eng = Engine(o.to_params())
+    want = eng.process_se_fastq(good)
+    with pytest.raises(FqkError):
+        eng.process_se_fastq(bad)
+    eng.close()
+    eng = Engine(o.to_params())
+    got = eng.process_se_fastq(good)
+    eng.close()
+    assert got[1] == want[1] == 500 and got[0][abi.CH_OUT1] == want[0][abi.CH_OUT1]
+
+
+@pytest.mark.gpu
+def test_merged_name_of_a_read_name_that_starts_with_a_space():
+    """OverlapAnalysis::merge (src/overlapanalysis.cpp:95-100) splices the tag at name.substr(0, pos - 1); with the first
+    space at position 0 that is substr(0, npos): the WHOLE name, then the tag, then the whole name again."""
+    import re
+    from fqtool_b200.engine import Engine
+    o = from_cli("-m --discard_unmerged -q -I r2".split()); o.maxCycles = 320
+    r1 = parse_fastq(FQ[0])[:600]; r2 = parse_fastq(FQ[1])[:600]
+    eng = Engine(o.to_params())
+    a, nrec_a, _, out_a = eng.process_pe_text(flat(r1, 0, 600), flat(r2, 0, 600), 0, 0)
+    s1 = [[b" " + r[0]] + r[1:] for r in r1]
+    b, nrec_b, _, out_b = eng.process_pe_text(flat(s1, 0, 600), flat(r2, 0, 600), 0, 0)
+    eng.close()
+    merged = [i for i in range(600) if out_a[2]["flags"][i] & 0x10]
+    la = a[abi.CH_MERGED].split(b"\n"); lb = b[abi.CH_MERGED].split(b"\n")
+    assert nrec_a[abi.CH_MERGED] == nrec_b[abi.CH_MERGED] == len(merged) > 50 and len(la) == len(lb) == 4 * len(merged) + 1
+    for j, i in enumerate(merged):
+        tag = re.search(rb"_merged_\d+_\d+", la[4 * j]).group(0)
+        assert lb[4 * j] == s1[i][0] + tag + s1[i][0]
+        assert lb[4 * j + 1:4 * j + 4] == la[4 * j + 1:4 * j + 4]
