@@ -144,7 +144,9 @@ inline void wantChannel(fq_text_out* outs, int ch, size_t cap){ outs[ch].data = 
 inline void dropChannels(fq_text_out* outs){ for(int ch = 0; ch < FQK_CH_COUNT; ++ch){ delete[] outs[ch].data; outs[ch].data = nullptr; } }
 
 struct Seam {
-    std::mutex mtx;                 // one GPU context per process; worker threads take turns (pack order = call order)
+    std::mutex mtx;                 // one GPU context per process; worker threads take turns.  With -w 1 packs arrive in input
+                                    // order; with -w > 1 in lock order, so firstIndex is NOT the read's position in the file then
+                                    // (only Duplicate's mean-GC-of-the-first-read depends on it)
     fqk_ctx* ctx = nullptr;
     fq_params P;
     fq_stats_layout L;
