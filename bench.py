@@ -52,7 +52,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default="cfg2")
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "generic"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "generic", "sample"])
+    ap.add_argument("--sample-out", default="", help="--impl sample: write the first --cpu-sample units of --config's stream here (.npz)")
+    ap.add_argument("--check-units", type=int, default=4_000_000,
+                    help="units of every timed stream whose records and accumulators are compared with the oracle (0 = skip)")
     ap.add_argument("--reads", type=int, default=0, help="reads (pairs) per GPU; 0 = the config's size capped by HBM")
     ap.add_argument("--cpu-sample", type=int, default=4_000_000, help="reads of the CPU-baseline sample")
     ap.add_argument("--e2e-steps", type=int, default=5)
@@ -106,7 +109,101 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------ CPU baseline
-def cpu_reference_run(cfg, sample_reads, steps, warmup, torch_dev=None):
+def device_sample(cfg, n, torch_dev):
+    """First n units of the device-generated stream of cfg as host reads (seq, qual, off) per mate."""
+    import torch
+    from fqtool_b200 import batch, workload
+    b1, b2 = workload.generate(cfg, n, 0, torch_dev, None)
+    torch.cuda.synchronize()
+    r1 = batch.unpack(b1.to_host()); r2 = batch.unpack(b2.to_host()) if b2 else None
+    return r1, r2
+
+
+def write_sample(a):
+    """--impl sample (a helper process of the reference arm): the sample comes from the same counter-based generator the B200
+    arm times, which lives in libfqk.so; it is produced HERE and handed over as a file so that the process that times the
+    reference never loads the library or touches the GPU."""
+    import numpy as np
+    import torch
+    r1, r2 = device_sample(a.config, a.cpu_sample, torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
+    arrs = {"s1": r1[0], "q1": r1[1], "o1": r1[2]}
+    if r2 is not None:
+        arrs.update({"s2": r2[0], "q2": r2[1], "o2": r2[2]})
+    np.savez(a.sample_out, **arrs)
+
+
+def oracle_flat_threaded(params, r1, r2, threads):
+    """Records and flat accumulators of the CPU oracle (the reference's own objects when oracle/_ref is built, else the
+    port) over the reads, split into `threads` contiguous chunks run side by side: every entry of the flat buffer is a sum
+    over reads, so the chunk results add up (the duplication table is not part of this check: it is order-dependent and
+    covered by the parity tests and merge_check)."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import pyoracle
+    kind = "reference" if pyoracle.have_reference() else "port"
+    n = len(r1[2]) - 1
+    cuts = [n * t // threads for t in range(threads + 1)]
+
+    def sub(r, lo, hi):
+        seq, qual, off = r
+        a, b = int(off[lo]), int(off[hi])
+        return seq[a:b], qual[a:b], (off[lo:hi + 1] - off[lo]).astype(np.uint64)
+
+    def work(t):
+        lo, hi = cuts[t], cuts[t + 1]
+        o = pyoracle.Oracle(params, kind)
+        rec = (o.process_se(sub(r1, lo, hi), lo),) if r2 is None else o.process_pe(sub(r1, lo, hi), sub(r2, lo, hi), lo)
+        flat = o.finalize()
+        o.close()
+        return rec, flat
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(work, range(threads)))
+    recs = tuple(np.concatenate([p[0][k] for p in parts]) for k in range(len(parts[0][0])))
+    flat = np.sum([p[1] for p in parts], axis=0, dtype=np.uint64)
+    return kind, recs, flat
+
+
+def oracle_check(ctx, cfg, units, reads=None):
+    """The first `units` units of cfg's timed stream through the product path (fqk_process_*_device on a fresh context) against
+    the CPU oracle: every field of every record and every entry of the flat accumulator buffer, bit for bit."""
+    import numpy as np
+    import torch
+    from fqtool_b200 import abi, batch, workload
+    params = workload.options_for(cfg).to_params()
+    eng = ctx.engine(params, single=True)
+    b1, b2 = workload.generate(cfg, units, 0, ctx.dev, eng.stream)
+    o1 = torch.zeros(units * 16, dtype=torch.uint8, device=ctx.dev)
+    if b2 is None:
+        eng.process_se_device(b1.c_struct(), o1.data_ptr())
+    else:
+        o2 = torch.zeros(units * 16, dtype=torch.uint8, device=ctx.dev); op = torch.zeros(units * 24, dtype=torch.uint8, device=ctx.dev)
+        eng.process_pe_device(b1.c_struct(), b2.c_struct(), o1.data_ptr(), o2.data_ptr(), op.data_ptr())
+    eng.sync()
+    flat = eng.finalize()
+    L = eng.layout
+    recs = [o1.cpu().numpy().view(abi.READ_RESULT_DTYPE)]
+    if b2 is not None:
+        recs += [o2.cpu().numpy().view(abi.READ_RESULT_DTYPE), op.cpu().numpy().view(abi.PAIR_RESULT_DTYPE)]
+    if reads is None:
+        reads = (batch.unpack(b1.to_host()), batch.unpack(b2.to_host()) if b2 else None)
+    eng.close()
+    t0 = time.perf_counter()
+    kind, orecs, oflat = oracle_flat_threaded(params, reads[0], reads[1], os.cpu_count() or 1)
+    sec = time.perf_counter() - t0
+    for k, (x, y) in enumerate(zip(recs, orecs)):
+        for name in x.dtype.names:
+            if name == "reserved":
+                continue
+            bad = np.nonzero(x[name] != y[name])[0]
+            assert bad.size == 0, f"oracle_check {cfg}: records[{k}].{name} differs for {bad.size} units, first {bad[0]}"
+    bad = np.nonzero(flat != oflat)[0]
+    assert bad.size == 0, f"oracle_check {cfg}: flat accumulators differ at {bad[:8]}"
+    return {"status": "ok", "units": units, "oracle": kind, "oracle_seconds": round(sec, 2),
+            "reads_passed": int(flat[L.filter_off]), "flat_u64": int(len(flat)),
+            "what": "first units of the timed stream: every record field and every flat accumulator entry == CPU oracle, bit-exact"}
+
+
+def cpu_reference_run(cfg, sample_reads, steps, warmup, torch_dev=None, sample_file=None):
     """The reference's own hot path on all host cores (oracle/_ref, else the oracle port
     single-threaded), on a bounded sample of the same synthetic workload."""
     import numpy as np
@@ -114,13 +211,13 @@ def cpu_reference_run(cfg, sample_reads, steps, warmup, torch_dev=None):
     from oracle import pyoracle
     c = workload.CONFIGS[cfg]
     opt = workload.options_for(cfg)
-    if torch_dev is not None:
-        import torch
-        b1, b2 = workload.generate(cfg, sample_reads, 0, torch_dev, None)
-        torch.cuda.synchronize()
-        r1 = batch.unpack(b1.to_host()); r2 = batch.unpack(b2.to_host()) if b2 else None
+    if sample_file is not None:
+        z = np.load(sample_file)
+        r1 = (z["s1"], z["q1"], z["o1"]); r2 = (z["s2"], z["q2"], z["o2"]) if "s2" in z.files else None
         sample = f"first {sample_reads} {'pairs' if c['paired'] else 'reads'} of the device-generated {cfg} stream"
-        del b1, b2
+    elif torch_dev is not None:
+        r1, r2 = device_sample(cfg, sample_reads, torch_dev)
+        sample = f"first {sample_reads} {'pairs' if c['paired'] else 'reads'} of the device-generated {cfg} stream"
     else:
         if c["paired"]:
             r1, r2 = synth.pe_novaseq(sample_reads, c["L"], seed=c["seed"], frag_mean=c["frag"][0], frag_sd=c["frag"][1])
@@ -149,27 +246,51 @@ def cpu_reference_run(cfg, sample_reads, steps, warmup, torch_dev=None):
             o.close()
     sec = sum(times) / len(times)
     return {"value": bases / sec / 1e9, "unit": "Gbases/s", "cores": cores, "kind": kind, "sample": sample,
-            "ms_per_step": sec * 1e3}
+            "ms_per_step": sec * 1e3, "reads": (r1, r2)}
+
+
+def per_unit_bytes(c):
+    per_read_bytes = ((c["L"] + 15) // 16 * 16) * 1.25 + 6 + 16
+    return per_read_bytes * (2 if c["paired"] else 1) + (24 if c["paired"] else 0)
+
+
+def config_dict(a, c, reads):
+    """`config` of the JSON line: the same keys and values from both arms (the reference arm times a bounded sample of this
+    workload and says so in cpu_baseline.sample)."""
+    nb = (reads + BATCH_READS - 1) // BATCH_READS
+    return {"workload": c["desc"], "config": a.config, "flags": c["cli"], "reads_per_gpu": reads, "read_length": c["L"],
+            "batches_per_step": nb, "batch_reads": BATCH_READS,
+            "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit_bytes(c) / 1e9)}
 
 
 def run_reference_arm(a):
+    """The reference's own hot path on the host cores.  This process loads neither libfqk.so nor CUDA: the sample (first
+    --cpu-sample units of the stream the B200 arm times) is produced by a helper process (--impl sample) and read from a
+    file; without a GPU the numpy generator stands in."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    import tempfile
     from fqtool_b200 import workload
-    dev = None
-    try:
-        import torch
-        if torch.cuda.is_available():
-            dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
-    except Exception:
-        dev = None
     c = workload.CONFIGS[a.config]
-    cb = cpu_reference_run(a.config, a.cpu_sample, a.steps, min(a.warmup, 1), dev)
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
+    path = os.path.join(tmpdir, f"fqk_sample_{os.getpid()}.npz")
+    sample_file = None
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "sample", "--config", a.config, "--cpu-sample",
+                            str(a.cpu_sample), "--sample-out", path], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+        if r.returncode == 0 and os.path.exists(path):
+            sample_file = path
+        else:
+            sys.stderr.write("bench.py --impl reference: no device sample (%s); using the numpy generator\n" % r.stderr.strip()[-300:])
+        cb = cpu_reference_run(a.config, a.cpu_sample, a.steps, a.warmup, None, sample_file)
+    finally:
+        if os.path.exists(path):
+            os.remove(path)
     line = {"impl": "reference", "metric": "Gbases/s per-read QC+trim", "value": cb["value"], "unit": "Gbases/s",
-            "n_gpus": a.gpus, "steps": a.steps, "warmup": min(a.warmup, 1), "ms_per_step": cb["ms_per_step"],
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": c["desc"], "flags": c["cli"], "config": a.config},
+            "config": config_dict(a, c, a.reads or c["reads"]),
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -262,12 +383,18 @@ class Job:
         alg = workload.algorithmic_bytes(self.cfg, per_launch_units)
         achieved = alg / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
         roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": ctx.peak, "unit": "GB/s",
-                    "frac": achieved / ctx.peak, "traffic": ctx.traffic.get(names[dom]), "peak_source": ctx.peak_src,
+                    "frac": achieved / ctx.peak, "traffic": ctx.traffic.get(self.cfg, {}).get(names[dom]),
+                    "traffic_source": "profiles/traffic.json: dram bytes read + written per launch of 4 M units, ncu --set full capture of this "
+                                      "kernel on this configuration (null = not captured for this configuration)",
+                    "peak_source": ctx.peak_src,
                     "algorithmic_bytes_per_launch": alg, "avg_launch_ms": per_launch_ms,
                     "kernel_ms_share": {names[s]: kms[s] / max(kms[abi.T_ALL], 1e-9) for s in names if kn[s]},
                     "ms_per_launch": {names[s]: kms[s] / kn[s] for s in names if kn[s]},
                     "whole_path_achieved": workload.algorithmic_bytes(self.cfg, self.units) * steps / (kms[abi.T_ALL] / 1e3) / 1e9
                     if kms[abi.T_ALL] > 0 else None}
+        if roofline["whole_path_achieved"]:
+            # all kernels of the path together (cfg4: k_se_v3 + k_kmer_se + k_dup), against the same peak
+            roofline["whole_path_frac"] = roofline["whole_path_achieved"] / ctx.peak
         return {"value": total_bases * steps / (ms_total / 1e3) / 1e9, "unit": "Gbases/s", "ms_per_step": ms_total / steps,
                 "finalize_ms": fin_ms, "steps": steps, "warmup": warmup, "units_per_gpu": self.units,
                 "units_total": total_units, "batches_per_step": self.nb, "gpu_launches": launches, "roofline": roofline,
@@ -393,6 +520,8 @@ def main():
     a = parse()
     if a.impl == "reference":
         return run_reference_arm(a)
+    if a.impl == "sample":
+        return write_sample(a)
     import numpy as np
     from fqtool_b200 import abi, workload
     ctx = Ctx(a)
@@ -401,8 +530,7 @@ def main():
     c = workload.CONFIGS[cfg]
 
     # ---- workload: per-GPU share, resident in HBM (weak scaling: fixed per GPU) ----
-    per_read_bytes = ((c["L"] + 15) // 16 * 16) * 1.25 + 6 + 16
-    per_unit = per_read_bytes * (2 if c["paired"] else 1) + (24 if c["paired"] else 0)
+    per_unit = per_unit_bytes(c)
     free_b, _ = torch.cuda.mem_get_info(dev)
     cap = int(free_b * 0.80 / per_unit)
     reads = max(1, a.reads or min(c["reads"], cap))
@@ -620,24 +748,30 @@ def main():
         if world > 1:
             mcheck = merge_check(ctx)
 
-    cpu_baseline = None
+    cpu_baseline = oracle_checks = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         ctx.free()
-        cb = cpu_reference_run(cfg, a.cpu_sample, 3, 1, dev)     # same protocol as the reference arm: 1 warm-up, mean of 3
+        cb = cpu_reference_run(cfg, a.cpu_sample, 3, 1, dev)
         cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         cpu_baseline["protocol"] = "1 warm-up run, mean of 3 timed runs"
+        # the checker: what the timed kernels compute on the first units of every timed stream == the CPU oracle
+        if a.check_units > 0:
+            oracle_checks = {}
+            nmain = min(a.check_units, reads)
+            oracle_checks[cfg] = oracle_check(ctx, cfg, nmain, cb["reads"] if nmain == a.cpu_sample else None)
+            del cb
+            for xc in extra:
+                oracle_checks[xc] = oracle_check(ctx, xc, min(a.check_units, extra[xc]["units_per_gpu"]))
+                ctx.free()
 
     if rank == 0:
         line = {"metric": "Gbases/s per-read QC+trim", "value": main_rec["value"], "unit": "Gbases/s", "n_gpus": world,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": main_rec["ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": c["desc"], "config": cfg, "flags": c["cli"], "reads_per_gpu": reads,
-                           "read_length": c["L"], "batches_per_step": nb, "batch_reads": BATCH_READS,
-                           "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % (reads * per_unit / 1e9),
-                           "impl": a.impl},
+                "config": config_dict(a, c, reads), "impl": a.impl,
                 "clocks": clocks, "e2e": e2e, "e2e_ascii": e2e_ascii, "e2e_text": e2e_text, "e2e_fastq": e2e_fastq, "gpu_launches": main_rec["gpu_launches"],
                 "roofline": main_rec["roofline"], "finalize_ms": main_rec["finalize_ms"], "cpu_baseline": cpu_baseline,
-                "configs": extra or None, "scaling_cfg5": scaling_cfg5, "merge_check": mcheck}
+                "configs": extra or None, "scaling_cfg5": scaling_cfg5, "merge_check": mcheck, "oracle_check": oracle_checks}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

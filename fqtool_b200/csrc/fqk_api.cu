@@ -351,7 +351,7 @@ static int launch_se(fqk_ctx* c, const DevBatch& B, fq_read_result* out){
     Timer all(c, FQK_T_ALL);
     // k-mers as a pass of their own (k_kmer_se) after a fused kernel that runs WITHOUT them: k_se_v3 has no k-mer code and
     // is twice as fast as k_fused_se_ws, whose k-mer counting costs another 2.3 ms per 4 M reads (tools/prof_cfg4_parts.py)
-    static const bool kmer_fused = getenv("FQK_KMER_FUSED") != nullptr;       // A/B switch: k-mers inside k_fused_se_ws as in round 1
+    static const bool kmer_fused = fqk_tuning_env("FQK_KMER_FUSED") != nullptr;       // A/B switch: k-mers inside k_fused_se_ws as in round 1
     DevParams Dn = c->D; Dn.P.kmer_len = 0;
     const bool ksplit = c->impl == 0 && c->D.P.kmer_len >= 4 && c->D.P.kmer_len <= 13 && !kmer_fused && fused_supported_se(Dn, B);
     if(ksplit){

@@ -794,8 +794,8 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
     if(variant == 0 && !D.P.kmer_len && v3_tile(W) > 0){
         // generic option sets (adapter by sequence, polyG / polyX, ...): the trim role is the long one (one lane per read,
         // dependent scalar chains), so it gets 11 working warps and the statistics 4 (FQK_V3_WIDE=0 keeps 7 + 8)
-        static const bool wide_on = !(getenv("FQK_V3_WIDE") && atoi(getenv("FQK_V3_WIDE")) == 0);
-        static const int wide_fast = getenv("FQK_V3_WIDE_FAST") ? atoi(getenv("FQK_V3_WIDE_FAST")) : 0;   // experiment: 4 + 11 warps for the fast option sets too
+        static const bool wide_on = !(fqk_tuning_env("FQK_V3_WIDE") && atoi(fqk_tuning_env("FQK_V3_WIDE")) == 0);
+        static const int wide_fast = fqk_tuning_env("FQK_V3_WIDE_FAST") ? atoi(fqk_tuning_env("FQK_V3_WIDE_FAST")) : 0;   // experiment: 4 + 11 warps for the fast option sets too
         const bool wide = wide_on && (!v3_fast_options(D.P) || wide_fast) && v3_tile(W, 128) > 0;
         const int T = wide ? v3_tile(W, 128) : v3_tile(W);
         int rpb = (int)((B.n + sms - 1) / sms);
@@ -803,7 +803,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         rpb = (rpb + T - 1) / T * T;
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const size_t sm = v3_layout(W, T).total + 128;
-        static const int dbg = getenv("FQK_V3_DEBUG") ? atoi(getenv("FQK_V3_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
+        static const int dbg = fqk_tuning_env("FQK_V3_DEBUG") ? atoi(fqk_tuning_env("FQK_V3_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
         if(v3_fast_options(D.P) && wide) k_se_v3<true, 128><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         else if(v3_fast_options(D.P)) k_se_v3<true><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
         else if(wide) k_se_v3<false, 128><<<grid, V3_THREADS, sm, st>>>(D, B, out, flat, W, T, rpb, dbg);
@@ -818,7 +818,7 @@ int fused_launch_se(const DevParams& D, const DevBatch& B, fq_read_result* out, 
         const int grid = (int)((B.n + rpb - 1) / rpb);
         const StatsMode M{0, 0, 0, 0, 2, nullptr, nullptr, nullptr, nullptr};
         const size_t sm = ws_smem_bytes(W, T, D.P.kmer_len);
-        static const int split128 = getenv("FQK_WS_SPLIT128") ? 1 : 0;   // tuning aid: 4 + 16 warps measured slower than 8 + 8 on B200
+        static const int split128 = fqk_tuning_env("FQK_WS_SPLIT128") ? 1 : 0;   // tuning aid: 4 + 16 warps measured slower than 8 + 8 on B200
         if(W <= 128 && split128){                              // a read fits the 128 statistics threads
             if(D.P.kmer_len) k_fused_se_ws<0, true, 128><<<grid, 640, sm, st>>>(D, B, out, flat, W, T, rpb, M);
             else k_fused_se_ws<0, false, 128><<<grid, 640, sm, st>>>(D, B, out, flat, W, T, rpb, M);
@@ -883,9 +883,9 @@ static int pe4_ppb(uint32_t n, int sms, int T){
 }
 int pe4_launch(const DevParams& D, const DevBatch& B1, const DevBatch& B2, fq_read_result* o1, fq_read_result* o2,
                fq_pair_result* op, uint64_t* flat, int sms, cudaStream_t st){
-    static const int dbg = getenv("FQK_V4_DEBUG") ? atoi(getenv("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
-    static const bool fusedOnly = getenv("FQK_V4_SPLIT") && atoi(getenv("FQK_V4_SPLIT")) == 0;   // A/B switch: the one-kernel form
-    static const bool nolean = getenv("FQK_V4_GENERIC") != nullptr;       // A/B switch: the general code for every option set
+    static const int dbg = fqk_tuning_env("FQK_V4_DEBUG") ? atoi(fqk_tuning_env("FQK_V4_DEBUG")) : 0;   // timing experiments: 1 no trim work, 2 no statistics work
+    static const bool fusedOnly = fqk_tuning_env("FQK_V4_SPLIT") && atoi(fqk_tuning_env("FQK_V4_SPLIT")) == 0;   // A/B switch: the one-kernel form
+    static const bool nolean = fqk_tuning_env("FQK_V4_GENERIC") != nullptr;       // A/B switch: the general code for every option set
     const int ml = pe4_maxlen(B1, B2);
     V4Plan p = v4_plan(D, ml, g_smem_optin, 0);
     if(!p.ok) return -1;

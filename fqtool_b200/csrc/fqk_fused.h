@@ -1,6 +1,16 @@
 // fqk_fused.h -- fused single-end kernel (trim + filter + pre/post stats in one HBM pass); see fqk_fused.cu
 #pragma once
+#include <cstdlib>
 #include "fqk_trim.cuh"
+
+// A/B and timing switches (FQK_V3_DEBUG, FQK_V4_DEBUG, FQK_V4_T ... : some of them SKIP work) exist only in a library built
+// with -DFQK_TUNING_SWITCHES (FQK_NVCC_EXTRA=-DFQK_TUNING_SWITCHES python -m fqtool_b200.build --force, as tools/gpu_pe_*.sh
+// expect).  The shipped libfqk.so reads no environment variable on its kernel path.
+#ifdef FQK_TUNING_SWITCHES
+inline const char* fqk_tuning_env(const char* name){ return getenv(name); }
+#else
+inline const char* fqk_tuning_env(const char*){ return nullptr; }
+#endif
 void fused_configure(const cudaDeviceProp& prop);
 bool fused_supported_se(const DevParams& D, const DevBatch& B);
 // returns the number of kernels launched, or < 0 on error

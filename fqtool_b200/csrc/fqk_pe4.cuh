@@ -1204,8 +1204,8 @@ inline V4Plan v4_plan(const DevParams& D, int maxlen, size_t smem_optin, int mod
             if(score > best){ best = score; bestT = T; bestNS = NS; }
         }
     if(best < 0) return p;
-    static const int envT = getenv("FQK_V4_T") ? atoi(getenv("FQK_V4_T")) : 0, envNS = getenv("FQK_V4_NS") ? atoi(getenv("FQK_V4_NS")) : 0;
-    if(mode == (getenv("FQK_V4_TMODE") ? atoi(getenv("FQK_V4_TMODE")) : 0) && envT > 0 && envNS >= 2 && envNS <= (st ? 4 : 12) && envT % 32 == 0 &&
+    static const int envT = fqk_tuning_env("FQK_V4_T") ? atoi(fqk_tuning_env("FQK_V4_T")) : 0, envNS = fqk_tuning_env("FQK_V4_NS") ? atoi(fqk_tuning_env("FQK_V4_NS")) : 0;
+    if(mode == (fqk_tuning_env("FQK_V4_TMODE") ? atoi(fqk_tuning_env("FQK_V4_TMODE")) : 0) && envT > 0 && envNS >= 2 && envNS <= (st ? 4 : 12) && envT % 32 == 0 &&
        (size_t)v4_layout(p.Wr, p.Wm, envT, envNS, P.insert_size_max + 1, st).total + 128 <= budget){ bestT = envT; bestNS = envNS; }   // timing experiments
     p.T = bestT; p.NS = bestNS;
     p.smem = v4_layout(p.Wr, p.Wm, p.T, p.NS, P.insert_size_max + 1, st).total + 128;

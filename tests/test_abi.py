@@ -111,3 +111,14 @@ def test_invalid_params_rejected():
         for k, v in mut.items():
             setattr(p, k, v)
         assert lib.fqk_create(C.byref(h), C.byref(p), 0, 0, 1, None) == -1, mut
+
+
+def test_shipped_library_has_no_work_skipping_switches():
+    """The timing / A-B switches of the kernels (FQK_V3_DEBUG, FQK_V4_DEBUG ...: some skip work) are compiled in only with
+    -DFQK_TUNING_SWITCHES; the library the tests and bench.py load must not even contain their names."""
+    from fqtool_b200 import build
+    if "FQK_TUNING_SWITCHES" in os.environ.get("FQK_NVCC_EXTRA", ""):
+        pytest.skip("tuning build")
+    blob = open(build.LIB, "rb").read()
+    for name in (b"FQK_V3_DEBUG", b"FQK_V4_DEBUG", b"FQK_V3_WIDE_FAST", b"FQK_V4_TMODE", b"FQK_KMER_FUSED", b"FQK_V4_SPLIT"):
+        assert name not in blob, name

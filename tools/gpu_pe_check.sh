@@ -1,4 +1,5 @@
 #!/bin/bash
+# NEEDS a tuning build: FQK_NVCC_EXTRA=-DFQK_TUNING_SWITCHES python -m fqtool_b200.build --force (the shipped libfqk.so ignores FQK_V4_* / FQK_V3_*)
 # GPU check of the fused paired-end kernel: parity tests, then kernel timings with role switches.
 tag=${1:-pe}
 o=gpurun_out; mkdir -p $o

@@ -1,4 +1,5 @@
 #!/bin/bash
+# NEEDS a tuning build: FQK_NVCC_EXTRA=-DFQK_TUNING_SWITCHES python -m fqtool_b200.build --force (the shipped libfqk.so ignores FQK_V4_* / FQK_V3_*)
 # per-kernel times of the split paired-end path (ncu launch list) and tile-shape experiments for the trim kernel
 o=gpurun_out; mkdir -p $o
 for c in ${1:-cfg3 cfg5}; do

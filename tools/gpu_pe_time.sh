@@ -1,4 +1,5 @@
 #!/bin/bash
+# NEEDS a tuning build: FQK_NVCC_EXTRA=-DFQK_TUNING_SWITCHES python -m fqtool_b200.build --force (the shipped libfqk.so ignores FQK_V4_* / FQK_V3_*)
 # kernel timings of the fused paired-end kernel with role/part switches (FQK_V4_DEBUG bits: 1 no trim work, 2 no statistics
 # work, 4 no first analyze, 8 no second analyze, 16 no tail corrections, 32 no polyG)
 tag=${1:-pe}; cfgs=${2:-cfg3}; dbgs=${3:-0 2}

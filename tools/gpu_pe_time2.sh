@@ -1,4 +1,5 @@
 #!/bin/bash
+# NEEDS a tuning build: FQK_NVCC_EXTRA=-DFQK_TUNING_SWITCHES python -m fqtool_b200.build --force (the shipped libfqk.so ignores FQK_V4_* / FQK_V3_*)
 # like gpu_pe_time.sh with tile size / stage count overrides: gpu_pe_time2.sh <tag> <cfg> "<T:NS:dbg> ..."
 tag=${1:-pe}; c=${2:-cfg3}; shift 2
 o=gpurun_out; mkdir -p $o

@@ -50,7 +50,8 @@ def full(rep, out):
     open(out, "w").write("\n".join(lines) + "\n")
     tj = os.path.join(os.path.dirname(out), "traffic.json")
     old = json.load(open(tj)) if os.path.exists(tj) else {}
-    old.update(traffic)
+    # traffic.json is keyed by configuration, then kernel (bench.py reads [cfg][kernel]); NCU_CFG names the configuration
+    old.setdefault(os.environ.get("NCU_CFG", "other"), {}).update(traffic)
     json.dump(old, open(tj, "w"), indent=1, sort_keys=True)
     print(open(out).read())
 
