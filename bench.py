@@ -400,6 +400,60 @@ class Job:
                 "units_total": total_units, "batches_per_step": self.nb, "gpu_launches": launches, "roofline": roofline,
                 "flags": self.c["cli"]}
 
+    def e2e(self, steps):
+        """End to end through the host-buffer C-ABI call for this configuration: every batch of the step goes H2D from pinned
+        host memory, through the kernels, records D2H (fqk_process_pe / fqk_process_se, synchronous), then fqk_finalize.
+        Up to two distinct pinned host batches are cycled.  Median over steps of the max over ranks (wall clock)."""
+        import torch
+        from fqtool_b200 import abi
+        ctx, eng = self.ctx, self.eng
+        paired = self.c["paired"]
+        n_host = min(2, self.nb)
+        hbs = [(self.batches[i][0].to_host(pinned=True), self.batches[i][1].to_host(pinned=True) if paired else None) for i in range(n_host)]
+        pin = lambda nbytes: torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        hout = [(pin(h[0].n * 16), pin(h[0].n * 16) if paired else None, pin(h[0].n * 24) if paired else None) for h in hbs]
+        h2d = d2h = units = 0
+
+        def step():
+            nonlocal h2d, d2h, units
+            h2d = d2h = units = 0
+            pending = None
+            for i in range(self.nb):
+                (h1, h2), (r1, r2, rp) = hbs[i % n_host], hout[i % n_host]
+                if paired:
+                    eng.process_pe(h1, h2, (r1.numpy().view(abi.READ_RESULT_DTYPE), r2.numpy().view(abi.READ_RESULT_DTYPE),
+                                            rp.numpy().view(abi.PAIR_RESULT_DTYPE)))
+                    h2d += h1.nbytes + h2.nbytes; d2h += h1.n * (16 + 16 + 24)
+                else:
+                    t = eng.submit_se(h1, r1.numpy().view(abi.READ_RESULT_DTYPE))     # two packs in flight
+                    if pending is not None:
+                        eng.wait(pending)
+                    pending = t
+                    h2d += h1.nbytes; d2h += h1.n * 16
+                units += h1.n
+            if pending is not None:
+                eng.wait(pending)
+            return eng.finalize()
+        eng.reset()
+        step()
+        eng.reset()
+        times = []
+        for _ in range(max(steps, 1)):
+            ctx.barrier()
+            t0 = time.perf_counter()
+            flat = step()
+            ctx.barrier()
+            times.append(ctx.max_over_ranks(time.perf_counter() - t0))
+        med = sorted(times)[len(times) // 2]
+        bases = units * self.c["L"] * (2 if paired else 1) * ctx.world
+        return {"value": bases / med / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h + flat.nbytes,
+                "steps": len(times), "ms_per_step": med * 1e3, "h2d_gbs_per_gpu": h2d / med / 1e9,
+                "note": (f"{self.nb} synchronous fqk_process_pe calls + one fqk_finalize per step, {n_host} distinct pinned host batches "
+                         "(fq_batch layout); there is no pipelined paired-end entry point yet, so upload, kernels and download of a "
+                         "batch do not overlap") if paired else
+                        (f"{self.nb} fqk_submit_se / fqk_wait calls (two packs in flight) + one fqk_finalize per step, {n_host} distinct "
+                         "pinned host batches (fq_batch layout)")}
+
     def close(self):
         self.batches = self.outs = None
         self.eng.close()
@@ -590,6 +644,39 @@ def main():
            "note": f"{nb} fqk_submit_se/fqk_wait (SE, two packs in flight) or fqk_process_pe calls + one fqk_finalize per step over "
                    f"{n_host} distinct pinned host batches of {BATCH_READS} reads (already in the fq_batch layout; host packing is outside)"}
 
+    # ---- what the box allows: the same bytes moved by bare copies, no library and no kernel ----
+    # (all ranks at once, like the step: at N > 1 this is the ceiling of N GPUs pulling pinned host memory over PCIe together)
+    up = [torch.empty(h[0].nbytes + (h[1].nbytes if h[1] else 0), dtype=torch.uint8, pin_memory=True) for h in hbs]
+    d_in = [torch.empty_like(up[0], device=dev) for _ in range(2)]
+    d_out = torch.empty(hbs[0][0].n * (56 if c["paired"] else 16), dtype=torch.uint8, device=dev)
+    down = [torch.empty(d_out.numel(), dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+    s_up, s_dn = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def copy_step():
+        for i in range(nb):
+            with torch.cuda.stream(s_up):
+                d_in[i & 1].copy_(up[i % n_host], non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                down[i & 1].copy_(d_out, non_blocking=True)
+        s_up.synchronize(); s_dn.synchronize()
+    copy_step()
+    ctimes = []
+    for _ in range(3):
+        ctx.barrier()
+        t0 = time.perf_counter()
+        copy_step()
+        ctx.barrier()
+        ctimes.append(ctx.max_over_ranks(time.perf_counter() - t0))
+    cmed = sorted(ctimes)[1]
+    copy_bytes = nb * up[0].numel()
+    e2e["copy_ceiling"] = {"value": e2e_bases / cmed / 1e9, "unit": "Gbases/s", "ms_per_step": cmed * 1e3,
+                           "h2d_gbs_per_gpu": copy_bytes / cmed / 1e9, "h2d_gbs_e2e_per_gpu": h2d / med / 1e9,
+                           "e2e_over_ceiling": (e2e_bases / med) / (e2e_bases / cmed),
+                           "note": "the step's H2D and D2H bytes as bare cudaMemcpyAsync between pinned host and device buffers on two "
+                                   "streams (upload and download overlapped), all ranks at once, no library call and no kernel: "
+                                   "the end-to-end number cannot exceed this on this box"}
+    del up, d_in, d_out, down
+
     # ---- the same through the ASCII entry point (FASTQ characters in, packing on the GPU) ----
     e2e_ascii = e2e_text = e2e_fastq = None
     if not c["paired"]:
@@ -729,6 +816,7 @@ def main():
             j = Job(ctx, xc, a.extra_units, rank * a.extra_units)
             r = j.timed(a.extra_steps, 3)
             r["scaling"] = "weak"; r["workload"] = workload.CONFIGS[xc]["desc"]
+            r["e2e"] = j.e2e(3)
             extra[xc] = r
             j.close(); del j; ctx.free()
         # cfg5: strong scaling of a fixed total, contiguous shards by global pair index
@@ -739,6 +827,7 @@ def main():
         j = Job(ctx, "cfg5", hi - lo, lo)
         r = j.timed(max(3, a.extra_steps // 2 + 1), 3)
         r["scaling"] = "strong"; r["workload"] = workload.CONFIGS["cfg5"]["desc"]; r["pairs_total"] = tot
+        r["e2e"] = j.e2e(3)
         extra["cfg5"] = r
         scaling_cfg5 = {"n_gpus": world, "pairs_total": tot, "pairs_per_gpu": hi - lo, "value": r["value"], "unit": "Gbases/s",
                         "ms_per_step": r["ms_per_step"], "finalize_ms": r["finalize_ms"], "scaling": "strong",
