@@ -402,8 +402,8 @@ class Job:
 
     def e2e(self, steps):
         """End to end through the host-buffer C-ABI call for this configuration: every batch of the step goes H2D from pinned
-        host memory, through the kernels, records D2H (fqk_process_pe / fqk_process_se, synchronous), then fqk_finalize.
-        Up to two distinct pinned host batches are cycled.  Median over steps of the max over ranks (wall clock)."""
+        host memory, through the kernels, records D2H, then fqk_finalize.
+        Two packs in flight (fqk_submit_pe / fqk_submit_se + fqk_wait); up to two distinct pinned host batches are cycled.  Median over steps of the max over ranks (wall clock)."""
         import torch
         from fqtool_b200 import abi
         ctx, eng = self.ctx, self.eng
@@ -421,15 +421,15 @@ class Job:
             for i in range(self.nb):
                 (h1, h2), (r1, r2, rp) = hbs[i % n_host], hout[i % n_host]
                 if paired:
-                    eng.process_pe(h1, h2, (r1.numpy().view(abi.READ_RESULT_DTYPE), r2.numpy().view(abi.READ_RESULT_DTYPE),
-                                            rp.numpy().view(abi.PAIR_RESULT_DTYPE)))
+                    t = eng.submit_pe(h1, h2, (r1.numpy().view(abi.READ_RESULT_DTYPE), r2.numpy().view(abi.READ_RESULT_DTYPE),
+                                               rp.numpy().view(abi.PAIR_RESULT_DTYPE)))   # two pair packs in flight
                     h2d += h1.nbytes + h2.nbytes; d2h += h1.n * (16 + 16 + 24)
                 else:
                     t = eng.submit_se(h1, r1.numpy().view(abi.READ_RESULT_DTYPE))     # two packs in flight
-                    if pending is not None:
-                        eng.wait(pending)
-                    pending = t
                     h2d += h1.nbytes; d2h += h1.n * 16
+                if pending is not None:
+                    eng.wait(pending)
+                pending = t
                 units += h1.n
             if pending is not None:
                 eng.wait(pending)
@@ -448,11 +448,8 @@ class Job:
         bases = units * self.c["L"] * (2 if paired else 1) * ctx.world
         return {"value": bases / med / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h + flat.nbytes,
                 "steps": len(times), "ms_per_step": med * 1e3, "h2d_gbs_per_gpu": h2d / med / 1e9,
-                "note": (f"{self.nb} synchronous fqk_process_pe calls + one fqk_finalize per step, {n_host} distinct pinned host batches "
-                         "(fq_batch layout); there is no pipelined paired-end entry point yet, so upload, kernels and download of a "
-                         "batch do not overlap") if paired else
-                        (f"{self.nb} fqk_submit_se / fqk_wait calls (two packs in flight) + one fqk_finalize per step, {n_host} distinct "
-                         "pinned host batches (fq_batch layout)")}
+                "note": f"{self.nb} {'fqk_submit_pe' if paired else 'fqk_submit_se'} / fqk_wait calls (two packs in flight) + one "
+                        f"fqk_finalize per step, {n_host} distinct pinned host batches (fq_batch layout)"}
 
     def close(self):
         self.batches = self.outs = None
@@ -617,8 +614,11 @@ def main():
                 pending = t
                 h2d += h1.nbytes; d2h += h1.n * 16
             else:
-                eng.process_pe(h1, h2, (r1.numpy().view(abi.READ_RESULT_DTYPE), r2.numpy().view(abi.READ_RESULT_DTYPE),
-                                        rp.numpy().view(abi.PAIR_RESULT_DTYPE)))
+                t = eng.submit_pe(h1, h2, (r1.numpy().view(abi.READ_RESULT_DTYPE), r2.numpy().view(abi.READ_RESULT_DTYPE),
+                                           rp.numpy().view(abi.PAIR_RESULT_DTYPE)))
+                if pending is not None:
+                    eng.wait(pending)
+                pending = t
                 h2d += h1.nbytes + h2.nbytes; d2h += h1.n * (16 + 16 + 24)
             e2e_units += h1.n
         if pending is not None:
@@ -641,7 +641,7 @@ def main():
            "d2h_bytes_per_step": d2h + d2h_final, "steps": len(ts), "ms_per_step": med * 1e3,
            "statistic": "median over steps of the max over ranks", "best": e2e_bases / ts[0] / 1e9, "worst": e2e_bases / ts[-1] / 1e9,
            "ms_per_step_all": [round(t * 1e3, 2) for t in times],
-           "note": f"{nb} fqk_submit_se/fqk_wait (SE, two packs in flight) or fqk_process_pe calls + one fqk_finalize per step over "
+           "note": f"{nb} fqk_submit_se / fqk_submit_pe + fqk_wait calls (two packs in flight) + one fqk_finalize per step over "
                    f"{n_host} distinct pinned host batches of {BATCH_READS} reads (already in the fq_batch layout; host packing is outside)"}
 
     # ---- what the box allows: the same bytes moved by bare copies, no library and no kernel ----

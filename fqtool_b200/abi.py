@@ -123,7 +123,7 @@ EXPORTS = [
     "fqk_prepass_kmer_counts", "fqk_prepass_seed_hits", "fqk_process_se_text", "fqk_process_pe_text",
     "fqk_process_se_fastq", "fqk_process_pe_fastq", "fqk_submit_se_ascii",
     "fqk_submit_se_text", "fqk_wait_text", "fqk_submit_se_fastq", "fqk_wait_fastq",
-    "fqk_prepass_kmer_counts_static",
+    "fqk_prepass_kmer_counts_static", "fqk_submit_pe",
 ]
 
 _lib = None
@@ -153,6 +153,7 @@ def load():
     lib.fqk_process_pe_ascii.argtypes = [vp, P(FqAsciiBatch), P(FqAsciiBatch), vp, vp, vp]; lib.fqk_process_pe_ascii.restype = i32
     lib.fqk_submit_se.argtypes = [vp, P(FqBatch), vp, P(u64)]; lib.fqk_submit_se.restype = i32
     lib.fqk_wait.argtypes = [vp, u64]; lib.fqk_wait.restype = i32
+    lib.fqk_submit_pe.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp, P(u64)]; lib.fqk_submit_pe.restype = i32
     lib.fqk_submit_se_ascii.argtypes = [vp, P(FqAsciiBatch), vp, P(u64)]; lib.fqk_submit_se_ascii.restype = i32
     lib.fqk_process_se_device.argtypes = [vp, P(FqBatch), vp]; lib.fqk_process_se_device.restype = i32
     lib.fqk_process_pe_device.argtypes = [vp, P(FqBatch), P(FqBatch), vp, vp, vp]

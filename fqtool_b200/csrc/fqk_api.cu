@@ -94,6 +94,7 @@ struct fqk_ctx {
     // pipelined single-end path (fqk_submit_se / fqk_wait): two slots, copies on their own streams
     cudaStream_t h2d = nullptr, d2h = nullptr;
     StagedBatch pst[2]; DevBuf pres[2];
+    StagedBatch pst2[2]; DevBuf pres2[2], presp[2];   // read 2 and the pair records of a pipelined paired-end pack (fqk_submit_pe)
     cudaEvent_t evH2D[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr}, evD2H[2] = {nullptr, nullptr};
     uint32_t* perr_host = nullptr;            // pinned: error flag snapshot of each slot
     uint64_t submitted = 0;
@@ -284,6 +285,8 @@ extern "C" void fqk_destroy(fqk_ctx* c){
     for(auto& e : c->evpool) cudaEventDestroy(e);
     for(int i = 0; i < 2; ++i){
         c->pst[i].off.release(); c->pst[i].len.release(); c->pst[i].b2.release(); c->pst[i].q.release(); c->pres[i].release();
+        c->pst2[i].off.release(); c->pst2[i].len.release(); c->pst2[i].b2.release(); c->pst2[i].q.release();
+        c->pres2[i].release(); c->presp[i].release();
         if(c->evH2D[i]) cudaEventDestroy(c->evH2D[i]);
         if(c->evK[i]) cudaEventDestroy(c->evK[i]);
         if(c->evD2H[i]) cudaEventDestroy(c->evD2H[i]);
@@ -1109,6 +1112,48 @@ extern "C" int fqk_submit_se(fqk_ctx* c, const fq_batch* in, fq_read_result* out
     CU(cudaEventRecord(c->evK[s], c->stream));
     CU(cudaStreamWaitEvent(c->d2h, c->evK[s], 0));
     CU(cudaMemcpyAsync(out, c->pres[s].p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaEventRecord(c->evD2H[s], c->d2h));
+    *ticket = t; c->submitted = t + 1;
+    return 0;
+}
+
+// Pipelined form of fqk_process_pe (the reference runs up to 16 workers through processPairEnd side by side,
+// /root/reference/src/peprocessor.cpp:546-566; here ONE thread keeps two pair packs in flight): same slots, streams and
+// events as fqk_submit_se, both mates and three record arrays per slot.  fqk_wait(ticket) completes it.
+extern "C" int fqk_submit_pe(fqk_ctx* c, const fq_batch* r1, const fq_batch* r2, fq_read_result* o1, fq_read_result* o2,
+                             fq_pair_result* op, uint64_t* ticket){
+    if(!c || !r1 || !r2 || !ticket) return FQK_E_INVALID;
+    if(!c->D.P.is_paired) return fail(c, FQK_E_INVALID, "context was created for single-end data");
+    if(r1->n_reads != r2->n_reads) return fail(c, FQK_E_INVALID, "read1/read2 batches differ in size");
+    if(c->D.P.correction_enabled)
+        return fail(c, FQK_E_INVALID, "base correction (-c) returns a per-pack edit list (fqk_get_corrections): use fqk_process_pe");
+    if(r1->n_reads && (!o1 || !o2 || !op)) return FQK_E_INVALID;
+    CU(cudaSetDevice(c->device));
+    int rcp = pipe_init(c); if(rcp) return rcp;
+    const uint64_t t = c->submitted;
+    const int s = (int)(t & 1);
+    const size_t n = r1->n_reads;
+    if(t >= 2){                                                         // the slot's previous pack has left the device
+        CU(cudaEventSynchronize(c->evD2H[s]));
+        note_pack_error(c, c->perr_host[s]);
+    }
+    if(n == 0){ CU(cudaEventRecord(c->evD2H[s], c->d2h)); *ticket = t; c->submitted = t + 1; return 0; }
+    if(c->pres[s].ensure(n * sizeof(fq_read_result)) || c->pres2[s].ensure(n * sizeof(fq_read_result)) ||
+       c->presp[s].ensure(n * sizeof(fq_pair_result))) return fail(c, FQK_E_NOMEM, "result allocation failed");
+    CU(cudaStreamWaitEvent(c->h2d, c->evK[s], 0));                      // staging of this slot is free again
+    int rc = stage(c, c->pst[s], r1, c->h2d); if(rc) return rc;
+    rc = stage(c, c->pst2[s], r2, c->h2d); if(rc) return rc;
+    CU(cudaEventRecord(c->evH2D[s], c->h2d));
+    CU(cudaStreamWaitEvent(c->stream, c->evH2D[s], 0));
+    rc = launch_pe(c, c->pst[s].dev, c->pst2[s].dev, (fq_read_result*)c->pres[s].p, (fq_read_result*)c->pres2[s].p,
+                   (fq_pair_result*)c->presp[s].p);
+    if(rc) return rc;
+    CU(cudaEventRecord(c->evK[s], c->stream));
+    CU(cudaStreamWaitEvent(c->d2h, c->evK[s], 0));
+    CU(cudaMemcpyAsync(o1, c->pres[s].p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaMemcpyAsync(o2, c->pres2[s].p, n * sizeof(fq_read_result), cudaMemcpyDeviceToHost, c->d2h));
+    CU(cudaMemcpyAsync(op, c->presp[s].p, n * sizeof(fq_pair_result), cudaMemcpyDeviceToHost, c->d2h));
     CU(cudaMemcpyAsync(&c->perr_host[s], c->err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->d2h));
     CU(cudaEventRecord(c->evD2H[s], c->d2h));
     *ticket = t; c->submitted = t + 1;

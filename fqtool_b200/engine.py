@@ -195,6 +195,15 @@ class Engine:
         self._check(self.lib.fqk_submit_se(self.h, C.byref(b), abi.ptr(out), C.byref(t)), "fqk_submit_se")
         return t.value
 
+    def submit_pe(self, batch1, batch2, out):
+        """Pipelined fqk_process_pe: returns a ticket; the batches and out = (records1, records2, pairs) must stay alive
+        until wait(ticket)."""
+        b1, b2 = batch1.c_struct(), batch2.c_struct()
+        t = C.c_uint64(0)
+        self._check(self.lib.fqk_submit_pe(self.h, C.byref(b1), C.byref(b2), abi.ptr(out[0]), abi.ptr(out[1]), abi.ptr(out[2]),
+                                           C.byref(t)), "fqk_submit_pe")
+        return t.value
+
     def submit_se_ascii(self, reads, out, first_index=0):
         """Pipelined fqk_process_se_ascii; returns (ticket, keep): `keep` and `out` must stay alive until wait(ticket)."""
         b, keep = self._ascii(reads, first_index)

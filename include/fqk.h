@@ -360,6 +360,12 @@ int  fqk_submit_se(fqk_ctx* ctx, const fq_batch* in, fq_read_result* out, uint64
 /* the same for FASTQ characters (fq_ascii_batch): per-read offsets, lengths and the packed layout are all derived on the
  * device, the call only enqueues copies and kernels; in->off / seq / qual must stay valid until fqk_wait */
 int  fqk_submit_se_ascii(fqk_ctx* ctx, const fq_ascii_batch* in, fq_read_result* out, uint64_t* ticket);
+/* the same for pairs (PairEndProcessor's workers run side by side, /root/reference/src/peprocessor.cpp:546-566; here one
+ * caller thread keeps two pair packs in flight): both batches and the three record arrays must stay valid until
+ * fqk_wait(ticket).  Not available with correction_enabled (the edit list of fqk_get_corrections belongs to ONE pack):
+ * FQK_E_INVALID, use fqk_process_pe. */
+int  fqk_submit_pe(fqk_ctx* ctx, const fq_batch* r1, const fq_batch* r2, fq_read_result* out1, fq_read_result* out2,
+                   fq_pair_result* pairs, uint64_t* ticket);
 int  fqk_wait(fqk_ctx* ctx, uint64_t ticket);
 
 /*

@@ -91,6 +91,38 @@ def test_pipelined_submit_wait_matches_sync():
     e.close()
 
 
+@pytest.mark.parametrize("name", ["cfg3", "pe_dup_kmer", "cfg5"])
+def test_pipelined_submit_pe_matches_sync(name):
+    """fqk_submit_pe / fqk_wait (two pair packs in flight) give the same records, accumulators and duplication table as
+    fqk_process_pe, i.e. as the oracle; with -c the pipelined form is refused."""
+    from fqtool_b200 import abi, batch
+    from fqtool_b200.engine import Engine, FqkError
+    opt = configs.options(name, max_cycles=320)
+    r1, r2 = synth.pe_novaseq(9001, 150, seed=31, frag_mean=230, frag_sd=80)
+    want = util.run_oracle(opt, r1, r2)
+    e = Engine(opt.to_params())
+    bounds = np.linspace(0, 9001, 8).astype(int)
+    packs = [(batch.pack(batch.slice_reads(r1, lo, hi), int(lo)), batch.pack(batch.slice_reads(r2, lo, hi), int(lo)))
+             for lo, hi in zip(bounds[:-1], bounds[1:])]
+    outs = [(np.zeros(p[0].n, dtype=abi.READ_RESULT_DTYPE), np.zeros(p[0].n, dtype=abi.READ_RESULT_DTYPE),
+             np.zeros(p[0].n, dtype=abi.PAIR_RESULT_DTYPE)) for p in packs]
+    pending = None
+    for (p1, p2), o in zip(packs, outs):
+        t = e.submit_pe(p1, p2, o)
+        if pending is not None:
+            e.wait(pending)
+        pending = t
+    e.wait(pending)
+    recs = tuple(np.concatenate([o[k] for o in outs]) for k in range(3))
+    got = (recs, e.finalize(), e.dup_table() if opt.duplicate.enabled else None)
+    util.assert_same(got, want[:3])
+    e.close()
+    e = Engine(configs.options("pe_correct_merge").to_params())
+    with pytest.raises(FqkError):
+        e.submit_pe(packs[0][0], packs[0][1], outs[0])
+    e.close()
+
+
 @pytest.mark.parametrize("name", ["cfg2", "cfg4", "cfg3", "pe_correct_merge"])
 def test_ascii_entry_points_match_packed_path(name):
     """fqk_process_*_ascii (device-side packing) against the ORACLE (and hence the host-packed path); foreign alphabet is
