@@ -12,5 +12,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 for c in cfg2 cfg3 cfg4 cfg5; do
     timeout 400 ncu --set full --clock-control none -k regex:'k_se_v3|k_pe_v4|k_kmer_se|k_dup$' -c 3 -f -o $o/${tag}_$c \
         python tools/prof_run.py $c 4000000 1 > $o/${tag}_ncu_$c.log 2>&1; echo "$c full capture rc=$?"
+    # gpurun brings back at most 64 MiB: keep the raw metric table, drop the report
+    ncu -i $o/${tag}_$c.ncu-rep --page raw --csv > $o/${tag}_${c}_raw.csv 2>> $o/${tag}_ncu_$c.log && rm -f $o/${tag}_$c.ncu-rep
 done
 ls -la $o/${tag}_*
